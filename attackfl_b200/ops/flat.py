@@ -1,0 +1,194 @@
+"""Python bindings of the flat-vector kernels (K1/K2 FedAvg+moments, K4 craft, K6 select, T8 optimisers,
+K5a/K5b hyper-network).  Every function dispatches on the tensor's device: CUDA tensors go to the sm_100a
+library, CPU tensors to the CPU twin built from the same sources."""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import native
+from .native import check, lib_for, ptr, stream_ptr
+
+c_i, c_f, c_i64, c_u64, c_u32 = ctypes.c_int, ctypes.c_float, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint32
+MAX_ATT = 4
+BETAS = (0.9, 0.999)
+EPS = 1e-8
+
+
+def adam_flat(w, g, m, v, lr: float, step: int, betas=BETAS, eps: float = EPS, gscale: Optional[torch.Tensor] = None):
+    """In-place Adam on flat fp32 tensors (any shape, numel % 4 == 0); ``step`` is 1-based."""
+    lib = lib_for(w)
+    rc = lib.afl_adam_flat(ptr(w), ptr(g), ptr(m), ptr(v), c_i64(w.numel()), c_f(lr), c_f(betas[0]), c_f(betas[1]),
+                           c_f(eps), c_i(step), ptr(gscale), stream_ptr(w))
+    check(lib, rc, "afl_adam_flat")
+
+
+def sgdm_flat(w, g, buf, lr: float, momentum: float, first_step: bool, gscale: Optional[torch.Tensor] = None):
+    lib = lib_for(w)
+    rc = lib.afl_sgdm_flat(ptr(w), ptr(g), ptr(buf), c_i64(w.numel()), c_f(lr), c_f(momentum),
+                           c_i(1 if first_step else 0), ptr(gscale), stream_ptr(w))
+    check(lib, rc, "afl_sgdm_flat")
+
+
+def fedavg(rows: torch.Tensor, weights: torch.Tensor, out: Optional[torch.Tensor] = None,
+           bcast: Optional[torch.Tensor] = None, *, member: Optional[torch.Tensor] = None,
+           z: Optional[torch.Tensor] = None, ref: Optional[torch.Tensor] = None, want_mu: bool = False,
+           want_sd: bool = False, want_lie: bool = False, strict_k1: bool = False):
+    """K1 (+K2).  ``rows [C, d_pad]``, ``weights [C]`` (already normalised).  ``bcast [Cb, d_pad]`` receives the
+    result in every row (the START fan-out).  ``member [A, C]`` (0/1 floats) selects each attacker's genuine
+    subset; returns ``(out, mu, sd, lie)`` with ``mu/sd/lie`` of shape ``[A, d_pad]`` or ``None``."""
+    C, d_pad = rows.shape
+    dev = rows.device
+    lib = lib_for(rows)
+    if out is None:
+        out = torch.empty(d_pad, dtype=torch.float32, device=dev)
+    A = 0 if member is None else member.shape[0]
+    mu = torch.empty(A, d_pad, dtype=torch.float32, device=dev) if (A and (want_mu or want_lie)) else None
+    sd = torch.empty(A, d_pad, dtype=torch.float32, device=dev) if (A and (want_sd or want_lie)) else None
+    lie = torch.empty(A, d_pad, dtype=torch.float32, device=dev) if (A and want_lie) else None
+    weights = weights.to(device=dev, dtype=torch.float32).contiguous()
+    if A == 0:
+        rc = lib.afl_fedavg(ptr(rows), ptr(weights), c_i(C), c_i64(d_pad), ptr(out), ptr(bcast),
+                            c_i(0 if bcast is None else bcast.shape[0]), c_i(0), ptr(None), ptr(None), ptr(None),
+                            ptr(None), ptr(None), ptr(None), ptr(None), c_i(0), stream_ptr(rows))
+        check(lib, rc, "afl_fedavg")
+        return out, None, None, None
+    member = member.to(device=dev, dtype=torch.float32).contiguous()
+    kcount = member.sum(1).contiguous()
+    z = (torch.zeros(A, device=dev) if z is None else z.to(device=dev, dtype=torch.float32)).contiguous()
+    for a0 in range(0, A, MAX_ATT):
+        a1 = min(A, a0 + MAX_ATT)
+        first = a0 == 0
+        rc = lib.afl_fedavg(ptr(rows), ptr(weights), c_i(C), c_i64(d_pad), ptr(out) if first else ptr(None),
+                            ptr(bcast) if first else ptr(None), c_i(0 if (bcast is None or not first) else bcast.shape[0]),
+                            c_i(a1 - a0), ptr(ref), ptr(member[a0:a1]), ptr(kcount[a0:a1]), ptr(z[a0:a1]),
+                            ptr(mu[a0:a1]) if mu is not None else ptr(None),
+                            ptr(sd[a0:a1]) if sd is not None else ptr(None),
+                            ptr(lie[a0:a1]) if lie is not None else ptr(None), c_i(1 if strict_k1 else 0),
+                            stream_ptr(rows))
+        check(lib, rc, "afl_fedavg")
+    return out, mu, sd, lie
+
+
+def gamma_search(G: torch.Tensor, k: int, rule: str, exclude_first: bool = True, paper: bool = False) -> torch.Tensor:
+    """K4 bisection on a ``(k+2)x(k+2)`` fp32 Gram matrix; returns device tensor ``[gamma, gamma_succ, thr, probes]``."""
+    lib = lib_for(G)
+    G = G.to(torch.float32).contiguous()
+    out = torch.zeros(4, dtype=torch.float32, device=G.device)
+    rc = lib.afl_gamma_search_dev(ptr(G), c_i(k), c_i(0 if rule == "max" else 1), c_i(1 if exclude_first else 0),
+                                  c_i(1 if paper else 0), ptr(out), stream_ptr(G))
+    check(lib, rc, "afl_gamma_search_dev")
+    return out
+
+
+def craft_axpy(mu: torch.Tensor, p: Optional[torch.Tensor], gamma: torch.Tensor, sign_mode: bool = False,
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    lib = lib_for(mu)
+    out = torch.empty_like(mu) if out is None else out
+    rc = lib.afl_craft_axpy(ptr(out), ptr(mu), ptr(p), ptr(gamma), c_i(1 if sign_mode else 0), c_i64(mu.numel()),
+                            stream_ptr(mu))
+    check(lib, rc, "afl_craft_axpy")
+    return out
+
+
+def craft_random(w: torch.Tensor, valid: Optional[torch.Tensor], perturbation: float, seed: int, stream_id: int,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    lib = lib_for(w)
+    out = torch.empty_like(w) if out is None else out
+    rc = lib.afl_craft_random(ptr(out), ptr(w), ptr(valid), c_f(perturbation), c_u64(seed & (2 ** 64 - 1)),
+                              c_u32(stream_id), c_i64(w.numel()), stream_ptr(w))
+    check(lib, rc, "afl_craft_random")
+    return out
+
+
+def coord_select(rows: torch.Tensor, mode: str, trim: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K6: ``mode='median'`` (lower median) or ``'trimmed'`` (drop ``trim`` per side, mean of the rest)."""
+    C, d_pad = rows.shape
+    lib = lib_for(rows)
+    out = torch.empty(d_pad, dtype=torch.float32, device=rows.device) if out is None else out
+    rc = lib.afl_coord_select(ptr(rows), c_i(C), c_i64(d_pad), ptr(out), c_i(0 if mode == "median" else 1),
+                              c_i(trim), stream_ptr(rows))
+    check(lib, rc, "afl_coord_select")
+    return out
+
+
+# ---------------------------------------------------------------------------------------- hyper-network
+class NativeHyper:
+    """Device-side state of a ``FusedHyperNet`` in the layout the K5 kernels expect.
+
+    ``small = params | m | v`` where ``params = emb | w0 b0 | w1 b1 | w2 b2``; the head lives in
+    ``head_w [D_pad, H]``, ``head_b [D_pad]`` with Adam moments ``mw, vw, mb, vb``.
+    """
+
+    def __init__(self, fused):
+        from ..models.hyper import FusedHyperNet
+        assert isinstance(fused, FusedHyperNet) and fused.n_hidden == 2
+        self.fused = fused
+        dev = fused.device
+        self.n_nodes, self.E, self.H = fused.n_nodes, fused.E, fused.H
+        self.tot = self.n_nodes * self.E + self.H * self.E + self.H + 2 * (self.H * self.H + self.H)
+        self.small = torch.zeros(3 * self.tot, dtype=torch.float32, device=dev)
+        self.head_w, self.head_b = fused.head_w, fused.head_b
+        self.mw, self.vw = fused.m["head_w"], fused.v["head_w"]
+        self.mb, self.vb = fused.m["head_b"], fused.v["head_b"]
+        self.delta = torch.zeros(fused.layout.padded, dtype=torch.float32, device=dev)
+        self.acts = torch.zeros(self.E + 5 * self.H, dtype=torch.float32, device=dev)
+        self.red = torch.zeros(self.H + 3, dtype=torch.float32, device=dev)
+        self.f1 = torch.zeros(self.H, dtype=torch.float32, device=dev)
+        self._client_idx = torch.arange(self.n_nodes, dtype=torch.int32, device=dev)
+        self.pack()
+
+    def _names(self) -> List[str]:
+        return ["emb", "mlp_w0", "mlp_b0", "mlp_w1", "mlp_b1", "mlp_w2", "mlp_b2"]
+
+    def pack(self) -> None:
+        """fused tensors -> ``small``."""
+        for base, src in ((0, self.fused.trainable()), (self.tot, self.fused.m), (2 * self.tot, self.fused.v)):
+            o = base
+            for n in self._names():
+                t = src[n].reshape(-1)
+                self.small[o:o + t.numel()].copy_(t)
+                o += t.numel()
+
+    def unpack(self) -> None:
+        """``small`` -> fused tensors (so export / torch paths see the native updates)."""
+        for base, dst in ((0, self.fused.trainable()), (self.tot, self.fused.m), (2 * self.tot, self.fused.v)):
+            o = base
+            for n in self._names():
+                t = dst[n]
+                t.copy_(self.small[o:o + t.numel()].view_as(t))
+                o += t.numel()
+
+    def emit(self, clients: Sequence[int], out: Optional[torch.Tensor] = None, chunk: int = 64) -> torch.Tensor:
+        """K5a: rows ``theta[j] = h(clients[j])``; ``out [n, D_pad]`` may be a slice of the client arena."""
+        dev = self.small.device
+        lib = lib_for(self.small)
+        d_pad = self.fused.layout.padded
+        n = len(clients)
+        out = torch.empty(n, d_pad, dtype=torch.float32, device=dev) if out is None else out
+        cl = torch.as_tensor(list(clients), dtype=torch.int32, device=dev)
+        f = torch.empty(max(n, 1) * self.H, dtype=torch.float32, device=dev)
+        for c0 in range(0, n, chunk):
+            c1 = min(n, c0 + chunk)
+            rc = lib.afl_hyper_emit(ptr(self.head_w), ptr(self.head_b), ptr(self.small), c_i(self.n_nodes), c_i(self.E),
+                                    c_i(self.H), ptr(cl[c0:c1]), c_i(c1 - c0), ptr(f), ptr(self.acts),
+                                    ptr(out[c0:c1]), c_i64(out.stride(0)), c_i64(d_pad), stream_ptr(self.small))
+            check(lib, rc, "afl_hyper_emit")
+        return out
+
+    def step(self, client: int, theta_client: torch.Tensor, lr: float, clip: float) -> None:
+        """K5b: one sequential pFedHN step (no host sync; the clip coefficient stays on the device)."""
+        lib = lib_for(self.small)
+        self.fused.step += 1
+        rc = lib.afl_hyper_step(ptr(self.head_w), ptr(self.head_b), ptr(self.mw), ptr(self.vw), ptr(self.mb),
+                                ptr(self.vb), ptr(self.small), c_i(self.n_nodes), c_i(self.E), c_i(self.H),
+                                c_i(int(client)), ptr(self._client_idx[int(client):int(client) + 1]), ptr(theta_client),
+                                ptr(self.delta), ptr(self.f1), ptr(self.acts), ptr(self.red),
+                                c_i64(self.fused.layout.padded), c_f(lr), c_f(BETAS[0]), c_f(BETAS[1]), c_f(EPS),
+                                c_i(self.fused.step), c_f(clip), stream_ptr(self.small))
+        check(lib, rc, "afl_hyper_step")
+
+    def embedding(self, i: int) -> torch.Tensor:
+        return self.small[i * self.E:(i + 1) * self.E].view(1, self.E).clone()

@@ -1,0 +1,399 @@
+// CUDA kernels + C-ABI wrappers for the flat-vector ops (sm_100a).  The numerical cores live in
+// flat_core.h (shared with the CPU twin); this file adds grids, shared-memory staging and the
+// bandwidth-oriented hyper-network kernels.
+#include <cuda_runtime.h>
+#include <stdio.h>
+
+#include "../include/attackfl_b200.h"
+#include "flat_core.h"
+#include "runtime.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__global__ void __launch_bounds__(kThreads) adam_kernel(float* w, const float* g, float* m, float* v, int64_t n,
+                                                        float lr, float b1, float b2, float eps, float bc1, float bc2,
+                                                        const float* gscale_ptr) {
+  const float gs = gscale_ptr ? gscale_ptr[0] : 1.f;
+  afl_adam_core(w, g, m, v, 0, n, lr, b1, b2, eps, bc1, bc2, gs, blockIdx.x * kThreads + threadIdx.x,
+                gridDim.x * kThreads);
+}
+
+__global__ void __launch_bounds__(kThreads) sgdm_kernel(float* w, const float* g, float* buf, int64_t n, float lr,
+                                                        float momentum, int first, const float* gscale_ptr) {
+  const float gs = gscale_ptr ? gscale_ptr[0] : 1.f;
+  afl_sgdm_core(w, g, buf, 0, n, lr, momentum, first, gs, blockIdx.x * kThreads + threadIdx.x, gridDim.x * kThreads);
+}
+
+template <int A>
+__global__ void __launch_bounds__(kThreads) fedavg_kernel(AflFedavgArgs a) {
+  extern __shared__ float sm[];
+  float* wsm = sm;
+  float* msm = sm + a.C;
+  for (int i = threadIdx.x; i < a.C; i += kThreads) wsm[i] = a.weights[i];
+  for (int i = threadIdx.x; i < A * a.C; i += kThreads) msm[i] = a.member[i];
+  __syncthreads();
+  afl_fedavg_core<A>(a, wsm, msm, 0, a.d_pad, blockIdx.x * kThreads + threadIdx.x, gridDim.x * kThreads);
+}
+
+__global__ void gamma_kernel(const float* G, int k, int rule, int exclude_first, int paper, float* out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) afl_gamma_search(G, k, rule, exclude_first, paper, out);
+}
+
+__global__ void __launch_bounds__(kThreads) craft_axpy_kernel(float* out, const float* mu, const float* p,
+                                                              const float* gamma, float sign_mode, int64_t n) {
+  afl_craft_axpy_core(out, mu, p, gamma, sign_mode, 0, n, blockIdx.x * kThreads + threadIdx.x, gridDim.x * kThreads);
+}
+
+__global__ void __launch_bounds__(kThreads) craft_random_kernel(float* out, const float* w, const float* valid,
+                                                                float pert, uint32_t s0, uint32_t s1, uint32_t stream,
+                                                                int64_t n) {
+  afl_craft_random_core(out, w, valid, pert, s0, s1, stream, 0, n, blockIdx.x * kThreads + threadIdx.x,
+                        gridDim.x * kThreads);
+}
+
+__global__ void __launch_bounds__(128) select_kernel(const float* rows, int C, int64_t d_pad, float* out, int mode,
+                                                     int trim) {
+  afl_select_core(rows, C, d_pad, out, mode, trim, 0, d_pad, blockIdx.x * 128 + threadIdx.x, gridDim.x * 128);
+}
+
+// ------------------------------------------------------------------------------------------ hyper kernels
+// Tile of TR rows of W_h staged in shared memory with a padded row (H+1) so both access patterns
+// (lane = row, lane = column) are bank-conflict free.  W_h is read from HBM exactly once per pass.
+constexpr int kTR = 64;
+
+__global__ void __launch_bounds__(kThreads) hyper_emit_kernel(const float* __restrict__ head_w,
+                                                              const float* __restrict__ head_b,
+                                                              const float* __restrict__ f, int C, int H,
+                                                              float* theta, int64_t theta_ld, int64_t d_pad) {
+  extern __shared__ float sm[];
+  float* fs = sm;                       // [C][H]
+  float* tile = sm + C * H;             // [kTR][H+1]
+  for (int i = threadIdx.x; i < C * H; i += kThreads) fs[i] = f[i];
+  const int64_t n_tiles = (d_pad + kTR - 1) / kTR;
+  for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
+    const int64_t d0 = tIdx * kTR;
+    const int rows = (int)AFL_MIN((int64_t)kTR, d_pad - d0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < rows * H; i += kThreads) {
+      const int r = i / H, h = i - r * H;
+      tile[r * (H + 1) + h] = head_w[d0 * H + i];
+    }
+    __syncthreads();
+    for (int it = threadIdx.x; it < kTR * C; it += kThreads) {
+      const int r = it % kTR, c = it / kTR;      // lanes walk rows => coalesced theta stores
+      if (r < rows) {
+        const float* tr = tile + r * (H + 1);
+        const float* fr = fs + c * H;
+        float acc = head_b[d0 + r];
+        for (int h = 0; h < H; ++h) acc += tr[h] * fr[h];
+        theta[(int64_t)c * theta_ld + d0 + r] = acc;
+      }
+    }
+  }
+}
+
+// pass 1: delta, |delta|^2 and W_h^T delta.  red: [1+H] floats, zeroed by the caller.
+__global__ void __launch_bounds__(kThreads) hyper_delta_kernel(const float* __restrict__ head_w,
+                                                               const float* __restrict__ head_b,
+                                                               const float* __restrict__ f, int H,
+                                                               const float* __restrict__ theta_client, float* delta,
+                                                               int64_t d_pad, float* red) {
+  extern __shared__ float sm[];
+  float* fs = sm;                       // [H]
+  float* dl = sm + H;                   // [kTR]
+  float* tile = dl + kTR;               // [kTR][H+1]
+  for (int i = threadIdx.x; i < H; i += kThreads) fs[i] = f[i];
+  float acc_h = 0.f;                    // thread h < H accumulates (W^T delta)[h]
+  float acc_sq = 0.f;                   // thread r < kTR accumulates delta^2
+  const int64_t n_tiles = (d_pad + kTR - 1) / kTR;
+  for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
+    const int64_t d0 = tIdx * kTR;
+    const int rows = (int)AFL_MIN((int64_t)kTR, d_pad - d0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < rows * H; i += kThreads) {
+      const int r = i / H, h = i - r * H;
+      tile[r * (H + 1) + h] = head_w[d0 * H + i];
+    }
+    __syncthreads();
+    if (threadIdx.x < rows) {
+      const int r = threadIdx.x;
+      const float* tr = tile + r * (H + 1);
+      float a = head_b[d0 + r];
+      for (int h = 0; h < H; ++h) a += tr[h] * fs[h];
+      const float d = a - theta_client[d0 + r];
+      delta[d0 + r] = d;
+      dl[r] = d;
+      acc_sq += d * d;
+    }
+    __syncthreads();
+    if (threadIdx.x < H) {
+      const int h = threadIdx.x;
+      float a = 0.f;
+      for (int r = 0; r < rows; ++r) a += tile[r * (H + 1) + h] * dl[r];
+      acc_h += a;
+    }
+  }
+  if (threadIdx.x < H) atomicAdd(red + 1 + threadIdx.x, acc_h);
+  // block-reduce acc_sq through shared memory
+  __syncthreads();
+  if (threadIdx.x < kTR) dl[threadIdx.x] = acc_sq;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int r = 0; r < kTR; ++r) s += dl[r];
+    atomicAdd(red, s);
+  }
+}
+
+// Small replicated part of the step: MLP backward, embedding gradient, clip coefficient and Adam on
+// the MLP / embedding table.  One block.  Layout of `small` (all fp32):
+//   emb [n_nodes*E] | w0 [H*E] b0 [H] | w1 [H*H] b1 [H] | w2 [H*H] b2 [H]      (params, then m, then v copies)
+// acts (written by hyper_features_kernel): e[E] z0[H] a0[H] z1[H] a1[H] f[H]
+struct HyperSmall {
+  float* params; float* m; float* v; int n_nodes, E, H;
+  float* acts; float* red; float* coef_out; float* norm_out;
+  int client; float lr, b1, b2, eps, bc1, bc2, clip;
+};
+
+__device__ inline int hs_off_w(const HyperSmall& s, int layer) {
+  int o = s.n_nodes * s.E;
+  if (layer == 0) return o;
+  o += s.H * s.E + s.H;
+  if (layer == 1) return o;
+  return o + s.H * s.H + s.H;
+}
+__device__ inline int hs_total(const HyperSmall& s) { return hs_off_w(s, 2) + s.H * s.H + s.H; }
+
+__global__ void __launch_bounds__(kThreads) hyper_features_kernel(HyperSmall s, const int* clients, int n, float* f_out) {
+  // f_out: [n][H]; acts saved only when n == 1
+  extern __shared__ float sm[];
+  float* x = sm; float* y = sm + s.H;
+  const int E = s.E, H = s.H;
+  for (int q = 0; q < n; ++q) {
+    const int c = clients[q];
+    __syncthreads();
+    for (int i = threadIdx.x; i < E; i += kThreads) { x[i] = s.params[c * E + i]; if (n == 1) s.acts[i] = x[i]; }
+    __syncthreads();
+    for (int layer = 0; layer < 3; ++layer) {
+      const int in = layer == 0 ? E : H;
+      const float* W = s.params + hs_off_w(s, layer);
+      const float* B = W + H * in;
+      for (int j = threadIdx.x; j < H; j += kThreads) {
+        float a = B[j];
+        for (int i = 0; i < in; ++i) a += W[j * in + i] * x[i];
+        y[j] = a;
+      }
+      __syncthreads();
+      for (int j = threadIdx.x; j < H; j += kThreads) {
+        const float z = y[j];
+        if (layer < 2) {
+          const float r = z > 0.f ? z : 0.f;
+          if (n == 1) { s.acts[E + 2 * layer * H + j] = z; s.acts[E + (2 * layer + 1) * H + j] = r; }
+          x[j] = r;
+        } else {
+          if (n == 1) s.acts[E + 4 * H + j] = z;
+          f_out[q * H + j] = z;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) hyper_small_step_kernel(HyperSmall s) {
+  extern __shared__ float sm[];
+  const int E = s.E, H = s.H;
+  float* g = sm;             // current upstream gradient [H]
+  float* gn = sm + H;        // next [H]
+  float* grads = sm + 2 * H; // full small-gradient vector, same layout as params
+  __shared__ float s_norm2, s_coef;
+  const int total = hs_total(s);
+  for (int i = threadIdx.x; i < total; i += kThreads) grads[i] = 0.f;
+  for (int i = threadIdx.x; i < H; i += kThreads) g[i] = s.red[1 + i];     // dL/df = W_h^T delta
+  __syncthreads();
+  const float* e = s.acts;
+  for (int layer = 2; layer >= 0; --layer) {
+    const int in = layer == 0 ? E : H;
+    const float* xin = layer == 0 ? e : s.acts + E + (2 * (layer - 1) + 1) * H;
+    const int ow = hs_off_w(s, layer);
+    for (int i = threadIdx.x; i < H * in; i += kThreads) grads[ow + i] = g[i / in] * xin[i % in];
+    for (int j = threadIdx.x; j < H; j += kThreads) grads[ow + H * in + j] = g[j];
+    const float* W = s.params + ow;
+    for (int i = threadIdx.x; i < in; i += kThreads) {
+      float a = 0.f;
+      for (int j = 0; j < H; ++j) a += W[j * in + i] * g[j];
+      if (layer > 0) { const float z = s.acts[E + 2 * (layer - 1) * H + i]; a = z > 0.f ? a : 0.f; }
+      gn[i] = a;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < in; i += kThreads) g[i] = gn[i];
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < E; i += kThreads) grads[s.client * E + i] = g[i];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // |grad|^2 = |delta|^2 (|f|^2 + 1) + |grad small|^2   (rank-1 head gradient)
+    const float* f = s.acts + E + 4 * H;
+    double f2 = 0.0, small2 = 0.0;
+    for (int i = 0; i < H; ++i) f2 += (double)f[i] * f[i];
+    for (int i = 0; i < total; ++i) small2 += (double)grads[i] * grads[i];
+    const double n2 = (double)s.red[0] * (f2 + 1.0) + small2;
+    const float norm = (float)sqrt(n2);
+    float coef = 1.f;
+    if (s.clip > 0.f) { coef = s.clip / (norm + 1e-6f); coef = coef < 1.f ? coef : 1.f; }
+    s_norm2 = norm; s_coef = coef;
+    s.coef_out[0] = coef; s.norm_out[0] = norm;
+  }
+  __syncthreads();
+  const float coef = s_coef;
+  const float step = s.lr / s.bc1, isq = 1.0f / sqrtf(s.bc2);
+  for (int i = threadIdx.x; i < total; i += kThreads) {
+    const float gg = grads[i] * coef;
+    const float mi = s.b1 * s.m[i] + (1.f - s.b1) * gg;
+    const float vi = s.b2 * s.v[i] + (1.f - s.b2) * gg * gg;
+    s.m[i] = mi; s.v[i] = vi;
+    s.params[i] -= step * (mi / (sqrtf(vi) * isq + s.eps));
+  }
+  (void)s_norm2;
+}
+
+__global__ void __launch_bounds__(kThreads) hyper_adam_kernel(float* head_w, float* head_b, float* mw, float* vw,
+                                                              float* mb, float* vb, const float* delta, const float* f,
+                                                              int H, const float* coef, float lr, float b1, float b2,
+                                                              float eps, float bc1, float bc2, int64_t d_pad) {
+  afl_hyper_adam_core(head_w, head_b, mw, vw, mb, vb, delta, f, H, coef, lr, b1, b2, eps, bc1, bc2, 0, d_pad,
+                      blockIdx.x * kThreads + threadIdx.x, gridDim.x * kThreads);
+}
+
+inline int grid_for(int64_t work_items, int threads, int max_blocks_per_sm = 8) {
+  int64_t b = (work_items + threads - 1) / threads;
+  const int64_t cap = (int64_t)afl_rt::num_sms() * max_blocks_per_sm;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace
+
+extern "C" {
+
+int afl_adam_flat(float* w, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                  int step, const float* gscale, void* stream) {
+  AFL_CHECK_ARG(n % 4 == 0, "afl_adam_flat: n must be a multiple of 4");
+  const float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
+  adam_kernel<<<grid_for(n / 4, kThreads), kThreads, 0, (cudaStream_t)stream>>>(w, g, m, v, n, lr, b1, b2, eps, bc1,
+                                                                                 bc2, gscale);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_adam_flat");
+}
+
+int afl_sgdm_flat(float* w, const float* g, float* buf, int64_t n, float lr, float momentum, int first_step,
+                  const float* gscale, void* stream) {
+  AFL_CHECK_ARG(n % 4 == 0, "afl_sgdm_flat: n must be a multiple of 4");
+  sgdm_kernel<<<grid_for(n / 4, kThreads), kThreads, 0, (cudaStream_t)stream>>>(w, g, buf, n, lr, momentum,
+                                                                                 first_step, gscale);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_sgdm_flat");
+}
+
+int afl_fedavg(const float* rows, const float* weights, int C, int64_t d_pad, float* out, float* bcast, int Cb,
+               int A, const float* ref, const float* member, const float* kcount, const float* z, float* mu,
+               float* sd, float* lie, int strict_k1, void* stream) {
+  AFL_CHECK_ARG(d_pad % 4 == 0, "afl_fedavg: d_pad must be a multiple of 4");
+  AFL_CHECK_ARG(A >= 0 && A <= AFL_MAX_ATT, "afl_fedavg: at most 4 moment sets per call");
+  AflFedavgArgs a{rows, weights, C, d_pad, out, bcast, Cb, A, ref, member, kcount, z, mu, sd, lie, strict_k1};
+  const size_t smem = sizeof(float) * (size_t)(C + A * C);
+  const int grid = grid_for(d_pad / 4, kThreads, 4);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (A) {
+    case 0: fedavg_kernel<0><<<grid, kThreads, smem, st>>>(a); break;
+    case 1: fedavg_kernel<1><<<grid, kThreads, smem, st>>>(a); break;
+    case 2: fedavg_kernel<2><<<grid, kThreads, smem, st>>>(a); break;
+    case 3: fedavg_kernel<3><<<grid, kThreads, smem, st>>>(a); break;
+    default: fedavg_kernel<4><<<grid, kThreads, smem, st>>>(a); break;
+  }
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_fedavg");
+}
+
+int afl_gamma_search_dev(const float* G, int k, int rule, int exclude_first, int paper, float* out4, void* stream) {
+  gamma_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(G, k, rule, exclude_first, paper, out4);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_gamma_search_dev");
+}
+
+int afl_craft_axpy(float* out, const float* mu, const float* p, const float* gamma_dev, int sign_mode, int64_t n,
+                   void* stream) {
+  AFL_CHECK_ARG(n % 4 == 0, "afl_craft_axpy: n must be a multiple of 4");
+  craft_axpy_kernel<<<grid_for(n / 4, kThreads), kThreads, 0, (cudaStream_t)stream>>>(out, mu, p, gamma_dev,
+                                                                                       (float)sign_mode, n);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_craft_axpy");
+}
+
+int afl_craft_random(float* out, const float* w, const float* valid, float perturbation, uint64_t seed,
+                     uint32_t stream_id, int64_t n, void* stream) {
+  craft_random_kernel<<<grid_for(n, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+      out, w, valid, perturbation, (uint32_t)seed, (uint32_t)(seed >> 32), stream_id, n);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_craft_random");
+}
+
+int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mode, int trim, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && C <= AFL_SEL_MAX, "afl_coord_select: 1 <= C <= 256");
+  AFL_CHECK_ARG(mode == 0 || 2 * trim < C, "afl_coord_select: 2*trim must be < C");
+  select_kernel<<<grid_for(d_pad, 128, 16), 128, 0, (cudaStream_t)stream>>>(rows, C, d_pad, out, mode, trim);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_coord_select");
+}
+
+// ---- hyper-network (K5a / K5b).  `small`: params | m | v, each hs_total floats (see HyperSmall).
+static size_t hyper_small_total(int n_nodes, int E, int H) { return (size_t)n_nodes * E + (size_t)H * E + H + 2 * ((size_t)H * H + H); }
+
+int afl_hyper_emit(const float* head_w, const float* head_b, float* small, int n_nodes, int E, int H,
+                   const int* clients_dev, int n, float* f_scratch /* [n*H] */, float* acts /* [E+5H] */,
+                   float* theta, int64_t theta_ld, int64_t d_pad, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t tot = hyper_small_total(n_nodes, E, H);
+  HyperSmall s{small, small + tot, small + 2 * tot, n_nodes, E, H, acts, nullptr, nullptr, nullptr, 0,
+               0, 0, 0, 0, 1, 1, 0};
+  hyper_features_kernel<<<1, kThreads, sizeof(float) * 2 * (size_t)AFL_MAX(H, E), st>>>(s, clients_dev, n, f_scratch);
+  afl_rt::count_launch();
+  const size_t smem = sizeof(float) * ((size_t)n * H + (size_t)kTR * (H + 1));
+  AFL_CHECK_ARG(smem <= 200 * 1024, "afl_hyper_emit: too many clients per call for shared memory (chunk them)");
+  AFL_CUDA(cudaFuncSetAttribute(hyper_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = grid_for((d_pad + kTR - 1) / kTR, 1, 2);
+  hyper_emit_kernel<<<grid, kThreads, smem, st>>>(head_w, head_b, f_scratch, n, H, theta, theta_ld, d_pad);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_hyper_emit");
+}
+
+int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb, float* vb, float* small,
+                   int n_nodes, int E, int H, int client, const int* client_dev, const float* theta_client,
+                   float* delta /* [d_pad] */, float* f_scratch /* [H] */, float* acts /* [E+5H] */,
+                   float* red /* [1+H+2]: |delta|^2, W^T delta, coef, norm */, int64_t d_pad, float lr, float b1,
+                   float b2, float eps, int step, float clip, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t tot = hyper_small_total(n_nodes, E, H);
+  const float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
+  HyperSmall s{small, small + tot, small + 2 * tot, n_nodes, E, H, acts, red, red + 1 + H, red + 2 + H, client,
+               lr, b1, b2, eps, bc1, bc2, clip};
+  AFL_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * (size_t)(H + 3), st));
+  hyper_features_kernel<<<1, kThreads, sizeof(float) * 2 * (size_t)AFL_MAX(H, E), st>>>(s, client_dev, 1, f_scratch);
+  const size_t smem1 = sizeof(float) * ((size_t)H + kTR + (size_t)kTR * (H + 1));
+  const int grid = grid_for((d_pad + kTR - 1) / kTR, 1, 2);
+  hyper_delta_kernel<<<grid, kThreads, smem1, st>>>(head_w, head_b, f_scratch, H, theta_client, delta, d_pad, red);
+  const size_t smem2 = sizeof(float) * (2 * (size_t)H + tot);
+  AFL_CHECK_ARG(smem2 <= 200 * 1024, "afl_hyper_step: embedding table too large for the single-block small step");
+  AFL_CUDA(cudaFuncSetAttribute(hyper_small_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  hyper_small_step_kernel<<<1, kThreads, smem2, st>>>(s);
+  hyper_adam_kernel<<<grid_for(d_pad * H, kThreads, 8), kThreads, 0, st>>>(head_w, head_b, mw, vw, mb, vb, delta,
+                                                                             f_scratch, H, red + 1 + H, lr, b1, b2,
+                                                                             eps, bc1, bc2, d_pad);
+  afl_rt::count_launch(4);
+  return afl_rt::check_last("afl_hyper_step");
+}
+
+}  // extern "C"

@@ -1,0 +1,653 @@
+// Op-program interpreter for multi-client local training (forward + backward + fused optimiser).
+//
+// What it replaces: the reference's per-client Python loop `train_ICU` (/root/reference/client.py:75-111):
+// ~525 optimiser steps per client per round, each ~150 ATen/cuDNN/cuBLAS launches, 3 H2D copies
+// and 2 host syncs.  Here a whole round of a client is ONE persistent kernel: a model is a short
+// list of ops (built in attackfl_b200/models/programs.py) executed by G thread blocks per client,
+// each owning tiles of S samples whose activations live in shared memory; parameters, Adam
+// state and per-block partial gradients are rows of the flat fp32 arena (L2-resident).
+//
+// Ops (forward semantics; backward is derived op by op, run in reverse order):
+//   LOAD     gather S records of the device-resident data set by index (vitals | labs | label)
+//   LINEAR   out = drop_p(act(in0 . W^T + b))         act in {none, relu, gelu}   (T5, T3/T4 pieces)
+//   LN       out = LayerNorm(in0 + drop_p(in1)) * g + b   (residual + dropout fused)   (T3/T4)
+//   GRU      T=1 bidirectional-GRU cell on precomputed W_ih x + b_ih      (T1)
+//   CONV     Conv1d(k=3, pad=1) + ReLU on [C][L] rows                                   (T2)
+//   POOL     AdaptiveAvgPool1d(4) (+ dropout)                                           (T2)
+//   DROPOUT  grouped Bernoulli dropout (group 16 = attention-weight dropout at T=1)     (T6)
+//   BCE      sigmoid + BCELoss, emits dL/dlogit, loss sum and a NaN flag                (T7)
+// The optimiser phase (Adam re-created per round / SGD-momentum, T8/T9) reduces the G partial
+// gradient rows and updates the owned 1/G slice of the parameter row.
+//
+// All functions are (tid, nthreads)-parametrised and contain no warp intrinsics, so the same
+// source is the CPU twin (tid=0, nthreads=1) used by the non-GPU tests.
+#pragma once
+#include "common.h"
+
+enum AflOpKind { AFL_OP_LOAD = 1, AFL_OP_LINEAR = 2, AFL_OP_LN = 3, AFL_OP_GRU = 4, AFL_OP_CONV = 5,
+                 AFL_OP_POOL = 6, AFL_OP_DROPOUT = 7, AFL_OP_BCE = 8 };
+enum AflAct { AFL_ACT_NONE = 0, AFL_ACT_RELU = 1, AFL_ACT_GELU = 2 };
+enum AflFlags { AFL_F_ACC0 = 1, AFL_F_ACC1 = 2, AFL_F_NEED_GIN0 = 4, AFL_F_MASK_INPUT = 8 };
+
+#define AFL_OP_WORDS 32
+#define AFL_LN_PARTS 8
+#define AFL_LN_EPS 1e-5f
+
+// One instruction; 32 x int32 so Python can pack programs as a plain int32 array.
+struct AflOp {
+  int32_t kind, act;
+  int32_t in0, in0_ld;      // pool offsets are in floats; ld = row (sample) stride
+  int32_t in1, in1_ld;
+  int32_t out, out_ld;
+  int32_t aux, aux2;        // saved tensors for backward (pre-activation / xhat / partials+rstd)
+  int32_t w, b, w2;         // parameter offsets inside the flat row (-1 = none)
+  int32_t N, K, L;          // out width, in width, conv length / dropout group / pool length
+  float p;                  // dropout probability
+  int32_t rng;              // per-op RNG stream id
+  int32_t g_out, g_in0, g_in1;   // gradient buffers (pool offsets)
+  int32_t flags;
+  int32_t in_cs, out_cs;    // conv/pool channel strides
+  int32_t pad[8];
+};
+
+struct AflTile {
+  float* pool;              // per-block activation pool (shared memory on the GPU)
+  const float* w;           // this client's parameter row
+  float* gw;                // this block's partial-gradient row
+  const float* data;        // [n_rows, rec] packed records
+  const int32_t* idx;       // this step's sample indices for the tile (may be null => consecutive)
+  float* probs;             // inference output (global), or null
+  float* loss_acc;          // [2]: loss sum, nan count  (per block, in pool tail or global)
+  int64_t row0;             // inference: first record index of this tile
+  int rec;                  // floats per record (24 for ICU)
+  int S;                    // samples per tile
+  int n_valid;              // valid samples in this tile
+  int accumulate;           // partial grads: += instead of =
+  int train;                // 1: dropout active
+  float inv_b;              // 1 / (batch size of this optimiser step)
+  uint32_t seed_lo, seed_hi, client, step;
+  int sample_base;          // index of the tile's first sample inside the step's batch
+};
+
+// ----------------------------------------------------------------------------------------- helpers
+AFL_DEV float afl_act_fwd(int act, float z) {
+  if (act == AFL_ACT_RELU) return z > 0.f ? z : 0.f;
+  if (act == AFL_ACT_GELU) return afl_gelu(z);
+  return z;
+}
+
+AFL_DEV float afl_drop_scale(const AflTile& t, const AflOp& op, int s, uint32_t elem) {
+  // returns 0 (dropped) or 1/(1-p); 1 when dropout is inactive
+  if (!(t.train && op.p > 0.f)) return 1.f;
+  bool keep = afl_keep(t.seed_lo, t.seed_hi, t.client, t.step, (uint32_t)(t.sample_base + s),
+                       (uint32_t)op.rng, elem, op.p);
+  return keep ? 1.f / (1.f - op.p) : 0.f;
+}
+
+AFL_DEV void afl_store(float* dst, float v, int acc) { *dst = acc ? *dst + v : v; }
+
+// ----------------------------------------------------------------------------------------- LOAD
+AFL_DEV void afl_load_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int nv = op.N, nl = op.K;       // vitals / labs widths
+  const int per = nv + nl + 1;
+  for (int it = tid; it < t.S * per; it += nt) {
+    int s = it / per, f = it - s * per;
+    float v = 0.f;
+    if (s < t.n_valid) {
+      int64_t r = t.idx ? (int64_t)t.idx[s] : t.row0 + s;
+      v = t.data[r * t.rec + f];
+      if ((op.flags & AFL_F_MASK_INPUT) && f < nv + nl && v == -2.0f) v = 0.f;
+    }
+    if (f < nv) t.pool[op.out + s * op.out_ld + f] = v;
+    else if (f < nv + nl) t.pool[op.aux + s * op.aux2 + (f - nv)] = v;
+    else t.pool[op.in1 + s] = v;
+  }
+}
+
+// ----------------------------------------------------------------------------------------- LINEAR
+#define AFL_TS 4   // samples per thread in the forward / dX mappings
+
+AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, K = op.K, S = t.S;
+  const int SG = (S + AFL_TS - 1) / AFL_TS;
+  const bool vec = (K & 3) == 0 && (op.in0_ld & 3) == 0 && (op.in0 & 3) == 0 && (op.w & 3) == 0;
+  for (int it = tid; it < N * SG; it += nt) {
+    const int n = it % N, sg = it / N;
+    const int s0 = sg * AFL_TS;
+    const float* wr = t.w + op.w + (int64_t)n * K;
+    const float* x0 = t.pool + op.in0 + s0 * op.in0_ld;
+    float acc[AFL_TS];
+#pragma unroll
+    for (int j = 0; j < AFL_TS; ++j) acc[j] = 0.f;
+    if (vec) {
+      for (int k = 0; k < K; k += 4) {
+        const float4 wv = *reinterpret_cast<const float4*>(wr + k);
+#pragma unroll
+        for (int j = 0; j < AFL_TS; ++j) {
+          if (s0 + j < S) {
+            const float4 xv = *reinterpret_cast<const float4*>(x0 + j * op.in0_ld + k);
+            acc[j] += wv.x * xv.x + wv.y * xv.y + wv.z * xv.z + wv.w * xv.w;
+          }
+        }
+      }
+    } else {
+      for (int k = 0; k < K; ++k) {
+        const float wv = wr[k];
+#pragma unroll
+        for (int j = 0; j < AFL_TS; ++j)
+          if (s0 + j < S) acc[j] += wv * x0[j * op.in0_ld + k];
+      }
+    }
+    const float bias = op.b >= 0 ? t.w[op.b + n] : 0.f;
+#pragma unroll
+    for (int j = 0; j < AFL_TS; ++j) {
+      const int s = s0 + j;
+      if (s >= S) break;
+      const float z = acc[j] + bias;
+      if (op.aux >= 0) t.pool[op.aux + s * N + n] = z;
+      float y = afl_act_fwd(op.act, z);
+      y *= afl_drop_scale(t, op, s, (uint32_t)n);
+      t.pool[op.out + s * op.out_ld + n] = y;
+    }
+  }
+}
+
+// Phase A: turn dL/dout into dL/dz in place (dropout mask, activation derivative).
+AFL_DEV void afl_linear_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S;
+  const bool drop = t.train && op.p > 0.f;
+  if (op.act == AFL_ACT_NONE && !drop) return;
+  for (int it = tid; it < N * S; it += nt) {
+    const int s = it / N, n = it - s * N;
+    float g = t.pool[op.g_out + s * op.out_ld + n];
+    if (drop) g *= afl_drop_scale(t, op, s, (uint32_t)n);
+    if (op.act == AFL_ACT_RELU) {
+      if (!(t.pool[op.out + s * op.out_ld + n] > 0.f)) g = 0.f;
+    } else if (op.act == AFL_ACT_GELU) {
+      g *= afl_gelu_grad(t.pool[op.aux + s * N + n]);
+    }
+    t.pool[op.g_out + s * op.out_ld + n] = g;
+  }
+}
+
+// Phase B: dX, dW, db from dz (three independent item ranges, one flat loop).
+AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, K = op.K, S = t.S;
+  const float* dz = t.pool + op.g_out;        // [S][.], row stride = out_ld (same layout as out)
+  const int ldz = op.out_ld;
+  const float* x = t.pool + op.in0;
+  const int SG = (S + AFL_TS - 1) / AFL_TS;
+  const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
+  const int n_dx = need_dx ? K * SG : 0;
+  const bool vec4 = (N & 3) == 0 && (op.g_out & 3) == 0 && (ldz & 3) == 0;
+  const int NQ = vec4 ? N / 4 : N;
+  const int n_dw = NQ * K;
+  const int n_db = op.b >= 0 ? N : 0;
+  const int total = n_dx + n_dw + n_db;
+  for (int it = tid; it < total; it += nt) {
+    if (it < n_dx) {
+      // dX[s][k] = sum_n dz[s][n] W[n][k]; lanes walk k => coalesced W reads
+      const int k = it % K, sg = it / K, s0 = sg * AFL_TS;
+      const float* wc = t.w + op.w + k;
+      float acc[AFL_TS];
+#pragma unroll
+      for (int j = 0; j < AFL_TS; ++j) acc[j] = 0.f;
+      if (vec4) {
+        for (int n = 0; n < N; n += 4) {
+          const float w0 = wc[(int64_t)n * K], w1 = wc[(int64_t)(n + 1) * K];
+          const float w2 = wc[(int64_t)(n + 2) * K], w3 = wc[(int64_t)(n + 3) * K];
+#pragma unroll
+          for (int j = 0; j < AFL_TS; ++j) {
+            if (s0 + j < S) {
+              const float4 d = *reinterpret_cast<const float4*>(dz + (s0 + j) * ldz + n);
+              acc[j] += d.x * w0 + d.y * w1 + d.z * w2 + d.w * w3;
+            }
+          }
+        }
+      } else {
+        for (int n = 0; n < N; ++n) {
+          const float wv = wc[(int64_t)n * K];
+#pragma unroll
+          for (int j = 0; j < AFL_TS; ++j)
+            if (s0 + j < S) acc[j] += dz[(s0 + j) * ldz + n] * wv;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < AFL_TS; ++j)
+        if (s0 + j < S) afl_store(t.pool + op.g_in0 + (s0 + j) * op.in0_ld + k, acc[j], op.flags & AFL_F_ACC0);
+    } else if (it < n_dx + n_dw) {
+      // dW[n][k] = sum_s dz[s][n] x[s][k]; lanes walk k => conflict-free x reads, coalesced writes
+      const int j2 = it - n_dx;
+      const int k = j2 % K, nq = j2 / K;
+      if (vec4) {
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int s = 0; s < S; ++s) {
+          const float xv = x[s * op.in0_ld + k];
+          const float4 d = *reinterpret_cast<const float4*>(dz + s * ldz + nq * 4);
+          a0 += d.x * xv; a1 += d.y * xv; a2 += d.z * xv; a3 += d.w * xv;
+        }
+        float* g = t.gw + op.w + (int64_t)(nq * 4) * K + k;
+        afl_store(g, a0, t.accumulate);
+        afl_store(g + K, a1, t.accumulate);
+        afl_store(g + 2 * (int64_t)K, a2, t.accumulate);
+        afl_store(g + 3 * (int64_t)K, a3, t.accumulate);
+      } else {
+        float a0 = 0.f;
+        for (int s = 0; s < S; ++s) a0 += dz[s * ldz + nq] * x[s * op.in0_ld + k];
+        afl_store(t.gw + op.w + (int64_t)nq * K + k, a0, t.accumulate);
+      }
+    } else {
+      const int n = it - n_dx - n_dw;
+      float a = 0.f;
+      for (int s = 0; s < S; ++s) a += dz[s * ldz + n];
+      afl_store(t.gw + op.b + n, a, t.accumulate);
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------- LAYERNORM
+// aux  : xhat [S][N];  aux2 : partials [S][2*P] followed by rstd [S]
+AFL_DEV void afl_ln_fwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S, P = AFL_LN_PARTS;
+  const int chunk = (N + P - 1) / P;
+  for (int it = tid; it < S * P; it += nt) {
+    const int s = it / P, part = it - s * P;
+    const int n0 = part * chunk, n1 = AFL_MIN(N, n0 + chunk);
+    float sum = 0.f, sq = 0.f;
+    for (int n = n0; n < n1; ++n) {
+      float x = t.pool[op.in0 + s * op.in0_ld + n];
+      if (op.in1 >= 0) x += t.pool[op.in1 + s * op.in1_ld + n] * afl_drop_scale(t, op, s, (uint32_t)n);
+      t.pool[op.out + s * op.out_ld + n] = x;
+      sum += x; sq += x * x;
+    }
+    t.pool[op.aux2 + s * 2 * P + 2 * part] = sum;
+    t.pool[op.aux2 + s * 2 * P + 2 * part + 1] = sq;
+  }
+}
+
+AFL_DEV void afl_ln_fwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S, P = AFL_LN_PARTS;
+  for (int it = tid; it < S * N; it += nt) {
+    const int s = it / N, n = it - s * N;
+    float sum = 0.f, sq = 0.f;
+#pragma unroll
+    for (int q = 0; q < P; ++q) {
+      sum += t.pool[op.aux2 + s * 2 * P + 2 * q];
+      sq += t.pool[op.aux2 + s * 2 * P + 2 * q + 1];
+    }
+    const float mean = sum / (float)N;
+    float var = sq / (float)N - mean * mean;
+    var = var > 0.f ? var : 0.f;
+    const float rstd = 1.0f / sqrtf(var + AFL_LN_EPS);
+    const float xh = (t.pool[op.out + s * op.out_ld + n] - mean) * rstd;
+    t.pool[op.aux + s * N + n] = xh;
+    t.pool[op.out + s * op.out_ld + n] = xh * t.w[op.w + n] + t.w[op.b + n];
+    if (n == 0) t.pool[op.aux2 + S * 2 * P + s] = rstd;
+  }
+}
+
+// backward phase A: per-row partial sums of dxhat and dxhat*xhat, plus dgamma / dbeta
+AFL_DEV void afl_ln_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S, P = AFL_LN_PARTS;
+  const int chunk = (N + P - 1) / P;
+  const int n_part = S * P;
+  for (int it = tid; it < n_part + N; it += nt) {
+    if (it < n_part) {
+      const int s = it / P, part = it - s * P;
+      const int n0 = part * chunk, n1 = AFL_MIN(N, n0 + chunk);
+      float a = 0.f, b = 0.f;
+      for (int n = n0; n < n1; ++n) {
+        const float dxh = t.pool[op.g_out + s * op.out_ld + n] * t.w[op.w + n];
+        a += dxh; b += dxh * t.pool[op.aux + s * N + n];
+      }
+      t.pool[op.aux2 + s * 2 * P + 2 * part] = a;
+      t.pool[op.aux2 + s * 2 * P + 2 * part + 1] = b;
+    } else {
+      const int n = it - n_part;
+      float dg = 0.f, db = 0.f;
+      for (int s = 0; s < S; ++s) {
+        const float g = t.pool[op.g_out + s * op.out_ld + n];
+        dg += g * t.pool[op.aux + s * N + n]; db += g;
+      }
+      afl_store(t.gw + op.w + n, dg, t.accumulate);
+      afl_store(t.gw + op.b + n, db, t.accumulate);
+    }
+  }
+}
+
+AFL_DEV void afl_ln_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S, P = AFL_LN_PARTS;
+  for (int it = tid; it < S * N; it += nt) {
+    const int s = it / N, n = it - s * N;
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int q = 0; q < P; ++q) {
+      a += t.pool[op.aux2 + s * 2 * P + 2 * q];
+      b += t.pool[op.aux2 + s * 2 * P + 2 * q + 1];
+    }
+    const float rstd = t.pool[op.aux2 + S * 2 * P + s];
+    const float dxh = t.pool[op.g_out + s * op.out_ld + n] * t.w[op.w + n];
+    const float dx = rstd * (dxh - a / (float)N - t.pool[op.aux + s * N + n] * (b / (float)N));
+    if (op.flags & AFL_F_NEED_GIN0) afl_store(t.pool + op.g_in0 + s * op.in0_ld + n, dx, op.flags & AFL_F_ACC0);
+    if (op.in1 >= 0)
+      afl_store(t.pool + op.g_in1 + s * op.in1_ld + n, dx * afl_drop_scale(t, op, s, (uint32_t)n), op.flags & AFL_F_ACC1);
+  }
+}
+
+// ----------------------------------------------------------------------------------------- GRU (T=1, h0=0)
+// in0: [S][3H] = W_ih x + b_ih (gate order r,z,n); w2: b_hh [3H]; out: [S][H] at column offset (ld = out_ld).
+AFL_DEV void afl_gru_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int H = op.N, S = t.S;
+  const float* bhh = t.w + op.w2;
+  for (int it = tid; it < S * H; it += nt) {
+    const int s = it / H, j = it - s * H;
+    float* g = t.pool + op.in0 + s * op.in0_ld;
+    const float r = afl_sigmoid(g[j] + bhh[j]);
+    const float z = afl_sigmoid(g[H + j] + bhh[H + j]);
+    const float n = tanhf(g[2 * H + j] + r * bhh[2 * H + j]);
+    g[j] = r; g[H + j] = z; g[2 * H + j] = n;
+    t.pool[op.out + s * op.out_ld + j] = (1.f - z) * n;
+  }
+}
+
+AFL_DEV void afl_gru_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int H = op.N, S = t.S;
+  const float* bhh = t.w + op.w2;
+  for (int it = tid; it < S * H; it += nt) {
+    const int s = it / H, j = it - s * H;
+    const float* g = t.pool + op.in0 + s * op.in0_ld;
+    const float r = g[j], z = g[H + j], n = g[2 * H + j];
+    const float dh = t.pool[op.g_out + s * op.out_ld + j];
+    const float dpn = dh * (1.f - z) * (1.f - n * n);
+    const float dpr = dpn * bhh[2 * H + j] * r * (1.f - r);
+    const float dpz = -dh * n * z * (1.f - z);
+    float* gi = t.pool + op.g_in0 + s * op.in0_ld;
+    gi[j] = dpr; gi[H + j] = dpz; gi[2 * H + j] = dpn;
+  }
+}
+
+AFL_DEV void afl_gru_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int H = op.N, S = t.S;
+  for (int j = tid; j < 3 * H; j += nt) {
+    float a = 0.f;
+    for (int s = 0; s < S; ++s) {
+      float d = t.pool[op.g_in0 + s * op.in0_ld + j];
+      if (j >= 2 * H) d *= t.pool[op.in0 + s * op.in0_ld + (j - 2 * H)];   // d b_hn = dpn * r
+      a += d;
+    }
+    afl_store(t.gw + op.w2 + j, a, t.accumulate);
+  }
+}
+
+// ----------------------------------------------------------------------------------------- CONV1D k=3 pad=1 + ReLU
+// in0: [S][Cin][.] (sample stride in0_ld, channel stride in_cs); out likewise; W [Cout][Cin][3]; N=Cout, K=Cin, L=len
+template <int L>
+AFL_DEV void afl_conv_fwd_t(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int Co = op.N, Ci = op.K, S = t.S;
+  for (int it = tid; it < S * Co; it += nt) {
+    const int co = it % Co, s = it / Co;
+    const float* wr = t.w + op.w + (int64_t)co * Ci * 3;
+    const float* xs = t.pool + op.in0 + s * op.in0_ld;
+    float acc[L];
+    const float bias = t.w[op.b + co];
+#pragma unroll
+    for (int l = 0; l < L; ++l) acc[l] = bias;
+    for (int ci = 0; ci < Ci; ++ci) {
+      const float w0 = wr[ci * 3], w1 = wr[ci * 3 + 1], w2 = wr[ci * 3 + 2];
+      const float* xr = xs + ci * op.in_cs;
+      float xm = 0.f, xc = xr[0];
+#pragma unroll
+      for (int l = 0; l < L; ++l) {
+        const float xp = (l + 1 < L) ? xr[l + 1] : 0.f;
+        acc[l] += w0 * xm + w1 * xc + w2 * xp;
+        xm = xc; xc = xp;
+      }
+    }
+    float* yr = t.pool + op.out + s * op.out_ld + co * op.out_cs;
+#pragma unroll
+    for (int l = 0; l < L; ++l) yr[l] = acc[l] > 0.f ? acc[l] : 0.f;
+  }
+}
+
+// Phase A: dz = dy * (y > 0) in place.
+AFL_DEV void afl_conv_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int Co = op.N, S = t.S, L = op.L;
+  for (int it = tid; it < S * Co * L; it += nt) {
+    const int l = it % L, r = it / L, co = r % Co, s = r / Co;
+    const int o = s * op.out_ld + co * op.out_cs + l;
+    if (!(t.pool[op.out + o] > 0.f)) t.pool[op.g_out + o] = 0.f;
+  }
+}
+
+template <int L>
+AFL_DEV void afl_conv_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int Co = op.N, Ci = op.K, S = t.S;
+  const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
+  const int n_dx = need_dx ? S * Ci : 0;
+  const int n_dw = Co * Ci;
+  const int total = n_dx + n_dw + Co;
+  for (int it = tid; it < total; it += nt) {
+    if (it < n_dx) {
+      // dx[s][ci][j] = sum_co sum_k w[co][ci][k] dz[s][co][j-k+1]
+      const int ci = it % Ci, s = it / Ci;
+      const float* dzs = t.pool + op.g_out + s * op.out_ld;
+      float acc[L];
+#pragma unroll
+      for (int l = 0; l < L; ++l) acc[l] = 0.f;
+      for (int co = 0; co < Co; ++co) {
+        const float* wr = t.w + op.w + ((int64_t)co * Ci + ci) * 3;
+        const float w0 = wr[0], w1 = wr[1], w2 = wr[2];
+        const float* dr = dzs + co * op.out_cs;
+        float dm = 0.f, dc = dr[0];
+#pragma unroll
+        for (int l = 0; l < L; ++l) {
+          const float dp = (l + 1 < L) ? dr[l + 1] : 0.f;
+          acc[l] += w0 * dp + w1 * dc + w2 * dm;
+          dm = dc; dc = dp;
+        }
+      }
+      float* gx = t.pool + op.g_in0 + s * op.in0_ld + ci * op.in_cs;
+#pragma unroll
+      for (int l = 0; l < L; ++l) afl_store(gx + l, acc[l], op.flags & AFL_F_ACC0);
+    } else if (it < n_dx + n_dw) {
+      // dW[co][ci][k] = sum_s sum_l dz[s][co][l] x[s][ci][l+k-1]
+      const int j2 = it - n_dx;
+      const int ci = j2 % Ci, co = j2 / Ci;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+      for (int s = 0; s < S; ++s) {
+        const float* dr = t.pool + op.g_out + s * op.out_ld + co * op.out_cs;
+        const float* xr = t.pool + op.in0 + s * op.in0_ld + ci * op.in_cs;
+        float xm = 0.f, xc = xr[0];
+#pragma unroll
+        for (int l = 0; l < L; ++l) {
+          const float xp = (l + 1 < L) ? xr[l + 1] : 0.f;
+          const float d = dr[l];
+          a0 += d * xm; a1 += d * xc; a2 += d * xp;
+          xm = xc; xc = xp;
+        }
+      }
+      float* g = t.gw + op.w + ((int64_t)co * Ci + ci) * 3;
+      afl_store(g, a0, t.accumulate); afl_store(g + 1, a1, t.accumulate); afl_store(g + 2, a2, t.accumulate);
+    } else {
+      const int co = it - n_dx - n_dw;
+      float a = 0.f;
+      for (int s = 0; s < S; ++s) {
+        const float* dr = t.pool + op.g_out + s * op.out_ld + co * op.out_cs;
+#pragma unroll
+        for (int l = 0; l < L; ++l) a += dr[l];
+      }
+      afl_store(t.gw + op.b + co, a, t.accumulate);
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------- POOL (adaptive avg -> 4) + dropout
+AFL_DEV void afl_pool_bounds(int L, int j, int& a, int& b) { a = (j * L) / 4; b = ((j + 1) * L + 3) / 4; }
+
+AFL_DEV void afl_pool_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int C = op.N, S = t.S, L = op.L;
+  for (int it = tid; it < S * C * 4; it += nt) {
+    const int j = it & 3, r = it >> 2, c = r % C, s = r / C;
+    int a, b; afl_pool_bounds(L, j, a, b);
+    const float* xr = t.pool + op.in0 + s * op.in0_ld + c * op.in_cs;
+    float sum = 0.f;
+    for (int l = a; l < b; ++l) sum += xr[l];
+    const float y = sum / (float)(b - a) * afl_drop_scale(t, op, s, (uint32_t)(c * 4 + j));
+    t.pool[op.out + s * op.out_ld + c * 4 + j] = y;
+  }
+}
+
+AFL_DEV void afl_pool_bwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int C = op.N, S = t.S, L = op.L;
+  for (int it = tid; it < S * C * L; it += nt) {
+    const int l = it % L, r = it / L, c = r % C, s = r / C;
+    float g = 0.f;
+    for (int j = 0; j < 4; ++j) {
+      int a, b; afl_pool_bounds(L, j, a, b);
+      if (l >= a && l < b)
+        g += t.pool[op.g_out + s * op.out_ld + c * 4 + j] * afl_drop_scale(t, op, s, (uint32_t)(c * 4 + j)) / (float)(b - a);
+    }
+    t.pool[op.g_in0 + s * op.in0_ld + c * op.in_cs + l] = g;
+  }
+}
+
+// ----------------------------------------------------------------------------------------- DROPOUT (grouped)
+AFL_DEV void afl_dropout_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S, G = op.L > 0 ? op.L : 1;
+  for (int it = tid; it < S * N; it += nt) {
+    const int s = it / N, n = it - s * N;
+    t.pool[op.out + s * op.out_ld + n] = t.pool[op.in0 + s * op.in0_ld + n] * afl_drop_scale(t, op, s, (uint32_t)(n / G));
+  }
+}
+
+AFL_DEV void afl_dropout_bwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  const int N = op.N, S = t.S, G = op.L > 0 ? op.L : 1;
+  for (int it = tid; it < S * N; it += nt) {
+    const int s = it / N, n = it - s * N;
+    const float g = t.pool[op.g_out + s * op.out_ld + n] * afl_drop_scale(t, op, s, (uint32_t)(n / G));
+    afl_store(t.pool + op.g_in0 + s * op.in0_ld + n, g, op.flags & AFL_F_ACC0);
+  }
+}
+
+// ----------------------------------------------------------------------------------------- BCE (sigmoid + BCELoss)
+// in0: logits [S] (ld 1); in1: labels [S]; g_in0: dL/dlogit; loss_acc[0] += sum loss, loss_acc[1] += #NaN
+AFL_DEV void afl_bce(const AflOp& op, const AflTile& t, int tid, int nt) {
+  for (int s = tid; s < t.S; s += nt) {
+    const float p = afl_sigmoid(t.pool[op.in0 + s * op.in0_ld]);
+    const float y = t.pool[op.in1 + s];
+    const bool valid = s < t.n_valid;
+    if (t.probs) {
+      if (valid) t.probs[t.row0 + s] = p;
+      continue;
+    }
+    float g = 0.f;
+    if (valid) {
+      float lp = logf(p), lq = logf(1.f - p);
+      lp = lp < -100.f ? -100.f : lp;
+      lq = lq < -100.f ? -100.f : lq;
+      const float loss = -(y * lp + (1.f - y) * lq);
+      g = (p - y) * t.inv_b;
+      // one lane per sample; S is small, serialise through slot s to stay warp-intrinsic free
+      t.pool[op.out + s] = loss;
+    } else {
+      t.pool[op.out + s] = 0.f;
+    }
+    t.pool[op.g_in0 + s * op.in0_ld] = g;
+  }
+}
+
+AFL_DEV void afl_bce_reduce(const AflOp& op, const AflTile& t, int tid, int nt) {
+  if (t.probs || tid != 0) return;
+  float sum = 0.f, bad = 0.f;
+  for (int s = 0; s < t.n_valid; ++s) {
+    const float l = t.pool[op.out + s];
+    if (l != l) bad += 1.f; else sum += l;
+  }
+  t.loss_acc[0] += sum;
+  t.loss_acc[1] += bad;
+}
+
+// ----------------------------------------------------------------------------------------- dispatch
+AFL_DEV void afl_conv_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  if (op.L == 7) afl_conv_fwd_t<7>(op, t, tid, nt);
+  else if (op.L == 16) afl_conv_fwd_t<16>(op, t, tid, nt);
+}
+AFL_DEV void afl_conv_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+  if (op.L == 7) afl_conv_bwd_b_t<7>(op, t, tid, nt);
+  else if (op.L == 16) afl_conv_bwd_b_t<16>(op, t, tid, nt);
+}
+
+AFL_DEV void afl_run_forward(const AflOp* ops, int n_ops, const AflTile& t, int tid, int nt) {
+  for (int i = 0; i < n_ops; ++i) {
+    const AflOp& op = ops[i];
+    switch (op.kind) {
+      case AFL_OP_LOAD: afl_load_fwd(op, t, tid, nt); break;
+      case AFL_OP_LINEAR: afl_linear_fwd(op, t, tid, nt); break;
+      case AFL_OP_LN: afl_ln_fwd_a(op, t, tid, nt); AFL_SYNC(); afl_ln_fwd_b(op, t, tid, nt); break;
+      case AFL_OP_GRU: afl_gru_fwd(op, t, tid, nt); break;
+      case AFL_OP_CONV: afl_conv_fwd(op, t, tid, nt); break;
+      case AFL_OP_POOL: afl_pool_fwd(op, t, tid, nt); break;
+      case AFL_OP_DROPOUT: afl_dropout_fwd(op, t, tid, nt); break;
+      case AFL_OP_BCE: afl_bce(op, t, tid, nt); AFL_SYNC(); afl_bce_reduce(op, t, tid, nt); break;
+      default: break;
+    }
+    AFL_SYNC();
+  }
+}
+
+AFL_DEV void afl_run_backward(const AflOp* ops, int n_ops, const AflTile& t, int tid, int nt) {
+  for (int i = n_ops - 1; i >= 0; --i) {
+    const AflOp& op = ops[i];
+    switch (op.kind) {
+      case AFL_OP_LINEAR: afl_linear_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_linear_bwd_b(op, t, tid, nt); break;
+      case AFL_OP_LN: afl_ln_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_ln_bwd_b(op, t, tid, nt); break;
+      case AFL_OP_GRU: afl_gru_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_gru_bwd_b(op, t, tid, nt); break;
+      case AFL_OP_CONV: afl_conv_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_conv_bwd_b(op, t, tid, nt); break;
+      case AFL_OP_POOL: afl_pool_bwd(op, t, tid, nt); break;
+      case AFL_OP_DROPOUT: afl_dropout_bwd(op, t, tid, nt); break;
+      default: break;   // LOAD / BCE have no backward work (BCE wrote dL/dlogit in forward)
+    }
+    AFL_SYNC();
+  }
+}
+
+// ----------------------------------------------------------------------------------------- optimiser phase
+struct AflOpt {
+  int kind;            // 0 = Adam, 1 = SGD-momentum
+  float lr, beta1, beta2, eps, momentum;
+  float bc1, bc2;      // Adam bias corrections 1-beta^t for this step
+  int first_step;      // SGD: momentum buffer initialised with the gradient (torch semantics)
+  float clip_coef;     // gradient scale (1 = none)
+};
+
+// Reduce G partial rows over [lo, hi) and apply the update.  gpart: [G][d_pad].
+AFL_DEV void afl_reduce_update(float* w, float* m, float* v, const float* gpart, int G, int64_t d_pad,
+                               int64_t lo, int64_t hi, const AflOpt& o, int tid, int nt) {
+  for (int64_t i = lo + tid; i < hi; i += nt) {
+    float g = 0.f;
+    for (int q = 0; q < G; ++q) g += gpart[(int64_t)q * d_pad + i];
+    g *= o.clip_coef;
+    if (o.kind == 0) {
+      const float mi = o.beta1 * m[i] + (1.f - o.beta1) * g;
+      const float vi = o.beta2 * v[i] + (1.f - o.beta2) * g * g;
+      m[i] = mi; v[i] = vi;
+      const float denom = sqrtf(vi) / sqrtf(o.bc2) + o.eps;
+      w[i] -= (o.lr / o.bc1) * (mi / denom);
+    } else {
+      const float b = o.first_step ? g : o.momentum * m[i] + g;
+      m[i] = b;
+      w[i] -= o.lr * b;
+    }
+  }
+}
+
+// Sum of squares of the reduced gradient over [lo, hi) (for clip-mode "proper"); returns thread partial.
+AFL_DEV float afl_reduce_sqnorm(const float* gpart, int G, int64_t d_pad, int64_t lo, int64_t hi, int tid, int nt) {
+  float acc = 0.f;
+  for (int64_t i = lo + tid; i < hi; i += nt) {
+    float g = 0.f;
+    for (int q = 0; q < G; ++q) g += gpart[(int64_t)q * d_pad + i];
+    acc += g * g;
+  }
+  return acc;
+}

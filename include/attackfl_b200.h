@@ -1,0 +1,97 @@
+/* attackfl_b200 native library — C ABI.
+ *
+ * Two shared objects export this interface:
+ *   attackfl_b200/lib/libattackfl_b200.so   CUDA build, sm_100a (pointers are device pointers, `stream` is a
+ *                                           cudaStream_t; every call is asynchronous on that stream)
+ *   attackfl_b200/lib/libattackfl_cpu.so    CPU twin compiled from the same kernel sources (pointers are host
+ *                                           pointers, `stream` is ignored); backs `--device cpu` and the tests
+ * All functions return 0 on success; otherwise afl_last_error() describes the failure.
+ * Citations are relative to the reference repository filrg/attackFL.
+ */
+#ifndef ATTACKFL_B200_H_
+#define ATTACKFL_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* afl_last_error(void);
+long long afl_launch_count(void);          /* kernels launched by this library since the last reset */
+void afl_reset_launch_count(void);
+int afl_is_cuda_build(void);
+int afl_num_sms(void);
+
+/* T8 — flat optimisers over n = rows*d_pad coordinates (client.py:78,107: Adam(lr), re-created per round;
+ * `momentum` is plumbed but unused in the reference, honoured here by afl_sgdm_flat).  gscale (device scalar,
+ * nullable) multiplies the gradient (used for gradient clipping, client.py:104-105 / server.py:667-668). */
+int afl_adam_flat(float* w, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                  int step, const float* gscale, void* stream);
+int afl_sgdm_flat(float* w, const float* g, float* buf, int64_t n, float lr, float momentum, int first_step,
+                  const float* gscale, void* stream);
+
+/* K1 + K2 — sample-weighted FedAvg reduce fused with the broadcast of the new global row to `Cb` client rows
+ * (server.py:751-775 + the START fan-out at :588-614) and, in the same pass over the rows, the per-attacker
+ * shifted moments -> mean / unbiased std / LIE row mu + z*sd (src/Utils.py:83-98,207-214).
+ * rows [C][d_pad]; weights [C]; member [A][C] 0/1; kcount,z [A]; mu,sd,lie [A][d_pad]; A <= 4 per call. */
+int afl_fedavg(const float* rows, const float* weights, int C, int64_t d_pad, float* out, float* bcast, int Cb,
+               int A, const float* ref, const float* member, const float* kcount, const float* z, float* mu,
+               float* sd, float* lie, int strict_k1, void* stream);
+
+/* K4 — gamma bisection on the (k+2)x(k+2) Gram matrix of [g_1-c..g_k-c, mu-c, p] (src/Utils.py:115-130;
+ * rule 0 = Min-Max / Opt-Fang, 1 = Min-Sum; exclude_first reproduces the aliasing of genuine model 0,
+ * paper=1 returns gamma_succ).  out4 = {gamma, gamma_succ, threshold, probes} in device memory. */
+int afl_gamma_search_dev(const float* G, int k, int rule, int exclude_first, int paper, float* out4, void* stream);
+/* out = mu - gamma*p (sign_mode=1: p = sign(mu), Opt-Fang); gamma is read from device memory. */
+int afl_craft_axpy(float* out, const float* mu, const float* p, const float* gamma_dev, int sign_mode, int64_t n,
+                   void* stream);
+/* Random attack: out = (w + N(0,1)*perturbation) * valid   (src/Utils.py:52-57), Philox + Box-Muller. */
+int afl_craft_random(float* out, const float* w, const float* valid, float perturbation, uint64_t seed,
+                     uint32_t stream_id, int64_t n, void* stream);
+
+/* K6 — per-coordinate selection over C rows: mode 0 lower median (src/Utils.py:344-357), mode 1 trimmed mean
+ * dropping `trim` values per side (src/Utils.py:267-302). */
+int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mode, int trim, void* stream);
+
+/* K5a — hyper-network emit: theta[c] = W_h . MLP(E[clients[c]]) + b_h for n clients (src/Model.py:285-304,
+ * server.py:589-590,674-678).  small = params|m|v of {emb, mlp}; acts [E+5H] (n==1 only); f_scratch [n*H]. */
+int afl_hyper_emit(const float* head_w, const float* head_b, float* small, int n_nodes, int E, int H,
+                   const int* clients_dev, int n, float* f_scratch, float* acts, float* theta, int64_t theta_ld,
+                   int64_t d_pad, void* stream);
+/* K5b — one sequential pFedHN step for `client` (server.py:644-670): delta = h(client) - theta_client, closed-form
+ * rank-1 head gradient, MLP/embedding backward, global-norm clip, dense Adam.  red [H+3] scratch:
+ * red[H+1] = clip coefficient, red[H+2] = pre-clip gradient norm. */
+int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb, float* vb, float* small,
+                   int n_nodes, int E, int H, int client, const int* client_dev, const float* theta_client,
+                   float* delta, float* f_scratch, float* acts, float* red, int64_t d_pad, float lr, float b1,
+                   float b2, float eps, int step, float clip, void* stream);
+
+/* T1-T7 — local training of a chunk of clients for one round as ONE persistent kernel (client.py:75-111;
+ * models src/Model.py:27-246).  ops: int32 program [n_ops][32] (attackfl_b200/models/programs.py);
+ * w,m,v [C][d_pad]; gpart [C][G][d_pad]; data [rows][rec]; idx [C][epochs][>=n] int32; G blocks per client,
+ * M tiles of S samples per block (G*M*S >= batch).  loss_out [C][2] = {sum of per-sample losses, #NaN losses},
+ * steps_out [C]; bar [C] and gnorm [C][2] are scratch.  opt_kind 0 Adam / 1 SGD-momentum. */
+int afl_train_capacity(int pool_floats, int n_ops);
+int afl_train_round(const int32_t* ops_dev, int n_ops, int pool_floats, float* w, float* m, float* v, float* gpart,
+                    int64_t d_pad, const float* data, int rec, const int32_t* idx, int64_t idx_stride_c,
+                    int64_t idx_stride_e, const int32_t* n_data, const int32_t* client_ids, int n_clients, int G,
+                    int M, int S, int batch, int epochs, int opt_kind, float lr, float beta1, float beta2, float eps,
+                    float momentum, int clip_proper, float clip, uint64_t seed, int dropout, float* loss_out,
+                    int32_t* steps_out, uint32_t* bar, float* gnorm, void* stream);
+/* Batched inference of n_models rows over the same records (src/Validation.py:92-122,178-213); probs [n_models][n_rows]. */
+int afl_infer(const int32_t* ops_dev, int n_ops, int pool_floats, const float* w, int64_t d_pad, int n_models,
+              const float* data, int rec, int64_t n_rows, float* probs, int S, void* stream);
+
+/* Test hooks (host-side in both builds): one forward+backward of a single tile on host memory through the
+ * same op implementations, and the dropout keep decision for (seed, client, step, sample, rng, elem, p). */
+int afl_debug_tile(const int32_t* ops, int n_ops, int pool_floats, const float* w, float* gw, const float* data,
+                   int rec, const int32_t* idx, int S, int n_valid, float inv_b, uint64_t seed, uint32_t client,
+                   uint32_t step, int sample_base, int train, float* pool_out, float* loss_out2);
+int afl_dropout_keep(uint64_t seed, uint32_t client, uint32_t step, uint32_t sample, uint32_t rng, uint32_t elem,
+                     float p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ATTACKFL_B200_H_ */

@@ -1,0 +1,163 @@
+"""Native kernels vs plain PyTorch fp32 references.  Each test runs on the CPU twin (same kernel
+sources compiled with g++) and, marked ``gpu``, on the sm_100a library."""
+import math
+
+import pytest
+import torch
+
+from attackfl_b200 import FlatLayout, models
+from attackfl_b200 import aggregators as agg
+from attackfl_b200 import attacks as atk
+from attackfl_b200.models.hyper import FusedHyperNet
+from attackfl_b200.ops import flat
+
+DEVICES = ["cpu", pytest.param("cuda", marks=pytest.mark.gpu)]
+
+
+def _rand_rows(c, d, device, seed=0, spread=0.05):
+    g = torch.Generator().manual_seed(seed)
+    base = torch.randn(d, generator=g)
+    rows = base[None] + spread * torch.randn(c, d, generator=g)
+    return rows.to(device).contiguous()
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_adam_flat_matches_torch(device):
+    torch.manual_seed(0)
+    w0 = torch.randn(3, 1024)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.Adam([p], lr=0.004)
+    w = w0.clone().to(device)
+    m, v = torch.zeros_like(w), torch.zeros_like(w)
+    for step in range(1, 6):
+        g = torch.randn(3, 1024)
+        p.grad = g.clone()
+        opt.step()
+        flat.adam_flat(w, g.to(device), m, v, 0.004, step)
+    assert torch.allclose(w.cpu(), p.data, atol=1e-6, rtol=1e-5)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_sgdm_flat_matches_torch(device):
+    torch.manual_seed(0)
+    w0 = torch.randn(2048)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.SGD([p], lr=0.01, momentum=0.5)
+    w = w0.clone().to(device)
+    buf = torch.zeros_like(w)
+    for step in range(4):
+        g = torch.randn(2048)
+        p.grad = g.clone()
+        opt.step()
+        flat.sgdm_flat(w, g.to(device), buf, 0.01, 0.5, step == 0)
+    assert torch.allclose(w.cpu(), p.data, atol=1e-6, rtol=1e-5)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("c,a", [(3, 0), (8, 1), (24, 3), (16, 6)])
+def test_fedavg_with_moments(device, c, a):
+    d = 4096
+    rows = _rand_rows(c, d, device, seed=c)
+    sizes = torch.randint(12000, 15001, (c,)).float()
+    wts = (sizes / sizes.sum()).to(device)
+    bcast = torch.zeros(c, d, device=device)
+    member = None
+    z = None
+    if a:
+        g = torch.Generator().manual_seed(1)
+        member = (torch.rand(a, c, generator=g) < 0.6).float()
+        member[:, 0] = 1.0
+        member[:, 1] = 1.0
+        z = torch.linspace(0.5, 1.5, a)
+    out, mu, sd, lie = flat.fedavg(rows, wts, bcast=bcast, member=member, z=z, ref=rows[0].clone(), want_lie=bool(a))
+    want = agg.fedavg(rows.cpu(), sizes.tolist())
+    assert torch.allclose(out.cpu(), want, atol=1e-5, rtol=1e-5)
+    assert torch.allclose(bcast.cpu(), want[None].expand(c, d), atol=1e-5, rtol=1e-5)
+    for q in range(a):
+        sub = rows.cpu()[member[q] > 0]
+        assert torch.allclose(mu[q].cpu(), sub.mean(0), atol=1e-5, rtol=1e-5)
+        assert torch.allclose(sd[q].cpu(), sub.std(0), atol=1e-5, rtol=1e-4)
+        assert torch.allclose(lie[q].cpu(), atk.lie_attack(sub, float(z[q])), atol=1e-5, rtol=1e-4)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_fedavg_k1_guard(device):
+    rows = _rand_rows(4, 1024, device)
+    member = torch.tensor([[1.0, 0, 0, 0]])
+    wts = torch.full((4,), 0.25, device=device)
+    _, mu, sd, _ = flat.fedavg(rows, wts, member=member, want_mu=True, want_sd=True)
+    assert torch.equal(sd[0].cpu(), torch.zeros(1024)) and torch.allclose(mu[0], rows[0])
+    _, _, sd, _ = flat.fedavg(rows, wts, member=member, want_sd=True, strict_k1=True)
+    assert torch.isnan(sd).all()
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("c", [3, 10, 11, 37, 128])
+def test_coord_select(device, c):
+    rows = _rand_rows(c, 2048, device, seed=c, spread=1.0)
+    assert torch.equal(flat.coord_select(rows, "median").cpu(), agg.median(rows.cpu()))
+    k = int(c * 0.1)
+    got = flat.coord_select(rows, "trimmed", k).cpu()
+    assert torch.allclose(got, agg.trimmed_mean(rows.cpu(), 0.1), atol=1e-5, rtol=1e-5)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("mode", ["Min-Max", "Min-Sum", "Opt-Fang"])
+def test_gamma_search_and_craft(device, mode):
+    torch.manual_seed(3)
+    k, d = 9, 4096
+    rows = _rand_rows(k, d, "cpu", seed=5, spread=0.03)
+    res = {"Min-Max": atk.min_max_attack, "Min-Sum": atk.min_sum_attack, "Opt-Fang": atk.opt_fang_attack}[mode](
+        rows[0], rows, metric="flat", center=rows.mean(0))
+    mu, sd = atk.mean_std(rows)
+    p = sd if mode != "Opt-Fang" else torch.sign(mu)
+    c = rows.mean(0)
+    a = torch.cat([rows - c, (mu - c)[None], p[None]])
+    G = (a.double() @ a.double().t()).float().to(device)
+    out = flat.gamma_search(G, k, "sum" if mode == "Min-Sum" else "max")
+    assert out[0].item() == pytest.approx(res.gamma)
+    assert out[1].item() == pytest.approx(res.gamma_succ)
+    assert out[2].item() == pytest.approx(res.threshold, rel=1e-4)
+    crafted = flat.craft_axpy(mu.to(device), p.to(device), out, sign_mode=(mode == "Opt-Fang"))
+    assert torch.allclose(crafted.cpu(), res.crafted, atol=1e-5)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_craft_random(device):
+    w = torch.zeros(1 << 16, device=device)
+    valid = torch.ones_like(w)
+    valid[-100:] = 0
+    out = flat.craft_random(w, valid, 0.5, seed=7, stream_id=3).cpu()
+    assert abs(out[:-100].std().item() - 0.5) < 0.01 and abs(out.mean().item()) < 0.01
+    assert float(out[-100:].abs().sum()) == 0.0
+    again = flat.craft_random(w, valid, 0.5, seed=7, stream_id=3).cpu()
+    other = flat.craft_random(w, valid, 0.5, seed=7, stream_id=4).cpu()
+    assert torch.equal(out, again) and not torch.equal(out, other)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_hyper_emit_and_step_match_torch(device):
+    torch.manual_seed(0)
+    n = 4
+    h = models.HyperNetwork(models.TransformerModel(), n, 8, 100, False, 2)
+    ref = FusedHyperNet.from_module(h, device="cpu")
+    fused = FusedHyperNet.from_module(h, device=device)
+    nat = flat.NativeHyper(fused)
+    lay = fused.layout
+    theta = nat.emit(list(range(n)))
+    want = ref.emit_torch(torch.arange(n))
+    assert torch.allclose(theta.cpu(), want, atol=1e-5)
+    rows = []
+    for i in range(n):
+        torch.manual_seed(20 + i)
+        rows.append(lay.flatten(models.TransformerModel().state_dict()))
+    rows = torch.stack(rows)
+    agg.hyper_round_torch(ref, list(range(n)), rows, 1e-3, 1.0)
+    rows_d = rows.to(device)
+    for i in range(n):
+        nat.step(i, rows_d[i], 1e-3, 1.0)
+    nat.unpack()
+    got, exp = fused.export_state_dict(), ref.export_state_dict()
+    for k in exp:
+        assert torch.allclose(got[k], exp[k], atol=3e-6, rtol=1e-4), k
+    assert fused.step == ref.step == n
