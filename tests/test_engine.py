@@ -1,0 +1,127 @@
+"""End-to-end rounds through the public API (``Federation``): every mode, every attack, failure handling,
+checkpoint / resume.  CPU twin by default, GPU variants marked ``gpu``."""
+import os
+
+import pytest
+import torch
+
+from attackfl_b200 import from_dict, models
+from attackfl_b200.engine import ClientSpec, Federation
+
+DEVICES = ["cpu", pytest.param("cuda", marks=pytest.mark.gpu)]
+
+
+def _cfg(mode, model, n, rounds=2, **extra):
+    d = {"server": {"num-round": rounds, "clients": n, "mode": mode, "model": model, "data-name": "ICU",
+                    "data-distribution": {"num-data-range": [300, 400]}, "random-seed": 1},
+         "learning": {"epoch": 2, "batch-size": 32, "learning-rate": 0.004, "hyper-lr": 0.001, "clip-grad-norm": 1.0},
+         "runtime": {"synthetic_train_rows": 1024, "synthetic_test_rows": 512}}
+    for k, v in extra.items():
+        d.setdefault(k, {}).update(v)
+    return from_dict(d)
+
+
+def _specs(n, **attackers):
+    sp = [ClientSpec(i) for i in range(n)]
+    for i, (mode, rnd, args) in attackers.items():
+        sp[int(i[1:])] = ClientSpec(int(i[1:]), True, mode, rnd, args)
+    return sp
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("model", ["TransformerModel", "RNNModel", "CNNModel"])
+def test_fedavg_learns(tmp_path, device, model):
+    fed = Federation(_cfg("fedavg", model, 3, rounds=3), _specs(3), device=device, workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert [r.ok for r in res] == [True] * 3
+    assert res[-1].metric > 0.7
+    sd = torch.load(tmp_path / f"{model}.pth", weights_only=True)
+    models.build(model).load_state_dict(sd)                     # reference-compatible .pth
+    assert os.path.exists(tmp_path / "metrics.jsonl")
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_attacks_activate_from_their_round(tmp_path, device):
+    sp = _specs(6, c3=("Random", 2, [0.5]), c4=("LIE", 2, [0.74]), c5=("Min-Max", 3, None))
+    fed = Federation(_cfg("fedavg", "RNNModel", 6, rounds=3), sp, device=device, workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert res[0].attackers == [] and res[1].attackers == [3, 4] and res[2].attackers == [3, 4, 5]
+    assert all(r.ok for r in res)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("mode", ["Min-Sum", "Opt-Fang"])
+def test_gram_attacks_run(tmp_path, device, mode):
+    sp = _specs(5, c4=(mode, 2, None))
+    fed = Federation(_cfg("fedavg", "TransformerModel", 5, rounds=2), sp, device=device, workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert res[1].attackers == [4] and all(r.ok for r in res)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_hyper_mode_and_resume(tmp_path, device):
+    cfg = _cfg("hyper", "TransformerModel", 3, rounds=2)
+    fed = Federation(cfg, _specs(3), device=device, workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert all(r.ok for r in res)
+    p = tmp_path / "TransformerModel_hyper_3.pth"
+    sd = torch.load(p, weights_only=True)
+    assert len(sd) == 121 and "hyper_layers.fc1__weight.weight" in sd
+    h = models.HyperNetwork(models.TransformerModel(), 3, 8, 100, False, 2)
+    h.load_state_dict(sd)
+    cfg2 = _cfg("hyper", "TransformerModel", 3, rounds=1, server={"parameters": {"load": True}})
+    fed2 = Federation(cfg2, _specs(3), device=device, workdir=str(tmp_path), verbose=False)
+    got = fed2.hyper.export_state_dict()
+    assert all(torch.allclose(got[k], sd[k]) for k in sd)       # real resume
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("mode", ["trimmed_mean", "median", "krum", "shieldfl", "scionfl", "FLTrust", "fltracer",
+                                  "byzantine", "gmm"])
+def test_defences_run(tmp_path, device, mode):
+    fed = Federation(_cfg(mode, "TransformerModel", 5), _specs(5), device=device, workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert all(r.ok for r in res) and res[-1].metric > 0.6
+
+
+def test_nan_update_fails_round_and_retries(tmp_path):
+    """A NaN model => validation fails => round discarded and repeated (server.py:546-563)."""
+    fed = Federation(_cfg("fedavg", "TransformerModel", 3, rounds=2), _specs(3), device="cpu", workdir=str(tmp_path),
+                     verbose=False)
+    r1 = fed.run_round()
+    assert r1.ok and fed.remaining == 1
+    good = fed.global_row.clone()
+    orig = fed._aggregate
+
+    def poisoned(rows_all, reporting):
+        info = orig(rows_all, reporting)
+        fed.global_row.fill_(float("nan"))
+        return info
+    fed._aggregate = poisoned
+    r2 = fed.run_round()
+    assert not r2.ok and fed.remaining == 1 and fed.failures_in_a_row == 1
+    assert torch.equal(fed.global_row, good)                    # poisoned global is not propagated (Q10)
+    fed._aggregate = orig
+    r3 = fed.run_round()
+    assert r3.ok and fed.remaining == 0
+
+
+def test_torch_backend_matches_native_without_dropout(tmp_path):
+    """The pure-PyTorch fall-back trainer and the native kernel implement the same round."""
+    out = []
+    for backend in ("native", "torch"):
+        cfg = _cfg("fedavg", "TransformerModel", 2, rounds=1, learning={"dropout": False}, runtime={"backend": backend})
+        fed = Federation(cfg, _specs(2), device="cpu", workdir=str(tmp_path), verbose=False, save=False)
+        fed.run()
+        out.append(fed.global_row.clone())
+    assert torch.allclose(out[0], out[1], atol=5e-4, rtol=1e-2)
+
+
+def test_har_round(tmp_path):
+    d = {"server": {"num-round": 1, "clients": 2, "mode": "fedavg", "model": "TransformerClassifier", "data-name": "HAR",
+                    "data-distribution": {"num-data-range": [16, 24]}, "random-seed": 1},
+         "learning": {"epoch": 1, "batch-size": 8, "learning-rate": 0.001},
+         "runtime": {"synthetic_train_rows": 32, "synthetic_test_rows": 16}}
+    fed = Federation(from_dict(d), _specs(2), device="cpu", workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert res[0].ok and 0.0 <= res[0].metric <= 1.0
