@@ -107,9 +107,11 @@ class Federation:
             self.T = T
             self.train_prog = build_program(self.model_name, self.layout, train=True, dropout=l.dropout,
                                             module=self.module).to(self.device)
-            s_inf = 32 if self.model_name != "CNNModel" else 8
-            self.infer_prog = build_program(self.model_name, self.layout, S=s_inf, train=False,
-                                            module=self.module).to(self.device)
+            for s_inf in (32, 16, 8, 4):                  # largest inference tile whose pool fits in shared memory
+                prog = build_program(self.model_name, self.layout, S=s_inf, train=False, module=self.module)
+                if prog.smem_bytes() <= 200 * 1024:
+                    break
+            self.infer_prog = prog.to(self.device)
 
         # ---- data (device resident)
         if train_set is None:

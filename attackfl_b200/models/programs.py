@@ -30,7 +30,7 @@ ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
 F_ACC0, F_ACC1, F_NEED_GIN0, F_MASK_INPUT = 1, 2, 4, 8
 
 _FIELDS = ["kind", "act", "in0", "in0_ld", "in1", "in1_ld", "out", "out_ld", "aux", "aux2", "w", "b", "w2",
-           "N", "K", "L", "p", "rng", "g_out", "g_in0", "g_in1", "flags", "in_cs", "out_cs"]
+           "N", "K", "L", "p", "rng", "g_out", "g_in0", "g_in1", "flags", "in_cs", "out_cs", "grp_start", "grp_size"]
 
 
 def _align(x: int, a: int = 4) -> int:
@@ -72,7 +72,7 @@ class Program:
         return Program(self.ops.to(device), self.n_ops, self.pool_floats, self.S, self.rec, self.model,
                        self.train, self.act_floats, self.grad_floats)
 
-    def smem_bytes(self, threads: int = 256) -> int:
+    def smem_bytes(self, threads: int = 512) -> int:
         return 4 * self.pool_floats + 4 * OP_WORDS * self.n_ops + 4 * (threads + 4)
 
 
@@ -81,6 +81,7 @@ class Builder:
         self.layout, self.S, self.train = layout, S, train
         self.roots: List[_Root] = []
         self.ops: List[Dict] = []
+        self._sink: List[Dict] = self.ops
         self._rng = 0
 
     # -- buffers
@@ -93,17 +94,39 @@ class Builder:
     def view(self, b: Buf, col: int, width: int) -> Buf:
         return Buf(b.root, b.col + col, b.ld, width)
 
-    def _use(self, op_idx: int, produced: List[Optional[Buf]], consumed: List[Optional[Buf]]):
-        for b in produced:
-            if b is not None:
-                self.roots[b.root].producers.append(op_idx)
-        for b in consumed:
-            if b is not None:
-                self.roots[b.root].consumers.append(op_idx)
+    def _use(self, op: Dict, produced: List[Optional[Buf]], consumed: List[Optional[Buf]]):
+        op["_produced"] = [b for b in produced if b is not None]
+        op["_consumed"] = [b for b in consumed if b is not None]
 
-    def _emit(self, **kw) -> int:
-        self.ops.append(kw)
-        return len(self.ops) - 1
+    def _emit(self, **kw) -> Dict:
+        self._sink.append(kw)
+        return kw
+
+    # -- concurrent groups: independent op sequences (e.g. the two input branches) are emitted into separate
+    #    lists and zipped; ops at the same position form a group the kernel runs in one barrier interval.
+    def branch(self, fn) -> List[Dict]:
+        keep, self._sink = self._sink, []
+        try:
+            fn()
+            return self._sink
+        finally:
+            self._sink = keep
+
+    def zip_groups(self, *lists: List[Dict]) -> None:
+        n = len(lists[0])
+        assert all(len(l) == n for l in lists), "branches must have the same op sequence"
+        for j in range(n):
+            members = [l[j] for l in lists]
+            assert len({m["kind"] for m in members}) == 1, "grouped ops must have the same kind"
+            touched = set()
+            for m in members:                      # gradient targets must be disjoint inside a group (no races)
+                for b in m["_consumed"]:
+                    if self.roots[b.root].needs_grad:
+                        assert b.root not in touched, "ops of one group write the same gradient buffer"
+                        touched.add(b.root)
+            for m in members:
+                m["_group"] = members
+                self._sink.append(m)
 
     def _next_rng(self) -> int:
         self._rng += 1
@@ -173,6 +196,14 @@ class Builder:
 
     # -- planning + packing
     def finish(self, model: str) -> Program:
+        for r in self.roots:
+            r.producers, r.consumers = [], []
+        for i, op in enumerate(self.ops):
+            op["_idx"] = i
+            for b in op.get("_produced", []):
+                self.roots[b.root].producers.append(i)
+            for b in op.get("_consumed", []):
+                self.roots[b.root].consumers.append(i)
         off = 0
         for r in self.roots:
             r.off = off
@@ -185,7 +216,11 @@ class Builder:
             for rid, r in enumerate(self.roots):
                 if not r.needs_grad or not r.consumers:
                     continue
-                live.append((max(r.consumers), min(r.producers) if r.producers else 0, rid))
+                # ops of a concurrent group share one time step: widen to the group's first / last member
+                hi_op, lo_op = self.ops[max(r.consumers)], self.ops[min(r.producers) if r.producers else 0]
+                hi_t = hi_op["_group"][-1]["_idx"] if hi_op.get("_group") else hi_op["_idx"]
+                lo_t = lo_op["_group"][0]["_idx"] if lo_op.get("_group") else lo_op["_idx"]
+                live.append((hi_t, lo_t, rid))
             live.sort(reverse=True)
             placed: List[Tuple[int, int, int, int]] = []      # (goff, size, lo, hi)
             for hi, lo, rid in live:
@@ -240,6 +275,12 @@ class Builder:
                 if op["kind"] == K_BCE:
                     rec["g_in0"] = g_off(in0)
             rec["flags"] = flags
+            grp = op.get("_group")
+            if grp:
+                rec["grp_start"] = grp[0]["_idx"]
+                rec["grp_size"] = len(grp) if op is grp[0] else 0
+            else:
+                rec["grp_start"], rec["grp_size"] = i, 1
             for j, k in enumerate(_FIELDS):
                 if k == "p":
                     words[i, j] = struct.unpack("<i", struct.pack("<f", float(op.get("p", 0.0))))[0]
@@ -254,7 +295,8 @@ def _transformer(bd: Builder, d: int, ff: int, heads: int, dropout: bool):
     p1, p3 = (0.1, 0.3) if dropout else (0.0, 0.0)
     v, l, y = bd.load(mask_input=False)
     cat = bd.new(2 * d)
-    for bi, (name, x, k_in) in enumerate((("vitals", v, VITALS_DIM), ("labs", l, LABS_DIM))):
+
+    def branch(bi, name, x, k_in):
         t = f"{name}_transformer"
         h0 = bd.linear(x, f"{name}_dense.weight", f"{name}_dense.bias", d, k_in, ACT_GELU)
         # one token => softmax == 1 => attention = out_proj(dropout_head(V h0)); Q/K never touched
@@ -267,6 +309,9 @@ def _transformer(bd: Builder, d: int, ff: int, heads: int, dropout: bool):
         f2 = bd.linear(f1, f"{t}.ffn.3.weight", f"{t}.ffn.3.bias", d, ff)
         y2 = bd.layernorm(y1, f"{t}.ffn_norm.weight", f"{t}.ffn_norm.bias", d, res=f2, p=p1)
         bd.layernorm(y2, f"{name}_bn.weight", f"{name}_bn.bias", d, out=bd.view(cat, bi * d, d))
+
+    bd.zip_groups(bd.branch(lambda: branch(0, "vitals", v, VITALS_DIM)),
+                  bd.branch(lambda: branch(1, "labs", l, LABS_DIM)))
     c1 = bd.linear(cat, "fc1.weight", "fc1.bias", d, 2 * d, ACT_GELU, p=p3)
     c2 = bd.linear(c1, "fc2.weight", "fc2.bias", d // 2, d, ACT_GELU)
     logit = bd.linear(c2, "output.weight", "output.bias", 1, d // 2)
@@ -277,7 +322,8 @@ def _rnn(bd: Builder, H: int, dropout: bool):
     p3 = 0.3 if dropout else 0.0
     v, l, y = bd.load(mask_input=True)
     cat = bd.new(4 * H)
-    for bi, (name, x, k_in) in enumerate((("vitals", v, VITALS_DIM), ("labs", l, LABS_DIM))):
+
+    def branch(bi, name, x, k_in):
         cur, width = x, k_in
         for layer in (1, 2, 3):
             out = bd.new(2 * H)
@@ -292,6 +338,9 @@ def _rnn(bd: Builder, H: int, dropout: bool):
             bd.dropout(ln, 2 * H, p3, out=tgt)
         else:
             bd.layernorm(cur, f"{name}_ln.weight", f"{name}_ln.bias", 2 * H, out=tgt)
+
+    bd.zip_groups(bd.branch(lambda: branch(0, "vitals", v, VITALS_DIM)),
+                  bd.branch(lambda: branch(1, "labs", l, LABS_DIM)))
     c1 = bd.linear(cat, "fc1.weight", "fc1.bias", H, 4 * H, ACT_RELU)
     c2 = bd.linear(c1, "fc2.weight", "fc2.bias", H // 2, H, ACT_RELU)
     logit = bd.linear(c2, "output.weight", "output.bias", 1, H // 2)
@@ -303,12 +352,16 @@ def _cnn(bd: Builder, dropout: bool):
     ch = (1, 32, 64, 128)
     v, l, y = bd.load(mask_input=False)
     cat = bd.new(2 * ch[3] * 4)
-    for bi, (name, x, L) in enumerate((("vitals", v, VITALS_DIM), ("labs", l, LABS_DIM))):
+
+    def branch(bi, name, x, L):
         cur, cs = x, L
         for i in range(3):
             cur = bd.conv(cur, f"{name}_conv{i + 1}.weight", f"{name}_conv{i + 1}.bias", ch[i], ch[i + 1], L, cs)
             cs = L | 1
         bd.pool(cur, ch[3], L, cs, p3, bd.view(cat, bi * ch[3] * 4, ch[3] * 4))
+
+    bd.zip_groups(bd.branch(lambda: branch(0, "vitals", v, VITALS_DIM)),
+                  bd.branch(lambda: branch(1, "labs", l, LABS_DIM)))
     c = bd.linear(cat, "fc1.weight", "fc1.bias", 128, 1024, ACT_RELU)
     c = bd.linear(c, "fc2.weight", "fc2.bias", 64, 128, ACT_RELU)
     c = bd.linear(c, "fc3.weight", "fc3.bias", 32, 64, ACT_RELU)

@@ -14,7 +14,7 @@
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;
 
 struct TrainParams {
   const AflOp* ops; int n_ops; int pool_floats;

@@ -47,7 +47,8 @@ struct AflOp {
   int32_t g_out, g_in0, g_in1;   // gradient buffers (pool offsets)
   int32_t flags;
   int32_t in_cs, out_cs;    // conv/pool channel strides
-  int32_t pad[8];
+  int32_t grp_start, grp_size;   // concurrent-op groups (see afl_run_forward)
+  int32_t pad[6];
 };
 
 struct AflTile {
@@ -86,6 +87,26 @@ AFL_DEV float afl_drop_scale(const AflTile& t, const AflOp& op, int s, uint32_t 
 
 AFL_DEV void afl_store(float* dst, float v, int acc) { *dst = acc ? *dst + v : v; }
 
+// Scales for elements elem4..elem4+3 (elem4 % 4 == 0) from ONE Philox call.
+AFL_DEV float4 afl_drop_scale4(const AflTile& t, const AflOp& op, int s, uint32_t elem4) {
+  float4 r; r.x = r.y = r.z = r.w = 1.f;
+  if (!(t.train && op.p > 0.f)) return r;
+  const AflU4 u = afl_philox(elem4 >> 2, ((uint32_t)op.rng & 0xFFFFu) | (t.client << 16), t.step,
+                             (uint32_t)(t.sample_base + s), t.seed_lo, t.seed_hi);
+  const float inv = 1.f / (1.f - op.p), sc = 1.0f / 16777216.0f;
+  r.x = ((float)(u.x >> 8) * sc >= op.p) ? inv : 0.f;
+  r.y = ((float)(u.y >> 8) * sc >= op.p) ? inv : 0.f;
+  r.z = ((float)(u.z >> 8) * sc >= op.p) ? inv : 0.f;
+  r.w = ((float)(u.w >> 8) * sc >= op.p) ? inv : 0.f;
+  return r;
+}
+
+AFL_DEV void afl_store4(float* dst, float4 v, int acc) {
+  float4* d = reinterpret_cast<float4*>(dst);
+  if (acc) { const float4 o = *d; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+  *d = v;
+}
+
 // ----------------------------------------------------------------------------------------- LOAD
 AFL_DEV void afl_load_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int nv = op.N, nl = op.K;       // vitals / labs widths
@@ -107,6 +128,27 @@ AFL_DEV void afl_load_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
 // ----------------------------------------------------------------------------------------- LINEAR
 #define AFL_TS 4   // samples per thread in the forward / dX mappings
 
+// Weight row chunk of 4*Q floats is loaded into registers first (Q independent 128-bit loads in flight => one
+// L2 latency per chunk instead of one per 4 k), then swept over the thread's AFL_TS samples from shared memory.
+template <int Q>
+AFL_DEV void afl_lin_chunk(const float* wr, const float* x0, int ldx, int ns, float* acc) {
+  float4 wv[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) wv[q] = *reinterpret_cast<const float4*>(wr + 4 * q);
+#pragma unroll
+  for (int j = 0; j < AFL_TS; ++j) {
+    if (j < ns) {
+      float a = acc[j];
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const float4 xv = *reinterpret_cast<const float4*>(x0 + j * ldx + 4 * q);
+        a += wv[q].x * xv.x + wv[q].y * xv.y + wv[q].z * xv.z + wv[q].w * xv.w;
+      }
+      acc[j] = a;
+    }
+  }
+}
+
 AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int N = op.N, K = op.K, S = t.S;
   const int SG = (S + AFL_TS - 1) / AFL_TS;
@@ -114,35 +156,36 @@ AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) 
   for (int it = tid; it < N * SG; it += nt) {
     const int n = it % N, sg = it / N;
     const int s0 = sg * AFL_TS;
+    const int ns = AFL_MIN(AFL_TS, S - s0);
     const float* wr = t.w + op.w + (int64_t)n * K;
     const float* x0 = t.pool + op.in0 + s0 * op.in0_ld;
+    const float bias = op.b >= 0 ? t.w[op.b + n] : 0.f;      // issued early: overlaps the weight loads
     float acc[AFL_TS];
 #pragma unroll
     for (int j = 0; j < AFL_TS; ++j) acc[j] = 0.f;
     if (vec) {
-      for (int k = 0; k < K; k += 4) {
-        const float4 wv = *reinterpret_cast<const float4*>(wr + k);
-#pragma unroll
-        for (int j = 0; j < AFL_TS; ++j) {
-          if (s0 + j < S) {
-            const float4 xv = *reinterpret_cast<const float4*>(x0 + j * op.in0_ld + k);
-            acc[j] += wv.x * xv.x + wv.y * xv.y + wv.z * xv.z + wv.w * xv.w;
-          }
-        }
-      }
+      int k = 0;
+      for (; k + 64 <= K; k += 64) afl_lin_chunk<16>(wr + k, x0 + k, op.in0_ld, ns, acc);
+      for (; k + 16 <= K; k += 16) afl_lin_chunk<4>(wr + k, x0 + k, op.in0_ld, ns, acc);
+      for (; k + 4 <= K; k += 4) afl_lin_chunk<1>(wr + k, x0 + k, op.in0_ld, ns, acc);
     } else {
-      for (int k = 0; k < K; ++k) {
-        const float wv = wr[k];
+      float wv[8];
+      for (int k0 = 0; k0 < K; k0 += 8) {
+        const int kn = AFL_MIN(8, K - k0);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) wv[q] = q < kn ? wr[k0 + q] : 0.f;
 #pragma unroll
         for (int j = 0; j < AFL_TS; ++j)
-          if (s0 + j < S) acc[j] += wv * x0[j * op.in0_ld + k];
+          if (j < ns)
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              if (q < kn) acc[j] += wv[q] * x0[j * op.in0_ld + k0 + q];
       }
     }
-    const float bias = op.b >= 0 ? t.w[op.b + n] : 0.f;
 #pragma unroll
     for (int j = 0; j < AFL_TS; ++j) {
       const int s = s0 + j;
-      if (s >= S) break;
+      if (j >= ns) break;
       const float z = acc[j] + bias;
       if (op.aux >= 0) t.pool[op.aux + s * N + n] = z;
       float y = afl_act_fwd(op.act, z);
@@ -176,53 +219,80 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
   const float* dz = t.pool + op.g_out;        // [S][.], row stride = out_ld (same layout as out)
   const int ldz = op.out_ld;
   const float* x = t.pool + op.in0;
+  const int ldx = op.in0_ld;
   const int SG = (S + AFL_TS - 1) / AFL_TS;
   const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
   const int n_dx = need_dx ? K * SG : 0;
-  const bool vec4 = (N & 3) == 0 && (op.g_out & 3) == 0 && (ldz & 3) == 0;
-  const int NQ = vec4 ? N / 4 : N;
-  const int n_dw = NQ * K;
+  const bool nvec = (N & 3) == 0 && (op.g_out & 3) == 0 && (ldz & 3) == 0;
+  const bool kvec = (K & 3) == 0 && (op.in0 & 3) == 0 && (ldx & 3) == 0 && (op.w & 3) == 0;
+  const bool tile44 = nvec && kvec;                       // 4(n) x 4(k) register tile for dW
+  const int KQ = K >> 2;
+  const int n_dw = tile44 ? (N >> 2) * KQ : (nvec ? (N >> 2) * K : N * K);
   const int n_db = op.b >= 0 ? N : 0;
   const int total = n_dx + n_dw + n_db;
   for (int it = tid; it < total; it += nt) {
     if (it < n_dx) {
-      // dX[s][k] = sum_n dz[s][n] W[n][k]; lanes walk k => coalesced W reads
+      // dX[s][k] = sum_n dz[s][n] W[n][k]; lanes walk k => coalesced W reads; 16 W values preloaded per pass
       const int k = it % K, sg = it / K, s0 = sg * AFL_TS;
+      const int ns = AFL_MIN(AFL_TS, S - s0);
       const float* wc = t.w + op.w + k;
       float acc[AFL_TS];
 #pragma unroll
       for (int j = 0; j < AFL_TS; ++j) acc[j] = 0.f;
-      if (vec4) {
-        for (int n = 0; n < N; n += 4) {
-          const float w0 = wc[(int64_t)n * K], w1 = wc[(int64_t)(n + 1) * K];
-          const float w2 = wc[(int64_t)(n + 2) * K], w3 = wc[(int64_t)(n + 3) * K];
+      int n = 0;
+      if (nvec) {
+        for (; n + 16 <= N; n += 16) {
+          float wv[16];
+#pragma unroll
+          for (int q = 0; q < 16; ++q) wv[q] = wc[(int64_t)(n + q) * K];
 #pragma unroll
           for (int j = 0; j < AFL_TS; ++j) {
-            if (s0 + j < S) {
-              const float4 d = *reinterpret_cast<const float4*>(dz + (s0 + j) * ldz + n);
-              acc[j] += d.x * w0 + d.y * w1 + d.z * w2 + d.w * w3;
+            if (j < ns) {
+              float a = acc[j];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float4 d = *reinterpret_cast<const float4*>(dz + (s0 + j) * ldz + n + 4 * q);
+                a += d.x * wv[4 * q] + d.y * wv[4 * q + 1] + d.z * wv[4 * q + 2] + d.w * wv[4 * q + 3];
+              }
+              acc[j] = a;
             }
           }
         }
-      } else {
-        for (int n = 0; n < N; ++n) {
-          const float wv = wc[(int64_t)n * K];
+      }
+      for (; n < N; ++n) {
+        const float wv = wc[(int64_t)n * K];
 #pragma unroll
-          for (int j = 0; j < AFL_TS; ++j)
-            if (s0 + j < S) acc[j] += dz[(s0 + j) * ldz + n] * wv;
-        }
+        for (int j = 0; j < AFL_TS; ++j)
+          if (j < ns) acc[j] += dz[(s0 + j) * ldz + n] * wv;
       }
 #pragma unroll
       for (int j = 0; j < AFL_TS; ++j)
-        if (s0 + j < S) afl_store(t.pool + op.g_in0 + (s0 + j) * op.in0_ld + k, acc[j], op.flags & AFL_F_ACC0);
+        if (j < ns) afl_store(t.pool + op.g_in0 + (s0 + j) * ldx + k, acc[j], op.flags & AFL_F_ACC0);
     } else if (it < n_dx + n_dw) {
-      // dW[n][k] = sum_s dz[s][n] x[s][k]; lanes walk k => conflict-free x reads, coalesced writes
       const int j2 = it - n_dx;
-      const int k = j2 % K, nq = j2 / K;
-      if (vec4) {
+      if (tile44) {
+        // dW[n0..n0+3][k0..k0+3] = sum_s dz[s][n0..] (x) x[s][k0..]: 2 x 128-bit shared loads per 16 FMAs
+        const int kq = j2 % KQ, nq = j2 / KQ;
+        float4 a0, a1, a2, a3;
+        a0.x = a0.y = a0.z = a0.w = 0.f; a1 = a0; a2 = a0; a3 = a0;
+        for (int s = 0; s < S; ++s) {
+          const float4 d = *reinterpret_cast<const float4*>(dz + s * ldz + 4 * nq);
+          const float4 xv = *reinterpret_cast<const float4*>(x + s * ldx + 4 * kq);
+          a0.x += d.x * xv.x; a0.y += d.x * xv.y; a0.z += d.x * xv.z; a0.w += d.x * xv.w;
+          a1.x += d.y * xv.x; a1.y += d.y * xv.y; a1.z += d.y * xv.z; a1.w += d.y * xv.w;
+          a2.x += d.z * xv.x; a2.y += d.z * xv.y; a2.z += d.z * xv.z; a2.w += d.z * xv.w;
+          a3.x += d.w * xv.x; a3.y += d.w * xv.y; a3.z += d.w * xv.z; a3.w += d.w * xv.w;
+        }
+        float* g = t.gw + op.w + (int64_t)(4 * nq) * K + 4 * kq;
+        afl_store4(g, a0, t.accumulate);
+        afl_store4(g + K, a1, t.accumulate);
+        afl_store4(g + 2 * (int64_t)K, a2, t.accumulate);
+        afl_store4(g + 3 * (int64_t)K, a3, t.accumulate);
+      } else if (nvec) {
+        const int k = j2 % K, nq = j2 / K;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         for (int s = 0; s < S; ++s) {
-          const float xv = x[s * op.in0_ld + k];
+          const float xv = x[s * ldx + k];
           const float4 d = *reinterpret_cast<const float4*>(dz + s * ldz + nq * 4);
           a0 += d.x * xv; a1 += d.y * xv; a2 += d.z * xv; a3 += d.w * xv;
         }
@@ -232,9 +302,10 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
         afl_store(g + 2 * (int64_t)K, a2, t.accumulate);
         afl_store(g + 3 * (int64_t)K, a3, t.accumulate);
       } else {
+        const int k = j2 % K, n = j2 / K;
         float a0 = 0.f;
-        for (int s = 0; s < S; ++s) a0 += dz[s * ldz + nq] * x[s * op.in0_ld + k];
-        afl_store(t.gw + op.w + (int64_t)nq * K + k, a0, t.accumulate);
+        for (int s = 0; s < S; ++s) a0 += dz[s * ldz + n] * x[s * ldx + k];
+        afl_store(t.gw + op.w + (int64_t)n * K + k, a0, t.accumulate);
       }
     } else {
       const int n = it - n_dx - n_dw;
@@ -250,15 +321,31 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
 AFL_DEV void afl_ln_fwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int N = op.N, S = t.S, P = AFL_LN_PARTS;
   const int chunk = (N + P - 1) / P;
+  const bool v4 = (chunk & 3) == 0 && ((op.in0 | op.in0_ld | op.out | op.out_ld) & 3) == 0 &&
+                  (op.in1 < 0 || ((op.in1 | op.in1_ld) & 3) == 0);
   for (int it = tid; it < S * P; it += nt) {
     const int s = it / P, part = it - s * P;
     const int n0 = part * chunk, n1 = AFL_MIN(N, n0 + chunk);
     float sum = 0.f, sq = 0.f;
-    for (int n = n0; n < n1; ++n) {
-      float x = t.pool[op.in0 + s * op.in0_ld + n];
-      if (op.in1 >= 0) x += t.pool[op.in1 + s * op.in1_ld + n] * afl_drop_scale(t, op, s, (uint32_t)n);
-      t.pool[op.out + s * op.out_ld + n] = x;
-      sum += x; sq += x * x;
+    if (v4 && n1 - n0 == chunk) {
+      for (int n = n0; n < n1; n += 4) {
+        float4 x = *reinterpret_cast<const float4*>(t.pool + op.in0 + s * op.in0_ld + n);
+        if (op.in1 >= 0) {
+          const float4 r = *reinterpret_cast<const float4*>(t.pool + op.in1 + s * op.in1_ld + n);
+          const float4 d = afl_drop_scale4(t, op, s, (uint32_t)n);
+          x.x += r.x * d.x; x.y += r.y * d.y; x.z += r.z * d.z; x.w += r.w * d.w;
+        }
+        *reinterpret_cast<float4*>(t.pool + op.out + s * op.out_ld + n) = x;
+        sum += (x.x + x.y) + (x.z + x.w);
+        sq += (x.x * x.x + x.y * x.y) + (x.z * x.z + x.w * x.w);
+      }
+    } else {
+      for (int n = n0; n < n1; ++n) {
+        float x = t.pool[op.in0 + s * op.in0_ld + n];
+        if (op.in1 >= 0) x += t.pool[op.in1 + s * op.in1_ld + n] * afl_drop_scale(t, op, s, (uint32_t)n);
+        t.pool[op.out + s * op.out_ld + n] = x;
+        sum += x; sq += x * x;
+      }
     }
     t.pool[op.aux2 + s * 2 * P + 2 * part] = sum;
     t.pool[op.aux2 + s * 2 * P + 2 * part + 1] = sq;
@@ -267,8 +354,11 @@ AFL_DEV void afl_ln_fwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
 
 AFL_DEV void afl_ln_fwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int N = op.N, S = t.S, P = AFL_LN_PARTS;
-  for (int it = tid; it < S * N; it += nt) {
-    const int s = it / N, n = it - s * N;
+  const bool v4 = (N & 3) == 0 && ((op.out | op.out_ld | op.aux | op.w | op.b) & 3) == 0;
+  const int W = v4 ? 4 : 1;
+  const int NQ = N / W;
+  for (int it = tid; it < S * NQ; it += nt) {
+    const int s = it / NQ, n = (it - s * NQ) * W;
     float sum = 0.f, sq = 0.f;
 #pragma unroll
     for (int q = 0; q < P; ++q) {
@@ -279,9 +369,19 @@ AFL_DEV void afl_ln_fwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
     float var = sq / (float)N - mean * mean;
     var = var > 0.f ? var : 0.f;
     const float rstd = 1.0f / sqrtf(var + AFL_LN_EPS);
-    const float xh = (t.pool[op.out + s * op.out_ld + n] - mean) * rstd;
-    t.pool[op.aux + s * N + n] = xh;
-    t.pool[op.out + s * op.out_ld + n] = xh * t.w[op.w + n] + t.w[op.b + n];
+    if (v4) {
+      float4 x = *reinterpret_cast<const float4*>(t.pool + op.out + s * op.out_ld + n);
+      const float4 ga = *reinterpret_cast<const float4*>(t.w + op.w + n);
+      const float4 be = *reinterpret_cast<const float4*>(t.w + op.b + n);
+      float4 xh; xh.x = (x.x - mean) * rstd; xh.y = (x.y - mean) * rstd; xh.z = (x.z - mean) * rstd; xh.w = (x.w - mean) * rstd;
+      *reinterpret_cast<float4*>(t.pool + op.aux + s * N + n) = xh;
+      x.x = xh.x * ga.x + be.x; x.y = xh.y * ga.y + be.y; x.z = xh.z * ga.z + be.z; x.w = xh.w * ga.w + be.w;
+      *reinterpret_cast<float4*>(t.pool + op.out + s * op.out_ld + n) = x;
+    } else {
+      const float xh = (t.pool[op.out + s * op.out_ld + n] - mean) * rstd;
+      t.pool[op.aux + s * N + n] = xh;
+      t.pool[op.out + s * op.out_ld + n] = xh * t.w[op.w + n] + t.w[op.b + n];
+    }
     if (n == 0) t.pool[op.aux2 + S * 2 * P + s] = rstd;
   }
 }
@@ -317,8 +417,12 @@ AFL_DEV void afl_ln_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
 
 AFL_DEV void afl_ln_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int N = op.N, S = t.S, P = AFL_LN_PARTS;
-  for (int it = tid; it < S * N; it += nt) {
-    const int s = it / N, n = it - s * N;
+  const bool v4 = (N & 3) == 0 && ((op.g_out | op.out_ld | op.aux | op.g_in0 | op.in0_ld | op.w) & 3) == 0 &&
+                  (op.in1 < 0 || ((op.g_in1 | op.in1_ld) & 3) == 0);
+  const int W = v4 ? 4 : 1;
+  const int NQ = N / W;
+  for (int it = tid; it < S * NQ; it += nt) {
+    const int s = it / NQ, n = (it - s * NQ) * W;
     float a = 0.f, b = 0.f;
 #pragma unroll
     for (int q = 0; q < P; ++q) {
@@ -326,11 +430,27 @@ AFL_DEV void afl_ln_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
       b += t.pool[op.aux2 + s * 2 * P + 2 * q + 1];
     }
     const float rstd = t.pool[op.aux2 + S * 2 * P + s];
-    const float dxh = t.pool[op.g_out + s * op.out_ld + n] * t.w[op.w + n];
-    const float dx = rstd * (dxh - a / (float)N - t.pool[op.aux + s * N + n] * (b / (float)N));
-    if (op.flags & AFL_F_NEED_GIN0) afl_store(t.pool + op.g_in0 + s * op.in0_ld + n, dx, op.flags & AFL_F_ACC0);
-    if (op.in1 >= 0)
-      afl_store(t.pool + op.g_in1 + s * op.in1_ld + n, dx * afl_drop_scale(t, op, s, (uint32_t)n), op.flags & AFL_F_ACC1);
+    const float m1 = a / (float)N, m2 = b / (float)N;
+    if (v4) {
+      const float4 g = *reinterpret_cast<const float4*>(t.pool + op.g_out + s * op.out_ld + n);
+      const float4 ga = *reinterpret_cast<const float4*>(t.w + op.w + n);
+      const float4 xh = *reinterpret_cast<const float4*>(t.pool + op.aux + s * N + n);
+      float4 dx;
+      dx.x = rstd * (g.x * ga.x - m1 - xh.x * m2); dx.y = rstd * (g.y * ga.y - m1 - xh.y * m2);
+      dx.z = rstd * (g.z * ga.z - m1 - xh.z * m2); dx.w = rstd * (g.w * ga.w - m1 - xh.w * m2);
+      if (op.flags & AFL_F_NEED_GIN0) afl_store4(t.pool + op.g_in0 + s * op.in0_ld + n, dx, op.flags & AFL_F_ACC0);
+      if (op.in1 >= 0) {
+        const float4 d = afl_drop_scale4(t, op, s, (uint32_t)n);
+        float4 r; r.x = dx.x * d.x; r.y = dx.y * d.y; r.z = dx.z * d.z; r.w = dx.w * d.w;
+        afl_store4(t.pool + op.g_in1 + s * op.in1_ld + n, r, op.flags & AFL_F_ACC1);
+      }
+    } else {
+      const float dxh = t.pool[op.g_out + s * op.out_ld + n] * t.w[op.w + n];
+      const float dx = rstd * (dxh - m1 - t.pool[op.aux + s * N + n] * m2);
+      if (op.flags & AFL_F_NEED_GIN0) afl_store(t.pool + op.g_in0 + s * op.in0_ld + n, dx, op.flags & AFL_F_ACC0);
+      if (op.in1 >= 0)
+        afl_store(t.pool + op.g_in1 + s * op.in1_ld + n, dx * afl_drop_scale(t, op, s, (uint32_t)n), op.flags & AFL_F_ACC1);
+    }
   }
 }
 
@@ -577,37 +697,65 @@ AFL_DEV void afl_conv_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) 
   else if (op.L == 16) afl_conv_bwd_b_t<16>(op, t, tid, nt);
 }
 
+// Ops of one *group* are mutually independent (e.g. the vitals and labs branches); the block's threads are split
+// evenly between them so both run in the same barrier interval.  op.grp_size is stored on the first op of a group,
+// op.grp_start on every op.  All ops of a group have the same kind (same phase structure).
+AFL_DEV void afl_fwd_phases(int kind, const AflOp& op, const AflTile& t, int tid, int nt, bool active) {
+  switch (kind) {
+    case AFL_OP_LOAD: if (active) afl_load_fwd(op, t, tid, nt); break;
+    case AFL_OP_LINEAR: if (active) afl_linear_fwd(op, t, tid, nt); break;
+    case AFL_OP_LN: if (active) afl_ln_fwd_a(op, t, tid, nt); AFL_SYNC(); if (active) afl_ln_fwd_b(op, t, tid, nt); break;
+    case AFL_OP_GRU: if (active) afl_gru_fwd(op, t, tid, nt); break;
+    case AFL_OP_CONV: if (active) afl_conv_fwd(op, t, tid, nt); break;
+    case AFL_OP_POOL: if (active) afl_pool_fwd(op, t, tid, nt); break;
+    case AFL_OP_DROPOUT: if (active) afl_dropout_fwd(op, t, tid, nt); break;
+    case AFL_OP_BCE: if (active) afl_bce(op, t, tid, nt); AFL_SYNC(); if (active) afl_bce_reduce(op, t, tid, nt); break;
+    default: break;
+  }
+}
+
+AFL_DEV void afl_bwd_phases(int kind, const AflOp& op, const AflTile& t, int tid, int nt, bool active) {
+  switch (kind) {
+    case AFL_OP_LINEAR: if (active) afl_linear_bwd_a(op, t, tid, nt); AFL_SYNC(); if (active) afl_linear_bwd_b(op, t, tid, nt); break;
+    case AFL_OP_LN: if (active) afl_ln_bwd_a(op, t, tid, nt); AFL_SYNC(); if (active) afl_ln_bwd_b(op, t, tid, nt); break;
+    case AFL_OP_GRU: if (active) afl_gru_bwd_a(op, t, tid, nt); AFL_SYNC(); if (active) afl_gru_bwd_b(op, t, tid, nt); break;
+    case AFL_OP_CONV: if (active) afl_conv_bwd_a(op, t, tid, nt); AFL_SYNC(); if (active) afl_conv_bwd_b(op, t, tid, nt); break;
+    case AFL_OP_POOL: if (active) afl_pool_bwd(op, t, tid, nt); break;
+    case AFL_OP_DROPOUT: if (active) afl_dropout_bwd(op, t, tid, nt); break;
+    default: break;   // LOAD / BCE have no backward work (BCE wrote dL/dlogit in forward)
+  }
+}
+
 AFL_DEV void afl_run_forward(const AflOp* ops, int n_ops, const AflTile& t, int tid, int nt) {
-  for (int i = 0; i < n_ops; ++i) {
-    const AflOp& op = ops[i];
-    switch (op.kind) {
-      case AFL_OP_LOAD: afl_load_fwd(op, t, tid, nt); break;
-      case AFL_OP_LINEAR: afl_linear_fwd(op, t, tid, nt); break;
-      case AFL_OP_LN: afl_ln_fwd_a(op, t, tid, nt); AFL_SYNC(); afl_ln_fwd_b(op, t, tid, nt); break;
-      case AFL_OP_GRU: afl_gru_fwd(op, t, tid, nt); break;
-      case AFL_OP_CONV: afl_conv_fwd(op, t, tid, nt); break;
-      case AFL_OP_POOL: afl_pool_fwd(op, t, tid, nt); break;
-      case AFL_OP_DROPOUT: afl_dropout_fwd(op, t, tid, nt); break;
-      case AFL_OP_BCE: afl_bce(op, t, tid, nt); AFL_SYNC(); afl_bce_reduce(op, t, tid, nt); break;
-      default: break;
+  for (int i = 0; i < n_ops;) {
+    const int g = ops[i].grp_size > 1 ? ops[i].grp_size : 1;
+    const int per = nt / g > 0 ? nt / g : 1;                 // threads per member (nt = 1 on the CPU twin)
+    if (nt >= g) {
+      const int sub = tid / per;
+      const bool active = sub < g;
+      afl_fwd_phases(ops[i].kind, ops[i + (active ? sub : 0)], t, tid - sub * per, per, active);
+    } else {
+      for (int j = 0; j < g; ++j) afl_fwd_phases(ops[i].kind, ops[i + j], t, tid, nt, true);
     }
     AFL_SYNC();
+    i += g;
   }
 }
 
 AFL_DEV void afl_run_backward(const AflOp* ops, int n_ops, const AflTile& t, int tid, int nt) {
-  for (int i = n_ops - 1; i >= 0; --i) {
-    const AflOp& op = ops[i];
-    switch (op.kind) {
-      case AFL_OP_LINEAR: afl_linear_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_linear_bwd_b(op, t, tid, nt); break;
-      case AFL_OP_LN: afl_ln_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_ln_bwd_b(op, t, tid, nt); break;
-      case AFL_OP_GRU: afl_gru_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_gru_bwd_b(op, t, tid, nt); break;
-      case AFL_OP_CONV: afl_conv_bwd_a(op, t, tid, nt); AFL_SYNC(); afl_conv_bwd_b(op, t, tid, nt); break;
-      case AFL_OP_POOL: afl_pool_bwd(op, t, tid, nt); break;
-      case AFL_OP_DROPOUT: afl_dropout_bwd(op, t, tid, nt); break;
-      default: break;   // LOAD / BCE have no backward work (BCE wrote dL/dlogit in forward)
+  for (int i = n_ops - 1; i >= 0;) {
+    const int st = ops[i].grp_start;
+    const int g = ops[st].grp_size > 1 ? ops[st].grp_size : 1;
+    const int per = nt / g > 0 ? nt / g : 1;
+    if (nt >= g) {
+      const int sub = tid / per;
+      const bool active = sub < g;
+      afl_bwd_phases(ops[st].kind, ops[st + (active ? sub : 0)], t, tid - sub * per, per, active);
+    } else {
+      for (int j = 0; j < g; ++j) afl_bwd_phases(ops[st].kind, ops[st + j], t, tid, nt, true);
     }
     AFL_SYNC();
+    i = st - 1;
   }
 }
 
@@ -623,31 +771,51 @@ struct AflOpt {
 // Reduce G partial rows over [lo, hi) and apply the update.  gpart: [G][d_pad].
 AFL_DEV void afl_reduce_update(float* w, float* m, float* v, const float* gpart, int G, int64_t d_pad,
                                int64_t lo, int64_t hi, const AflOpt& o, int tid, int nt) {
-  for (int64_t i = lo + tid; i < hi; i += nt) {
-    float g = 0.f;
-    for (int q = 0; q < G; ++q) g += gpart[(int64_t)q * d_pad + i];
-    g *= o.clip_coef;
-    if (o.kind == 0) {
-      const float mi = o.beta1 * m[i] + (1.f - o.beta1) * g;
-      const float vi = o.beta2 * v[i] + (1.f - o.beta2) * g * g;
-      m[i] = mi; v[i] = vi;
-      const float denom = sqrtf(vi) / sqrtf(o.bc2) + o.eps;
-      w[i] -= (o.lr / o.bc1) * (mi / denom);
-    } else {
-      const float b = o.first_step ? g : o.momentum * m[i] + g;
-      m[i] = b;
-      w[i] -= o.lr * b;
+  const float stepsz = o.lr / o.bc1, isq = 1.0f / sqrtf(o.bc2);
+  for (int64_t i = lo + 4 * (int64_t)tid; i < hi; i += 4 * (int64_t)nt) {
+    float4 g; g.x = g.y = g.z = g.w = 0.f;
+    int q = 0;
+    for (; q + 4 <= G; q += 4) {          // 4 independent 128-bit loads in flight
+      const float4 p0 = *reinterpret_cast<const float4*>(gpart + (int64_t)q * d_pad + i);
+      const float4 p1 = *reinterpret_cast<const float4*>(gpart + (int64_t)(q + 1) * d_pad + i);
+      const float4 p2 = *reinterpret_cast<const float4*>(gpart + (int64_t)(q + 2) * d_pad + i);
+      const float4 p3 = *reinterpret_cast<const float4*>(gpart + (int64_t)(q + 3) * d_pad + i);
+      g.x += (p0.x + p1.x) + (p2.x + p3.x); g.y += (p0.y + p1.y) + (p2.y + p3.y);
+      g.z += (p0.z + p1.z) + (p2.z + p3.z); g.w += (p0.w + p1.w) + (p2.w + p3.w);
     }
+    for (; q < G; ++q) {
+      const float4 p0 = *reinterpret_cast<const float4*>(gpart + (int64_t)q * d_pad + i);
+      g.x += p0.x; g.y += p0.y; g.z += p0.z; g.w += p0.w;
+    }
+    float4 mv = *reinterpret_cast<const float4*>(m + i);
+    float4 wv = *reinterpret_cast<const float4*>(w + i);
+    if (o.kind == 0) {
+      float4 vv = *reinterpret_cast<const float4*>(v + i);
+#define AFL_UPD(c) { const float gg = g.c * o.clip_coef; mv.c = o.beta1 * mv.c + (1.f - o.beta1) * gg; \
+        vv.c = o.beta2 * vv.c + (1.f - o.beta2) * gg * gg; wv.c -= stepsz * (mv.c / (sqrtf(vv.c) * isq + o.eps)); }
+      AFL_UPD(x) AFL_UPD(y) AFL_UPD(z) AFL_UPD(w)
+#undef AFL_UPD
+      *reinterpret_cast<float4*>(v + i) = vv;
+    } else {
+#define AFL_UPD(c) { const float gg = g.c * o.clip_coef; mv.c = o.first_step ? gg : o.momentum * mv.c + gg; wv.c -= o.lr * mv.c; }
+      AFL_UPD(x) AFL_UPD(y) AFL_UPD(z) AFL_UPD(w)
+#undef AFL_UPD
+    }
+    *reinterpret_cast<float4*>(m + i) = mv;
+    *reinterpret_cast<float4*>(w + i) = wv;
   }
 }
 
 // Sum of squares of the reduced gradient over [lo, hi) (for clip-mode "proper"); returns thread partial.
 AFL_DEV float afl_reduce_sqnorm(const float* gpart, int G, int64_t d_pad, int64_t lo, int64_t hi, int tid, int nt) {
   float acc = 0.f;
-  for (int64_t i = lo + tid; i < hi; i += nt) {
-    float g = 0.f;
-    for (int q = 0; q < G; ++q) g += gpart[(int64_t)q * d_pad + i];
-    acc += g * g;
+  for (int64_t i = lo + 4 * (int64_t)tid; i < hi; i += 4 * (int64_t)nt) {
+    float4 g; g.x = g.y = g.z = g.w = 0.f;
+    for (int q = 0; q < G; ++q) {
+      const float4 p0 = *reinterpret_cast<const float4*>(gpart + (int64_t)q * d_pad + i);
+      g.x += p0.x; g.y += p0.y; g.z += p0.z; g.w += p0.w;
+    }
+    acc += (g.x * g.x + g.y * g.y) + (g.z * g.z + g.w * g.w);
   }
   return acc;
 }

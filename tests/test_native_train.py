@@ -55,7 +55,7 @@ def _masks(prog, seed, client, step, S):
         p = torch.tensor([row[16]], dtype=torch.int32).view(torch.float32).item()
         if p > 0:
             out.append((row[17], p, row[0], row[15]))
-    return out
+    return sorted(out)          # rng ids follow the branch-sequential build order (vitals, labs, head)
 
 
 def _mask(seed, client, step, S, rng, p, n):
@@ -248,7 +248,7 @@ def test_infer_matches_module(device, name):
     m, lay = _setup(name, seed=8)
     m.eval()
     ds = synthetic_icu(133, 4)
-    prog = build_program(name, lay, S=32 if name != "CNNModel" else 8, train=False).to(device)
+    prog = build_program(name, lay, S={"TransformerModel": 32, "RNNModel": 16, "CNNModel": 8}[name], train=False).to(device)
     rows = torch.stack([lay.flatten(m.state_dict()), lay.flatten(models.build(name).state_dict())]).to(device)
     probs = T.infer(prog, rows, ds.packed().to(device)).cpu()
     with torch.no_grad():
