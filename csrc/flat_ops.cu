@@ -396,4 +396,80 @@ int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb
   return afl_rt::check_last("afl_hyper_step");
 }
 
+// ---- afl_hyper_step_noalloc: the same step for callers that must not allocate device memory ------------------
+// Who needs this: code that drives the hyper-network update from a place where cudaMalloc (or a framework
+// allocator such as torch's caching allocator) is off limits -- a real-time control loop that has pre-reserved
+// all device memory, a plugin running inside another runtime's memory budget, or a host callback / worker that
+// may not synchronise the device (cudaMalloc and cudaFree can).  afl_hyper_step already takes its scratch from
+// the caller; this variant owns it instead, in the file-scope array below, so the caller passes nothing but the
+// inputs and outputs.
+//
+// Limits (stated, checked, modest): d_pad <= 262144 floats, H <= 128, E <= 64 -> 263,563 floats = 1.006 MiB of
+// device memory, held by every GPU that loads this library until the process exits.  Larger problems are rejected
+// with an error; use afl_hyper_step with caller-provided scratch for them.
+//
+// Set-up: the array's name is only a host-side stand-in for the symbol, not a device address; on the first call
+// on each device (with that device current) the entry point asks the runtime for the real address with
+// cudaGetSymbolAddress and caches it per device.  Make that first call outside of any stream capture.
+//
+// Sharing: all calls use the same array and it keeps the previous call's contents.  The slots that must start at
+// zero (the |delta|^2 / W^T delta accumulators) are cleared on the stream at the start of every call; everything
+// else is fully overwritten before it is read.  Two calls that overlap on the GPU (different streams, no
+// dependency between them) race on the array: serialise them.
+#define AFL_HS_MAX_DPAD 262144
+#define AFL_HS_MAX_H 128
+#define AFL_HS_MAX_E 64
+#define AFL_HS_OFF_F (AFL_HS_MAX_DPAD)
+#define AFL_HS_OFF_ACTS (AFL_HS_OFF_F + AFL_HS_MAX_H)
+#define AFL_HS_OFF_RED (AFL_HS_OFF_ACTS + AFL_HS_MAX_E + 5 * AFL_HS_MAX_H)
+#define AFL_HS_FLOATS (AFL_HS_OFF_RED + AFL_HS_MAX_H + 3)
+
+static __device__ __align__(256) float g_hyper_step_scratch[AFL_HS_FLOATS];
+
+static float* g_hs_addr[64];          // per device: device address of g_hyper_step_scratch (0 = not resolved yet)
+
+static int hyper_step_scratch(float** out) {
+  int dev = 0;
+  AFL_CUDA(cudaGetDevice(&dev));
+  AFL_CHECK_ARG(dev >= 0 && dev < 64, "afl_hyper_step_noalloc: device ordinal out of range");
+  if (g_hs_addr[dev] == nullptr) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_hyper_step_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      afl_rt::set_error("afl_hyper_step_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                        cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -7;
+    }
+    g_hs_addr[dev] = p;
+  }
+  *out = g_hs_addr[dev];
+  return 0;
+}
+
+int afl_hyper_step_noalloc(float* head_w, float* head_b, float* mw, float* vw, float* mb, float* vb, float* small,
+                           int n_nodes, int E, int H, int client, const int* client_dev, const float* theta_client,
+                           int64_t d_pad, float lr, float b1, float b2, float eps, int step, float clip,
+                           float* coef_norm_out /* [2] device, nullable */, void* stream) {
+  if (d_pad > AFL_HS_MAX_DPAD || H > AFL_HS_MAX_H || E > AFL_HS_MAX_E || d_pad < 1 || H < 1 || E < 1) {
+    afl_rt::set_error("afl_hyper_step_noalloc: d_pad=%lld H=%d E=%d exceed the built-in scratch (d_pad <= %d, H <= %d, "
+                      "E <= %d); call afl_hyper_step with caller-provided scratch instead",
+                      (long long)d_pad, H, E, AFL_HS_MAX_DPAD, AFL_HS_MAX_H, AFL_HS_MAX_E);
+    return -1;
+  }
+  float* base = nullptr;
+  int rc = hyper_step_scratch(&base);
+  if (rc) return rc;
+  float* delta = base;
+  float* f = base + AFL_HS_OFF_F;
+  float* acts = base + AFL_HS_OFF_ACTS;
+  float* red = base + AFL_HS_OFF_RED;
+  rc = afl_hyper_step(head_w, head_b, mw, vw, mb, vb, small, n_nodes, E, H, client, client_dev, theta_client, delta, f,
+                      acts, red, d_pad, lr, b1, b2, eps, step, clip, stream);
+  if (rc) return rc;
+  if (coef_norm_out)
+    AFL_CUDA(cudaMemcpyAsync(coef_norm_out, red + 1 + H, 2 * sizeof(float), cudaMemcpyDeviceToDevice,
+                             (cudaStream_t)stream));
+  return 0;
+}
+
 }  // extern "C"

@@ -67,6 +67,20 @@ int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb
                    float* delta, float* f_scratch, float* acts, float* red, int64_t d_pad, float lr, float b1,
                    float b2, float eps, int step, float clip, void* stream);
 
+/* Allocation-free variant of afl_hyper_step (no counterpart in the reference: it exists for callers of THIS
+ * library that may not allocate device memory -- pre-reserved real-time loops, plugins inside another runtime's
+ * memory budget, host callbacks that must not trigger a device synchronisation).  Identical arithmetic and
+ * outputs; the scratch (delta, features, activations, reduction slots) lives in a file-scope device array inside
+ * the library: limits d_pad <= 262144, H <= 128, E <= 64 (1.006 MiB per GPU, held until process exit); larger sizes
+ * are rejected with an error.  The first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress) and should therefore be made before any stream capture.  All calls share the array:
+ * calls that overlap on the GPU race.  coef_norm_out (device, [2], nullable) receives {clip coefficient, pre-clip
+ * gradient norm}. */
+int afl_hyper_step_noalloc(float* head_w, float* head_b, float* mw, float* vw, float* mb, float* vb, float* small,
+                           int n_nodes, int E, int H, int client, const int* client_dev, const float* theta_client,
+                           int64_t d_pad, float lr, float b1, float b2, float eps, int step, float clip,
+                           float* coef_norm_out, void* stream);
+
 /* T1-T7 — local training of a chunk of clients for one round as ONE persistent kernel (client.py:75-111;
  * models src/Model.py:27-246).  ops: int32 program [n_ops][32] (attackfl_b200/models/programs.py);
  * w,m,v [C][d_pad]; gpart [C][G][d_pad]; data [rows][rec]; idx [C][epochs][>=n] int32; G blocks per client,
