@@ -86,7 +86,9 @@ class Federation:
         self.py_rng = random.Random(s.random_seed)            # server.py:96-97
         self.client_rng = [random.Random((s.random_seed or 0) * 7919 + 13 * c + 1) for c in range(self.C)]
         self.torch_gen = torch.Generator(device="cpu").manual_seed(int(s.random_seed or 0) + 1234)
-        self.dev_gen = torch.Generator(device=self.device).manual_seed(int(s.random_seed or 0) + 4321)
+        # per-rank stream for the clients' private data sampling (clients on different ranks must not draw
+        # the same subsets); everything that decides control flow uses the rank-independent generators above
+        self.dev_gen = torch.Generator(device=self.device).manual_seed(int(s.random_seed or 0) + 4321 + 7919 * ctx.rank)
 
         # ---- model, layout, programs
         torch.manual_seed(int(s.random_seed or 0))

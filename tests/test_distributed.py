@@ -1,0 +1,47 @@
+"""SPMD engine under torch.distributed: gloo / world_size 2 on CPU here, NCCL + fused P2P kernels on GPUs."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _launch(tmp_path, world, mode, attack="", env_extra=None, timeout=600):
+    out = str(tmp_path / "res")
+    port = 29600 + (os.getpid() % 300)
+    env = dict(os.environ, PYTHONPATH=ROOT, ATTACKFL_QUIET="1")
+    env.update(env_extra or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "dist_worker.py"), out, mode, attack]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return [json.load(open(f"{out}.rank{k}.json")) for k in range(world)]
+
+
+@pytest.mark.parametrize("mode,attack", [("fedavg", "LIE"), ("fedavg", "Min-Max"), ("hyper", ""), ("median", "Random")])
+def test_two_ranks_gloo_agree(tmp_path, mode, attack):
+    recs = _launch(tmp_path, 2, mode, attack)
+    a, b = recs
+    assert a["world"] == 2 and a["local"] == [0, 1, 2] and b["local"] == [3, 4, 5]
+    assert a["ok"] == b["ok"] == [True, True]
+    assert a["checksum"] == pytest.approx(b["checksum"], rel=1e-6)          # replicated state stays in sync
+    assert a["metric"] == pytest.approx(b["metric"], rel=1e-6)
+    if attack:
+        assert a["attackers"][1] == [5]
+    assert a["metric"][-1] > (0.6 if mode != "hyper" else 0.45)      # the hyper-network needs more rounds to learn
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("collectives", ["nccl", "fused"])
+def test_two_gpus(tmp_path, collectives):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    recs = _launch(tmp_path, 2, "fedavg", "LIE", {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives})
+    a, b = recs
+    assert a["ok"] == b["ok"] == [True, True]
+    assert a["checksum"] == pytest.approx(b["checksum"], rel=1e-5)
+    assert a["fused"] == (collectives == "fused")
