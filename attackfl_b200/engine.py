@@ -330,7 +330,8 @@ class Federation:
         return loss_out
 
     # ================================================================================== attacks
-    def _prepare_crafts(self, rows_all: torch.Tensor, genuine: List[int], center: Optional[torch.Tensor]) -> Dict:
+    def _prepare_crafts(self, rows_all: Optional[torch.Tensor], genuine: List[int], center: Optional[torch.Tensor],
+                        defer_lie: bool = False) -> Dict:
         """End of round r: every attacker samples its subset of this round's genuine updates
         (``random.sample(..., max(int(rate*n),1))``, server.py:596-600) and its round-(r+1) row is crafted
         now, from the rows still in the arena (SURVEY §7.1 decision 2)."""
@@ -343,7 +344,15 @@ class Federation:
         a_cfg = self.cfg.attack
         native = self.backend == "native"
         lie = [sp for sp in attackers if sp.attack_mode == "LIE"]
-        if lie:
+        if lie and defer_lie:
+            # fused multi-GPU path: the moments are computed inside the K1-fused pass over peer memory
+            member = torch.zeros(len(lie), self.C)
+            for q, sp in enumerate(lie):
+                member[q, subsets[sp.index]] = 1.0
+            info["_lie_specs"] = lie
+            info["_lie_member"] = member
+            info["_lie_z"] = torch.tensor([float((sp.attack_args or [0.74])[0]) for sp in lie])
+        elif lie:
             if native:
                 from .ops import flat
                 member = torch.zeros(len(lie), rows_all.shape[0])
@@ -486,6 +495,23 @@ class Federation:
         self.have_global = True
         return info
 
+    def _aggregate_fused(self, reporting: List[int], center: Optional[torch.Tensor], info: Dict[str, object]) -> None:
+        """FedAvg + LIE moments + broadcast in one kernel per rank over NVLink peer memory (csrc/comm.cu)."""
+        w = torch.zeros(self.C, dtype=torch.float32)
+        for c in reporting:
+            w[c] = float(self.sizes[c])
+        w = w / w.sum()
+        lie_specs = info.pop("_lie_specs", None)
+        member, z = info.pop("_lie_member", None), info.pop("_lie_z", None)
+        ref = center if center is not None else self.init_row
+        rows = self.fused_comm.fedavg(w, member, z, ref.contiguous(), self.cfg.attack.strict_reference)
+        if lie_specs:
+            for q, sp in enumerate(lie_specs):
+                self.crafted[sp.index] = rows[q]
+                self.crafted_own[sp.index] = False
+        self.have_global = True
+        self._rows_hold_global = True
+
     def _fltrust_server_update(self) -> None:
         """Server trains on the root set: first 200 test samples, batch 100, no shuffle (server.py:289-294,711)."""
         s, l = self.cfg.server, self.cfg.learning
@@ -627,8 +653,12 @@ class Federation:
             self.ctx.all_reduce_sum(flags)
         reporting = list(starting)
         info: Dict[str, object] = {}
-        with self.timer.phase("gather"):
-            rows_all = self._all_rows()
+        fused = self.fused_comm is not None and self.mode == "fedavg"
+        need_gather = (not fused) or any(sp.attack and sp.attack_mode in GRAM_MODES for sp in self.specs)
+        rows_all = None
+        if need_gather:
+            with self.timer.phase("gather"):
+                rows_all = self._all_rows()
         flags_h = flags.cpu()                                     # D2H: 3 floats per client
         ok = bool((flags_h[:, 0] == 0).all()) and bool(torch.isfinite(flags_h[:, 1]).all())
         losses = [float(flags_h[c, 1] / max(float(flags_h[c, 2]) * l.epoch, 1.0)) for c in range(self.C)]
@@ -637,10 +667,12 @@ class Federation:
             genuine = [c for c in reporting if not self.specs[c].attack]
             center = self.global_row.clone() if (self.have_global and self.mode != "hyper") else None
             with self.timer.phase("craft"):
-                info.update(self._prepare_crafts(rows_all, genuine, center))
+                info.update(self._prepare_crafts(rows_all, genuine, center, defer_lie=fused))
             self.genuine_prev = genuine
             with self.timer.phase("aggregate"):
-                if self.mode == "hyper":
+                if fused:
+                    self._aggregate_fused(reporting, center, info)
+                elif self.mode == "hyper":
                     info.update(self._hyper_round(rows_all, reporting))
                 else:
                     info.update(self._aggregate(rows_all, reporting))

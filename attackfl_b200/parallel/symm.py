@@ -1,0 +1,109 @@
+"""Symmetric-memory runtime and the fused multi-GPU round end (K1-fused, ``csrc/comm.cu``).
+
+Replaces the reference's broker traffic (every UPDATE and every START is a pickled ``state_dict`` through
+RabbitMQ: ``/root/reference/src/RpcClient.py:111-114``, ``server.py:588-614``) and the NCCL fall-back path
+(all-gather of the client rows + replicated aggregation) with one kernel per rank that reads the client rows *in
+place* over NVLink and writes the new global model into every rank.
+
+``attach(fed)`` moves the engine's client rows, global model and LIE buffer into
+``torch.distributed._symmetric_memory`` tensors (peer-mapped on every rank; PyTorch/NCCL only exchange the
+handles), builds the pointer tables and installs ``fed.fused_comm``.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native
+from ..ops.native import check, ptr, stream_ptr
+
+MAX_ATT = 4
+
+
+class FusedComm:
+    def __init__(self, fed):
+        import torch.distributed._symmetric_memory as symm_mem
+        ctx = fed.ctx
+        assert ctx.distributed and fed.device.type == "cuda"
+        self.fed, self.world, self.rank = fed, ctx.world, ctx.rank
+        dev = fed.device
+        group = dist.group.WORLD
+        self.cpg = ctx.clients_per_rank(fed.C)
+        D = fed.D
+        self.n_lie = max(1, sum(1 for sp in fed.specs if sp.attack and sp.attack_mode == "LIE"))
+        self.rows = symm_mem.empty(self.cpg, D, dtype=torch.float32, device=dev)
+        self.glob = symm_mem.empty(D, dtype=torch.float32, device=dev)
+        self.lie = symm_mem.empty(self.n_lie, D, dtype=torch.float32, device=dev)
+        self.sig = symm_mem.empty(64, dtype=torch.int32, device=dev)
+        self.rows.zero_(); self.lie.zero_(); self.sig.zero_()
+        self.rows[:fed.CL].copy_(fed.rows[:fed.CL])
+        self.glob.copy_(fed.global_row)
+        self.h_rows = symm_mem.rendezvous(self.rows, group)
+        self.h_glob = symm_mem.rendezvous(self.glob, group)
+        self.h_lie = symm_mem.rendezvous(self.lie, group)
+        self.h_sig = symm_mem.rendezvous(self.sig, group)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        # the engine now works directly on the symmetric tensors
+        fed.rows = self.rows
+        fed.global_row = self.glob
+        # pointer tables
+        row_ptrs = []
+        for c in range(fed.C):
+            r = c // self.cpg
+            row_ptrs.append(int(self.h_rows.buffer_ptrs[r]) + (c - r * self.cpg) * D * 4)
+        self.row_ptrs = torch.tensor(row_ptrs, dtype=torch.int64, device=dev)
+        PtrArr = ctypes.c_void_p * self.world
+        self.glob_ptrs = PtrArr(*[int(p) for p in self.h_glob.buffer_ptrs])
+        self.lie_ptrs = PtrArr(*[int(p) for p in self.h_lie.buffer_ptrs])
+        self.sig_ptrs = PtrArr(*[int(p) for p in self.h_sig.buffer_ptrs])
+        self.ctrl = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.epoch = 0
+        self.multicast = bool(getattr(self.h_glob, "multicast_ptr", 0))
+
+    def fedavg(self, weights: torch.Tensor, member: Optional[torch.Tensor] = None, z: Optional[torch.Tensor] = None,
+               ref: Optional[torch.Tensor] = None, strict_k1: bool = False) -> Optional[torch.Tensor]:
+        """Weighted FedAvg over all ranks' rows -> ``fed.global_row`` on every rank and every local client row;
+        returns the LIE rows ``[A, D_pad]`` (clone) when ``member`` is given."""
+        fed = self.fed
+        dev = fed.device
+        lib = native.cuda_lib()
+        A = 0 if member is None else member.shape[0]
+        assert A <= self.n_lie
+        weights = weights.to(device=dev, dtype=torch.float32).contiguous()
+        out = None
+        passes = [(0, 0)] if A == 0 else [(a0, min(A, a0 + MAX_ATT)) for a0 in range(0, A, MAX_ATT)]
+        for pi, (a0, a1) in enumerate(passes):
+            self.epoch += 1
+            n = a1 - a0
+            if n:
+                mem = member[a0:a1].to(device=dev, dtype=torch.float32).contiguous()
+                kc = mem.sum(1).contiguous()
+                zz = z[a0:a1].to(device=dev, dtype=torch.float32).contiguous()
+                lie_ptrs = (ctypes.c_void_p * self.world)(*[int(p) + a0 * fed.D * 4 for p in self.h_lie.buffer_ptrs])
+            else:
+                mem = kc = zz = None
+                lie_ptrs = None
+            rc = lib.afl_fedavg_fused(
+                ptr(self.row_ptrs), ptr(weights), ctypes.c_int(fed.C), ctypes.c_int64(fed.D), ctypes.c_int(self.world),
+                ctypes.c_int(self.rank), self.glob_ptrs, lie_ptrs, self.sig_ptrs, ctypes.c_uint32(self.epoch),
+                ctypes.c_int(n), ptr(ref), ptr(mem), ptr(kc), ptr(zz), ctypes.c_int(1 if strict_k1 else 0),
+                ptr(self.rows) if pi == len(passes) - 1 else ctypes.c_void_p(0), ctypes.c_int(fed.CL), ptr(self.ctrl),
+                stream_ptr(self.rows))
+            check(lib, rc, "afl_fedavg_fused")
+        if A:
+            out = self.lie[:A].clone()
+        return out
+
+    def check_error(self) -> None:
+        if int(self.ctrl[2].item()) != 0:
+            raise RuntimeError("fused collective timed out waiting for a peer rank")
+
+
+def attach(fed) -> FusedComm:
+    fc = FusedComm(fed)
+    fed.fused_comm = fc
+    return fc
