@@ -107,8 +107,6 @@ class Federation:
         if backend == "native":
             from .ops import train as T
             self.T = T
-            self.train_prog = build_program(self.model_name, self.layout, train=True, dropout=l.dropout,
-                                            module=self.module).to(self.device)
             for s_inf in (32, 16, 8, 4):                  # largest inference tile whose pool fits in shared memory
                 prog = build_program(self.model_name, self.layout, S=s_inf, train=False, module=self.module)
                 if prog.smem_bytes() <= 200 * 1024:
@@ -143,8 +141,9 @@ class Federation:
         self.plan = None
         self.gpart = None
         if backend == "native":
-            self.plan = self.T.make_plan(self.train_prog, l.batch_size, max(self.CL, 1), self.D, self.device,
-                                         cfg.runtime.cta_per_client)
+            self.train_prog, self.plan = self.T.plan_for(self.model_name, self.layout, l.batch_size, max(self.CL, 1),
+                                                         self.device, dropout=l.dropout, module=self.module,
+                                                         blocks_per_client=cfg.runtime.cta_per_client)
             self.gpart = z(self.plan.chunk * self.plan.G, self.D)
 
         # ---- coordinator state (server.py:105-134)
@@ -523,6 +522,7 @@ class Federation:
         if self.backend == "native":
             T = self.T
             plan = T.make_plan(self.train_prog, s.fltrust_root_batch, 1, self.D, self.device)
+            plan.chunk = 1
             gp = torch.zeros(plan.chunk * plan.G, self.D, device=self.device)
             w = self.server_row[None].contiguous()
             m, v = torch.zeros_like(w), torch.zeros_like(w)

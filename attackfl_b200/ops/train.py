@@ -62,6 +62,28 @@ def make_plan(program: Program, batch: int, n_clients: int, d_pad: int, device, 
     return TrainPlan(G, M, S, chunk)
 
 
+TILE_CANDIDATES = {"TransformerModel": (8, 16), "RNNModel": (8, 16), "CNNModel": (4,)}
+
+
+def plan_for(model_name: str, layout, batch: int, n_clients: int, device, *, dropout: bool = True, module=None,
+             blocks_per_client: int = 0):
+    """Build the training program with the tile size that lets every tile of a batch run on its own block
+    (measured on B200: S=8 -> 16 blocks/client is 21-29 % faster than S=16 -> 8 blocks when 128 SMs are free);
+    fall back to larger tiles / several tiles per block when the rank hosts many clients."""
+    from ..models.programs import build_program
+    best = None
+    for S in TILE_CANDIDATES.get(model_name, (16,)):
+        prog = build_program(model_name, layout, S=S, train=True, dropout=dropout, module=module).to(device)
+        plan = make_plan(prog, batch, n_clients, layout.padded, device, blocks_per_client)
+        if best is None:
+            best = (prog, plan)
+        if plan.M == 1 and plan.chunk >= n_clients:
+            return prog, plan
+        if plan.M * plan.S < best[1].M * best[1].S or (plan.chunk >= n_clients > best[1].chunk):
+            best = (prog, plan)
+    return best
+
+
 def train_round(program: Program, plan: TrainPlan, w: torch.Tensor, m: torch.Tensor, v: Optional[torch.Tensor],
                 gpart: torch.Tensor, data: torch.Tensor, idx: torch.Tensor, n_data: torch.Tensor,
                 client_ids: torch.Tensor, batch: int, epochs: int, *, optimizer: str = "adam", lr: float = 0.004,

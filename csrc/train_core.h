@@ -130,13 +130,13 @@ AFL_DEV void afl_load_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
 
 // Weight row chunk of 4*Q floats is loaded into registers first (Q independent 128-bit loads in flight => one
 // L2 latency per chunk instead of one per 4 k), then swept over the thread's AFL_TS samples from shared memory.
-template <int Q>
+template <int Q, int TS>
 AFL_DEV void afl_lin_chunk(const float* wr, const float* x0, int ldx, int ns, float* acc) {
   float4 wv[Q];
 #pragma unroll
   for (int q = 0; q < Q; ++q) wv[q] = *reinterpret_cast<const float4*>(wr + 4 * q);
 #pragma unroll
-  for (int j = 0; j < AFL_TS; ++j) {
+  for (int j = 0; j < TS; ++j) {
     if (j < ns) {
       float a = acc[j];
 #pragma unroll
@@ -149,25 +149,26 @@ AFL_DEV void afl_lin_chunk(const float* wr, const float* x0, int ldx, int ns, fl
   }
 }
 
-AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+template <int TS>
+AFL_DEV void afl_linear_fwd_t(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int N = op.N, K = op.K, S = t.S;
-  const int SG = (S + AFL_TS - 1) / AFL_TS;
+  const int SG = (S + TS - 1) / TS;
   const bool vec = (K & 3) == 0 && (op.in0_ld & 3) == 0 && (op.in0 & 3) == 0 && (op.w & 3) == 0;
   for (int it = tid; it < N * SG; it += nt) {
     const int n = it % N, sg = it / N;
-    const int s0 = sg * AFL_TS;
-    const int ns = AFL_MIN(AFL_TS, S - s0);
+    const int s0 = sg * TS;
+    const int ns = AFL_MIN(TS, S - s0);
     const float* wr = t.w + op.w + (int64_t)n * K;
     const float* x0 = t.pool + op.in0 + s0 * op.in0_ld;
     const float bias = op.b >= 0 ? t.w[op.b + n] : 0.f;      // issued early: overlaps the weight loads
-    float acc[AFL_TS];
+    float acc[TS];
 #pragma unroll
-    for (int j = 0; j < AFL_TS; ++j) acc[j] = 0.f;
+    for (int j = 0; j < TS; ++j) acc[j] = 0.f;
     if (vec) {
       int k = 0;
-      for (; k + 64 <= K; k += 64) afl_lin_chunk<16>(wr + k, x0 + k, op.in0_ld, ns, acc);
-      for (; k + 16 <= K; k += 16) afl_lin_chunk<4>(wr + k, x0 + k, op.in0_ld, ns, acc);
-      for (; k + 4 <= K; k += 4) afl_lin_chunk<1>(wr + k, x0 + k, op.in0_ld, ns, acc);
+      for (; k + 64 <= K; k += 64) afl_lin_chunk<16, TS>(wr + k, x0 + k, op.in0_ld, ns, acc);
+      for (; k + 16 <= K; k += 16) afl_lin_chunk<4, TS>(wr + k, x0 + k, op.in0_ld, ns, acc);
+      for (; k + 4 <= K; k += 4) afl_lin_chunk<1, TS>(wr + k, x0 + k, op.in0_ld, ns, acc);
     } else {
       float wv[8];
       for (int k0 = 0; k0 < K; k0 += 8) {
@@ -175,7 +176,7 @@ AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) 
 #pragma unroll
         for (int q = 0; q < 8; ++q) wv[q] = q < kn ? wr[k0 + q] : 0.f;
 #pragma unroll
-        for (int j = 0; j < AFL_TS; ++j)
+        for (int j = 0; j < TS; ++j)
           if (j < ns)
 #pragma unroll
             for (int q = 0; q < 8; ++q)
@@ -183,7 +184,7 @@ AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) 
       }
     }
 #pragma unroll
-    for (int j = 0; j < AFL_TS; ++j) {
+    for (int j = 0; j < TS; ++j) {
       const int s = s0 + j;
       if (j >= ns) break;
       const float z = acc[j] + bias;
@@ -193,6 +194,11 @@ AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) 
       t.pool[op.out + s * op.out_ld + n] = y;
     }
   }
+}
+
+AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
+  // small tiles: 2 samples per thread so that every thread of the block has an item
+  if (t.S >= 16) afl_linear_fwd_t<4>(op, t, tid, nt); else afl_linear_fwd_t<2>(op, t, tid, nt);
 }
 
 // Phase A: turn dL/dout into dL/dz in place (dropout mask, activation derivative).
@@ -214,13 +220,14 @@ AFL_DEV void afl_linear_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt
 }
 
 // Phase B: dX, dW, db from dz (three independent item ranges, one flat loop).
-AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+template <int TS>
+AFL_DEV void afl_linear_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int N = op.N, K = op.K, S = t.S;
   const float* dz = t.pool + op.g_out;        // [S][.], row stride = out_ld (same layout as out)
   const int ldz = op.out_ld;
   const float* x = t.pool + op.in0;
   const int ldx = op.in0_ld;
-  const int SG = (S + AFL_TS - 1) / AFL_TS;
+  const int SG = (S + TS - 1) / TS;
   const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
   const int n_dx = need_dx ? K * SG : 0;
   const bool nvec = (N & 3) == 0 && (op.g_out & 3) == 0 && (ldz & 3) == 0;
@@ -233,12 +240,12 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
   for (int it = tid; it < total; it += nt) {
     if (it < n_dx) {
       // dX[s][k] = sum_n dz[s][n] W[n][k]; lanes walk k => coalesced W reads; 16 W values preloaded per pass
-      const int k = it % K, sg = it / K, s0 = sg * AFL_TS;
-      const int ns = AFL_MIN(AFL_TS, S - s0);
+      const int k = it % K, sg = it / K, s0 = sg * TS;
+      const int ns = AFL_MIN(TS, S - s0);
       const float* wc = t.w + op.w + k;
-      float acc[AFL_TS];
+      float acc[TS];
 #pragma unroll
-      for (int j = 0; j < AFL_TS; ++j) acc[j] = 0.f;
+      for (int j = 0; j < TS; ++j) acc[j] = 0.f;
       int n = 0;
       if (nvec) {
         for (; n + 16 <= N; n += 16) {
@@ -246,7 +253,7 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
 #pragma unroll
           for (int q = 0; q < 16; ++q) wv[q] = wc[(int64_t)(n + q) * K];
 #pragma unroll
-          for (int j = 0; j < AFL_TS; ++j) {
+          for (int j = 0; j < TS; ++j) {
             if (j < ns) {
               float a = acc[j];
 #pragma unroll
@@ -262,11 +269,11 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
       for (; n < N; ++n) {
         const float wv = wc[(int64_t)n * K];
 #pragma unroll
-        for (int j = 0; j < AFL_TS; ++j)
+        for (int j = 0; j < TS; ++j)
           if (j < ns) acc[j] += dz[(s0 + j) * ldz + n] * wv;
       }
 #pragma unroll
-      for (int j = 0; j < AFL_TS; ++j)
+      for (int j = 0; j < TS; ++j)
         if (j < ns) afl_store(t.pool + op.g_in0 + (s0 + j) * ldx + k, acc[j], op.flags & AFL_F_ACC0);
     } else if (it < n_dx + n_dw) {
       const int j2 = it - n_dx;
@@ -314,6 +321,10 @@ AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt
       afl_store(t.gw + op.b + n, a, t.accumulate);
     }
   }
+}
+
+AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
+  if (t.S >= 16) afl_linear_bwd_b_t<4>(op, t, tid, nt); else afl_linear_bwd_b_t<2>(op, t, tid, nt);
 }
 
 // ----------------------------------------------------------------------------------------- LAYERNORM
