@@ -81,7 +81,7 @@ class AttackCfg:
     metric: str = "flat"             # flat | layer-fro | reference   
     search: str = "reference"        # reference (last tried gamma) | paper (gamma_succ)
     strict_reference: bool = False   # Q9: True reproduces LIE NaN at k=1
-    gram_precision: str = "bf16"     # bf16 | bf16x3 (hi/lo split) | fp32
+    gram_precision: str = "tf32"     # tf32 (fp32 rows as TF32 operands, no cast pass) | bf16 | bf16x3 | fp32
 
 
 @dataclass

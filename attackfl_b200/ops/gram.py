@@ -18,7 +18,7 @@ def gram_torch(a: torch.Tensor) -> torch.Tensor:
     return a @ a.t()
 
 
-def gram(a: torch.Tensor, precision: str = "bf16") -> torch.Tensor:
+def gram(a: torch.Tensor, precision: str = "tf32") -> torch.Tensor:
     if a.is_cuda and precision != "fp32":
         from . import gram_native
         if gram_native.available():

@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(kThreads) hyper_features_kernel(HyperSmall s, 
   extern __shared__ float sm[];
   float* x = sm; float* y = sm + s.H;
   const int E = s.E, H = s.H;
-  for (int q = 0; q < n; ++q) {
+  for (int q = blockIdx.x; q < n; q += gridDim.x) {        // one block per client
     const int c = clients[q];
     __syncthreads();
     for (int i = threadIdx.x; i < E; i += kThreads) { x[i] = s.params[c * E + i]; if (n == 1) s.acts[i] = x[i]; }
@@ -233,12 +233,19 @@ __global__ void __launch_bounds__(kThreads) hyper_small_step_kernel(HyperSmall s
   }
   for (int i = threadIdx.x; i < E; i += kThreads) grads[s.client * E + i] = g[i];
   __syncthreads();
+  __shared__ double s_part[kThreads];
+  {
+    double acc = 0.0;                                    // block-parallel |grad small|^2
+    for (int i = threadIdx.x; i < total; i += kThreads) acc += (double)grads[i] * grads[i];
+    s_part[threadIdx.x] = acc;
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
     // |grad|^2 = |delta|^2 (|f|^2 + 1) + |grad small|^2   (rank-1 head gradient)
     const float* f = s.acts + E + 4 * H;
     double f2 = 0.0, small2 = 0.0;
     for (int i = 0; i < H; ++i) f2 += (double)f[i] * f[i];
-    for (int i = 0; i < total; ++i) small2 += (double)grads[i] * grads[i];
+    for (int i = 0; i < kThreads; ++i) small2 += s_part[i];
     const double n2 = (double)s.red[0] * (f2 + 1.0) + small2;
     const float norm = (float)sqrt(n2);
     float coef = 1.f;
@@ -359,7 +366,7 @@ int afl_hyper_emit(const float* head_w, const float* head_b, float* small, int n
   const size_t tot = hyper_small_total(n_nodes, E, H);
   HyperSmall s{small, small + tot, small + 2 * tot, n_nodes, E, H, acts, nullptr, nullptr, nullptr, 0,
                0, 0, 0, 0, 1, 1, 0};
-  hyper_features_kernel<<<1, kThreads, sizeof(float) * 2 * (size_t)AFL_MAX(H, E), st>>>(s, clients_dev, n, f_scratch);
+  hyper_features_kernel<<<n, kThreads, sizeof(float) * 2 * (size_t)AFL_MAX(H, E), st>>>(s, clients_dev, n, f_scratch);
   afl_rt::count_launch();
   const size_t smem = sizeof(float) * ((size_t)n * H + (size_t)kTR * (H + 1));
   AFL_CHECK_ARG(smem <= 200 * 1024, "afl_hyper_emit: too many clients per call for shared memory (chunk them)");

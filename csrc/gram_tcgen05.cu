@@ -70,8 +70,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format[4,6)=1 (F32), a_format[7,10)=1 (BF16),
 // b_format[10,13)=1 (BF16), a_major[15]=0, b_major[16]=0 (K-major), n_dim[17,23)=N>>3, m_dim[24,29)=M>>4.
-__device__ __forceinline__ uint32_t make_idesc(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+__device__ __forceinline__ uint32_t make_idesc(int M, int N, uint32_t fmt /* 1 = BF16, 2 = TF32 */) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
@@ -83,6 +83,15 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
 }
 
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -91,7 +100,9 @@ struct GramParams {
   int rows_box;          // 128 or 256: rows of the TMA box / smem tile
   int n_cols;            // UMMA N (multiple of 16, >= 16): padded number of Gram rows
   int m_tiles;           // 1 or 2
-  int n_kblocks;         // total 64-wide K blocks
+  int n_kblocks;         // total 128-byte-wide K blocks (64 bf16 or 32 tf32 elements)
+  int kblock_elems;      // 64 (bf16) or 32 (tf32)
+  int tf32;              // 1: fp32 rows read as tf32 operands (kind::tf32, K = 8 per MMA)
   int stages;
   float* partials;       // [gridDim.x][m_tiles*128][n_cols]
 };
@@ -140,13 +151,13 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramParams P) {
         const uint32_t ph = (uint32_t)(i / P.stages) & 1u;
         mbar_wait(empty + st, ph ^ 1u);
         mbar_expect_tx(full + st, (uint32_t)tile_bytes);
-        tma_load_2d(tiles + (size_t)st * tile_bytes, &tmap, (kb0 + i) * kBlockK, 0, full + st);
+        tma_load_2d(tiles + (size_t)st * tile_bytes, &tmap, (kb0 + i) * P.kblock_elems, 0, full + st);
       }
     }
   } else if (warp == 1) {
     if (lane == 0 && nkb > 0) {
       // ===== MMA issuer (single thread) =====
-      const uint32_t idesc = make_idesc(128, P.n_cols);
+      const uint32_t idesc = make_idesc(128, P.n_cols, P.tf32 ? 2u : 1u);
       for (int i = 0; i < nkb; ++i) {
         const int st = i % P.stages;
         const uint32_t ph = (uint32_t)(i / P.stages) & 1u;
@@ -159,7 +170,9 @@ gram_kernel(const __grid_constant__ CUtensorMap tmap, GramParams P) {
             // advance 32 bytes (16 bf16) along K inside the 128B swizzle row: +2 in the (addr>>4) field
             const uint64_t adesc = make_desc(tile_addr + (uint32_t)(mt * 128 * 128) + (uint32_t)(k * 32));
             const uint64_t bdesc = make_desc(tile_addr + (uint32_t)(k * 32));
-            umma_bf16(tmem_base + (uint32_t)(mt * P.n_cols), adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            // 32 bytes per MMA along K in both modes: 16 bf16 (kind::f16) or 8 tf32 (kind::tf32)
+            if (P.tf32) umma_tf32(tmem_base + (uint32_t)(mt * P.n_cols), adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            else umma_bf16(tmem_base + (uint32_t)(mt * P.n_cols), adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
         }
         umma_commit(empty + st);            // frees the smem stage when these MMAs retire
@@ -243,30 +256,34 @@ EncodeFn get_encode() {
   return fn;
 }
 
-int make_tmap(CUtensorMap* map, const void* base, int rows_box, int64_t Dp) {
+// bf16: operand copy [rows_box][Dp] (zero padded).  fp32/tf32: the caller's matrix itself, [R][D] with row stride lda;
+// rows >= R and columns >= D of a box are zero-filled by TMA (out-of-bounds fill), so no padded copy is needed.
+int make_tmap(CUtensorMap* map, const void* base, int rows_box, int64_t cols, int64_t rows, int64_t ld_elems, bool f32) {
   EncodeFn enc = get_encode();
   if (!enc) { afl_rt::set_error("cuTensorMapEncodeTiled not available"); return -5; }
-  cuuint64_t dims[2] = {(cuuint64_t)Dp, (cuuint64_t)rows_box};
-  cuuint64_t strides[1] = {(cuuint64_t)Dp * 2};
-  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)rows_box};
+  const int esz = f32 ? 4 : 2;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld_elems * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)rows_box};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { afl_rt::set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return -6; }
   return 0;
 }
 
-struct Geometry { int rows_box, n_cols, m_tiles, stages, grid; int64_t Dp; size_t smem, partial_floats; };
+struct Geometry { int rows_box, n_cols, m_tiles, stages, grid, kelems; int64_t Dp; size_t smem, partial_floats; };
 
-int geometry(int R, int64_t D, Geometry* g) {
+int geometry(int R, int64_t D, Geometry* g, int kelems = kBlockK) {
   if (R < 1 || R > kMaxRows) { afl_rt::set_error("gram: 1 <= R <= 256 required (got %d)", R); return -1; }
   g->rows_box = R <= 128 ? 128 : 256;
   g->m_tiles = g->rows_box / 128;
   g->n_cols = ((R + 15) / 16) * 16;
-  g->Dp = ((D + kBlockK - 1) / kBlockK) * kBlockK;
+  g->kelems = kelems;
+  g->Dp = ((D + kelems - 1) / kelems) * kelems;
   g->stages = g->rows_box == 128 ? 8 : 4;
-  const int nkb = (int)(g->Dp / kBlockK);
+  const int nkb = (int)(g->Dp / kelems);
   const int sms = afl_rt::num_sms();
   g->grid = nkb < sms ? nkb : sms;
   g->smem = 1024 + (size_t)g->stages * g->rows_box * 128 + (2 * g->stages + 1) * 8 + 16;
@@ -274,14 +291,13 @@ int geometry(int R, int64_t D, Geometry* g) {
   return 0;
 }
 
-int launch_gram(const __nv_bfloat16* a16, const __nv_bfloat16* b16_unused, const Geometry& g, float* partials,
+int launch_gram(const void* base, int64_t cols, int64_t rows, int64_t ld, bool f32, const Geometry& g, float* partials,
                 cudaStream_t st) {
-  (void)b16_unused;
   CUtensorMap map;
-  int rc = make_tmap(&map, a16, g.rows_box, g.Dp);
+  int rc = make_tmap(&map, base, g.rows_box, cols, rows, ld, f32);
   if (rc) return rc;
   AFL_CUDA(cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
-  GramParams P{g.rows_box, g.n_cols, g.m_tiles, (int)(g.Dp / kBlockK), g.stages, partials};
+  GramParams P{g.rows_box, g.n_cols, g.m_tiles, (int)(g.Dp / g.kelems), g.kelems, f32 ? 1 : 0, g.stages, partials};
   gram_kernel<<<g.grid, kThreads, g.smem, st>>>(map, P);
   afl_rt::count_launch();
   return afl_rt::check_last("gram_kernel");
@@ -314,11 +330,35 @@ int afl_gram_bf16(const float* A, int R, int64_t D, int64_t lda, void* a16, floa
   if (cg > afl_rt::num_sms() * 16) cg = afl_rt::num_sms() * 16;
   cast_rows_kernel<<<cg, 256, 0, st>>>(A, R, D, lda, (__nv_bfloat16*)a16, nullptr, g.rows_box, g.Dp);
   afl_rt::count_launch();
-  rc = launch_gram((const __nv_bfloat16*)a16, nullptr, g, partials, st);
+  rc = launch_gram(a16, g.Dp, g.rows_box, g.Dp, false, g, partials, st);
   if (rc) return rc;
   gram_reduce_kernel<<<(R * R + 255) / 256, 256, 0, st>>>(partials, g.grid, g.rows_box, g.n_cols, R, G);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_gram_bf16");
+}
+
+// G = A A^T with the fp32 rows used directly as TF32 tensor-core operands: no cast pass and no operand copy (TMA
+// reads the caller's matrix and zero-fills rows >= R / columns >= D), one pass over R*D*4 bytes; SURVEY §2.8 probe:
+// 4.6e-6 relative error on distances of centred rows.  A must be 16-byte aligned with lda % 4 == 0.
+int afl_gram_tf32(const float* A, int R, int64_t D, int64_t lda, float* partials, float* G, void* stream) {
+  Geometry g;
+  int rc = geometry(R, D, &g, 32);
+  if (rc) return rc;
+  AFL_CHECK_ARG((lda % 4) == 0 && (reinterpret_cast<uintptr_t>(A) % 16) == 0, "afl_gram_tf32: A must be 16-byte aligned, lda % 4 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  rc = launch_gram(A, D, R, lda, true, g, partials, st);
+  if (rc) return rc;
+  gram_reduce_kernel<<<(R * R + 255) / 256, 256, 0, st>>>(partials, g.grid, g.rows_box, g.n_cols, R, G);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_gram_tf32");
+}
+
+int afl_gram_tf32_workspace(int R, int64_t D, int64_t* partial_floats) {
+  Geometry g;
+  int rc = geometry(R, D, &g, 32);
+  if (rc) return rc;
+  *partial_floats = (int64_t)g.partial_floats;
+  return 0;
 }
 
 }  // extern "C"

@@ -78,6 +78,16 @@ int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb
                    float* delta, float* f_scratch, float* acts, float* red, int64_t d_pad, float lr, float b1,
                    float b2, float eps, int step, float clip, void* stream);
 
+/* K3 — split-K Gram matrix G [R][R] = A A^T on tcgen05 tensor cores (TMA -> 128B-swizzled smem -> tcgen05.mma ->
+ * TMEM -> tcgen05.ld), R <= 256 (src/Utils.py:30-49,108-113,142-147,176-185 pairwise distances; :326-342 Krum;
+ * server.py:310-350 ShieldFL; :703-743 FLTrust).  afl_gram_tf32 reads the fp32 rows directly as TF32 operands (no
+ * cast pass, TMA zero-fills the padding); afl_gram_bf16 first casts to a zero-padded bf16 copy (a16).  partials:
+ * split-K scratch, sizes from the *_workspace calls. */
+int afl_gram_workspace(int R, int64_t D, int64_t* bf16_elems, int64_t* partial_floats);
+int afl_gram_bf16(const float* A, int R, int64_t D, int64_t lda, void* a16, float* partials, float* G, void* stream);
+int afl_gram_tf32_workspace(int R, int64_t D, int64_t* partial_floats);
+int afl_gram_tf32(const float* A, int R, int64_t D, int64_t lda, float* partials, float* G, void* stream);
+
 /* Allocation-free variant of afl_hyper_step (no counterpart in the reference: it exists for callers of THIS
  * library that may not allocate device memory -- pre-reserved real-time loops, plugins inside another runtime's
  * memory budget, host callbacks that must not trigger a device synchronisation).  Identical arithmetic and
