@@ -49,6 +49,20 @@ def _write_datasets(workdir: str, train_rows: int, test_rows: int):
 
 
 def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_rows: int) -> dict:
+    """bench.py --impl reference: BASELINE config 3 (one LIE attacker per 8 clients)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    C = clients_per_gpu * world
+    attackers = {c: ("LIE", 2, [0.74]) for c in range(C) if c % clients_per_gpu == clients_per_gpu - 1}
+    return run_config(bench_config(C), attackers, args.steps, args.warmup, clients_per_gpu, train_rows, test_rows)
+
+
+def run_config(cfg: dict, attackers: dict, steps: int, warmup_req: int, clients_per_gpu: int, train_rows: int,
+               test_rows: int, min_warmup: int = 3) -> dict:
+    """Drives the unmodified reference for ``warmup + steps`` rounds of ``cfg`` (any mode / model) and times the
+    last ``steps`` rounds.  ``attackers``: client index -> (mode, first attack round, args)."""
+    import types
+    args = types.SimpleNamespace(steps=steps, warmup=warmup_req)
+    bench_config = lambda n: cfg
     import torch
     import torch.distributed as dist
 
@@ -72,7 +86,7 @@ def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_ro
             dist.init_process_group("gloo", rank=rank, world_size=world)
         else:
             dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
-    warmup = max(args.warmup, 3)
+    warmup = max(args.warmup, min_warmup)
     n_rounds = warmup + args.steps
     C = clients_per_gpu * world
     cfg = bench_config(C)
@@ -95,8 +109,8 @@ def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_ro
             clients = {}
             for c in my:
                 rc = client_mod.RpcClient(ids[c], "127.0.0.1", "admin", "admin", client_mod.train_on_device, dev)
-                if c % clients_per_gpu == clients_per_gpu - 1:
-                    rc.set_attack_config("LIE", 2, [0.74])
+                if c in attackers:
+                    rc.set_attack_config(*attackers[c])
                 clients[c] = rc
             server = server_mod.Server() if rank == 0 else None
 
@@ -145,7 +159,7 @@ def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_ro
         with contextlib.redirect_stdout(sink):
             for c in my:
                 clients[c].send_to_server({"action": "REGISTER", "client_id": ids[c], "message": "Hello from Client!",
-                                           "attack": c % clients_per_gpu == clients_per_gpu - 1})
+                                           "attack": c in attackers})
             to_server(gather(drain_rpc()))
 
         def one_round() -> bool:
@@ -207,8 +221,8 @@ def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_ro
         "unit": "client-rounds/s", "rounds_per_sec": round(args.steps / (dev_ms / 1e3), 5), "n_gpus": world,
         "steps": args.steps, "warmup": warmup, "ms_per_step": round(dev_ms / args.steps, 2), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "reference",
-        "config": {"model": cfg["server"]["model"], "mode": "fedavg", "attack": "LIE z=0.74, 1 attacker per 8 clients "
-                   "from round 2", "clients": C, "clients_per_gpu": clients_per_gpu, "local_epochs": 5,
+        "config": {"model": cfg["server"]["model"], "mode": cfg["server"]["mode"],
+                   "attack": {str(k): list(v) for k, v in attackers.items()}, "clients": C, "clients_per_gpu": clients_per_gpu, "local_epochs": 5,
                    "batch_size": 128, "num_data_range": [12000, 15000], "parallelism": f"fl-clients x{world}",
                    "transport": "in-memory pika stand-in + torch.distributed object collectives (no broker)",
                    "patch": "server.py:289 if->elif (fedavg crash fix, applied in memory)"},
