@@ -50,6 +50,7 @@ def server_parser() -> argparse.ArgumentParser:
     p.add_argument("--attacker", action="append", default=[], metavar="IDX:MODE:ROUND[:ARGS]",
                    help="with --local-clients: mark client IDX as an attacker, e.g. 7:LIE:2:0.74")
     p.add_argument("--register-timeout", type=float, default=None, help="seconds to wait for registrations")
+    p.add_argument("--gpus", type=int, default=0, help="ranks to launch (one per GPU); default runtime.gpus")
     return p
 
 

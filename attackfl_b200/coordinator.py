@@ -35,7 +35,13 @@ class Coordinator:
     def __init__(self, cfg: Config, device: Optional[str] = None, workdir: str = ".", ctx=None):
         self.cfg, self.device, self.workdir, self.ctx = cfg, device, workdir, ctx
         os.makedirs(cfg.log_path or ".", exist_ok=True)
-        self.logger = Logger(os.path.join(cfg.log_path or ".", "app.log"))
+        self.rank0 = ctx is None or ctx.rank == 0
+        if self.rank0:
+            self.logger = Logger(os.path.join(cfg.log_path or ".", "app.log"))
+        else:                                   # only rank 0 talks to the user / the log file
+            from .log import NullLogger, set_quiet
+            self.logger = NullLogger()
+            set_quiet(True)
         self.server: Optional[ControlServer] = None
         self.fed: Optional[Federation] = None
 

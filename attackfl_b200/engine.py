@@ -156,7 +156,7 @@ class Federation:
         self.sizes = [0] * self.C
         self.genuine_prev: Optional[List[int]] = None        # indices of last round's genuine reporters
         self.timer = PhaseTimer(self.device)
-        self.validator = Validator(self.data_name, self.logger)
+        self.validator = Validator(self.data_name, self.logger if ctx.rank == 0 else None, quiet=ctx.rank != 0)
         self.metrics = MetricsWriter(os.path.join(workdir, cfg.runtime.metrics_file) if (save and ctx.rank == 0) else None)
         self.history: List[RoundResult] = []
         self.fused_comm = None                               # set by parallel.symm.attach()

@@ -42,12 +42,15 @@ def roc_auc(scores: torch.Tensor, labels: torch.Tensor) -> float:
 class Validator:
     """``forward_fn(row_or_None, vitals, labs) -> probs`` abstracts torch modules vs the native kernel."""
 
-    def __init__(self, data_name: str, logger=None):
+    def __init__(self, data_name: str, logger=None, quiet: bool = False):
         self.data_name = data_name
         self.logger = logger
+        self.quiet = quiet
         self.last_metric: Optional[float] = None
 
     def _emit(self, text: str) -> None:
+        if self.quiet:
+            return
         print(text, flush=True)
         if self.logger is not None:
             self.logger.log_info(text)

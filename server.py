@@ -18,19 +18,39 @@ from attackfl_b200.log import print_with_color             # noqa: E402
 
 def main(argv=None) -> int:
     args = server_parser().parse_args(argv)
-    device = pick_device(args.device)
     cfg = load_config(args.config)
-    coord = Coordinator(cfg, device=device, workdir=".")
+    if args.gpus:
+        cfg.runtime.gpus = args.gpus
+    from attackfl_b200.parallel import launch
+    rc = launch.maybe_relaunch(cfg.runtime.gpus)           # one process per GPU (re-exec under torchrun)
+    if rc is not None:
+        return rc
+    ctx = None
+    if "RANK" in os.environ:
+        from attackfl_b200.parallel import ctx as pctx
+        ctx = pctx.init_from_env(args.device)
+        device = str(ctx.device)
+    else:
+        device = pick_device(args.device)
+    rank0 = ctx is None or ctx.rank == 0
+    coord = Coordinator(cfg, device=device, workdir=".", ctx=ctx)
+    specs = None
     if args.local_clients:
         cfg.server.clients = args.local_clients
         coord.logger.log_info("### Application start ###\n")
         specs = coord.local_specs(args.local_clients, args.attacker)
-    else:
+    elif rank0:
         coord.listen()
         specs = coord.wait_for_clients(args.register_timeout)
-    coord.start(specs)
+    if ctx is not None:
+        specs = launch.broadcast_specs(ctx, specs)
+    fed = coord.start(specs)
+    if ctx is not None and ctx.distributed and cfg.runtime.collectives == "fused" and fed.device.type == "cuda":
+        from attackfl_b200.parallel import symm
+        symm.attach(fed)
     coord.run()
-    print_with_color("Ok, ready!", "green")
+    if rank0:
+        print_with_color("Ok, ready!", "green")
     return 0
 
 
