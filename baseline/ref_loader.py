@@ -71,7 +71,12 @@ def load_server_client(workdir: str, config: dict, device: str = "cpu", patch_fe
     try:
         for name in ("server", "client"):
             sys.modules.pop(name, None)
-        client = importlib.import_module("client")
+        # load the reference's client.py by path: this repo has its own client.py / server.py CLI shims at its root,
+        # which must not shadow the reference's modules (server.py:31 does `from client import *`)
+        spec = importlib.util.spec_from_file_location("client", os.path.join(REF, "client.py"))
+        client = importlib.util.module_from_spec(spec)
+        sys.modules["client"] = client
+        spec.loader.exec_module(client)
         src = open(os.path.join(REF, "server.py")).read()
         if patch_fedavg:
             a = '                self.avg_all_parameters()\n            if server_mode == "FLTrust":'
