@@ -71,17 +71,18 @@ def plan_for(model_name: str, layout, batch: int, n_clients: int, device, *, dro
     (measured on B200: S=8 -> 16 blocks/client is 21-29 % faster than S=16 -> 8 blocks when 128 SMs are free);
     fall back to larger tiles / several tiles per block when the rank hosts many clients."""
     from ..models.programs import build_program
-    best = None
+    cands = []
     for S in TILE_CANDIDATES.get(model_name, (16,)):
         prog = build_program(model_name, layout, S=S, train=True, dropout=dropout, module=module).to(device)
         plan = make_plan(prog, batch, n_clients, layout.padded, device, blocks_per_client)
-        if best is None:
-            best = (prog, plan)
-        if plan.M == 1 and plan.chunk >= n_clients:
-            return prog, plan
-        if plan.M * plan.S < best[1].M * best[1].S or (plan.chunk >= n_clients > best[1].chunk):
-            best = (prog, plan)
-    return best
+        cands.append((prog, plan))
+    # 1) every tile on its own block and all clients co-resident: smallest tile wins (shortest dependent chains);
+    # 2) otherwise the blocks are capacity-limited and loop over tiles: fewest, largest tiles win (per-tile
+    #    overhead: ~40 barrier intervals), preferring plans that keep all clients in one launch.
+    par = [c for c in cands if c[1].M == 1 and c[1].chunk >= n_clients]
+    if par:
+        return min(par, key=lambda c: c[1].S)
+    return min(cands, key=lambda c: (0 if c[1].chunk >= n_clients else 1, c[1].M, -c[1].S))
 
 
 def train_round(program: Program, plan: TrainPlan, w: torch.Tensor, m: torch.Tensor, v: Optional[torch.Tensor],
