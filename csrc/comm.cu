@@ -76,7 +76,37 @@ __global__ void __launch_bounds__(kThreads) fedavg_fused_kernel(FusedArgs a) {
 
   // ---- phase 1: owned slice: gather (P2P loads) -> reduce -> scatter to every rank (P2P stores)
   const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
-  for (int64_t i = a.lo + 4 * tid; i < a.hi; i += 4 * nt) {
+  if (A == 0) {
+    // bandwidth path: U independent float4 columns per thread so that U remote loads are in flight per row
+    // (one 16-byte peer load per thread caps at ~300 GB/s: 148*256*16 B in flight / ~2 us NVLink latency)
+    constexpr int U = 4;
+    for (int64_t i0 = a.lo + 4 * tid; i0 < a.hi; i0 += 4 * nt * U) {
+      float4 acc[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) acc[u] = afl_f4(0.f);
+      for (int c = 0; c < a.C; ++c) {
+        const float* row = rp[c];
+        const float wc = wsm[c];
+        float4 x[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t i = i0 + (int64_t)u * 4 * nt;
+          x[u] = i < a.hi ? afl_ld4(row + i) : afl_f4(0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          acc[u].x += wc * x[u].x; acc[u].y += wc * x[u].y; acc[u].z += wc * x[u].z; acc[u].w += wc * x[u].w;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + (int64_t)u * 4 * nt;
+        if (i < a.hi)
+          for (int r = 0; r < a.world; ++r) afl_st4(a.glob[r] + i, acc[u]);
+      }
+    }
+  }
+  for (int64_t i = a.lo + 4 * tid; A > 0 && i < a.hi; i += 4 * nt) {
     float4 acc = afl_f4(0.f), rf = afl_f4(0.f);
     float4 s1[A > 0 ? A : 1], s2[A > 0 ? A : 1];
     if (A > 0) {
@@ -184,9 +214,6 @@ int afl_fedavg_fused(const float* const* row_ptrs, const float* weights, int C, 
   a.z = z; a.strict_k1 = strict_k1; a.local_rows = local_rows; a.CL = CL;
   a.grid_ctr = ctrl; a.go_flag = ctrl + 1; a.err = reinterpret_cast<int*>(ctrl + 2);
   const size_t smem = sizeof(float) * (size_t)(C + A * C + 2) + sizeof(void*) * (size_t)C;
-  int64_t work = (d_pad / 4 + kThreads - 1) / kThreads;
-  int grid = (int)(work < afl_rt::num_sms() ? work : afl_rt::num_sms());
-  if (grid < 1) grid = 1;
   void* args[] = {&a};
   cudaStream_t st = (cudaStream_t)stream;
   const void* fn = nullptr;
@@ -197,6 +224,14 @@ int afl_fedavg_fused(const float* const* row_ptrs, const float* weights, int C, 
     case 3: fn = (const void*)fedavg_fused_kernel<3>; break;
     default: fn = (const void*)fedavg_fused_kernel<4>; break;
   }
+  // co-resident grid (the in-kernel barriers need it): up to 4 blocks per SM for bytes in flight
+  int per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kThreads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (per_sm > 4) per_sm = 4;
+  const int64_t slice_items = (slice / 4 + kThreads - 1) / kThreads;
+  int64_t cap = (int64_t)per_sm * afl_rt::num_sms();
+  int grid = (int)(slice_items < cap ? slice_items : cap);
+  if (grid < 1) grid = 1;
   AFL_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, smem, st));
   afl_rt::count_launch();
   return afl_rt::check_last("afl_fedavg_fused");
