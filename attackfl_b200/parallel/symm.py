@@ -38,28 +38,26 @@ class FusedComm:
         self.glob = symm_mem.empty(D, dtype=torch.float32, device=dev)
         self.lie = symm_mem.empty(self.n_lie, D, dtype=torch.float32, device=dev)
         self.sig = symm_mem.empty(64, dtype=torch.int32, device=dev)
-        self.rows.zero_(); self.lie.zero_(); self.sig.zero_()
+        self.part = symm_mem.empty(1 + 2 * min(self.n_lie, MAX_ATT), D, dtype=torch.float32, device=dev)
+        self.rows.zero_(); self.lie.zero_(); self.sig.zero_(); self.part.zero_()
         self.rows[:fed.CL].copy_(fed.rows[:fed.CL])
         self.glob.copy_(fed.global_row)
         self.h_rows = symm_mem.rendezvous(self.rows, group)
         self.h_glob = symm_mem.rendezvous(self.glob, group)
         self.h_lie = symm_mem.rendezvous(self.lie, group)
         self.h_sig = symm_mem.rendezvous(self.sig, group)
+        self.h_part = symm_mem.rendezvous(self.part, group)
         torch.cuda.synchronize(dev)
         dist.barrier()
         # the engine now works directly on the symmetric tensors
         fed.rows = self.rows
         fed.global_row = self.glob
-        # pointer tables
-        row_ptrs = []
-        for c in range(fed.C):
-            r = c // self.cpg
-            row_ptrs.append(int(self.h_rows.buffer_ptrs[r]) + (c - r * self.cpg) * D * 4)
-        self.row_ptrs = torch.tensor(row_ptrs, dtype=torch.int64, device=dev)
+        # pointer tables (host arrays of peer-mapped device pointers)
         PtrArr = ctypes.c_void_p * self.world
         self.glob_ptrs = PtrArr(*[int(p) for p in self.h_glob.buffer_ptrs])
         self.lie_ptrs = PtrArr(*[int(p) for p in self.h_lie.buffer_ptrs])
         self.sig_ptrs = PtrArr(*[int(p) for p in self.h_sig.buffer_ptrs])
+        self.part_ptrs = PtrArr(*[int(p) for p in self.h_part.buffer_ptrs])
         self.ctrl = torch.zeros(4, dtype=torch.int32, device=dev)
         self.epoch = 0
         self.multicast = bool(getattr(self.h_glob, "multicast_ptr", 0))
@@ -73,26 +71,28 @@ class FusedComm:
         lib = native.cuda_lib()
         A = 0 if member is None else member.shape[0]
         assert A <= self.n_lie
-        weights = weights.to(device=dev, dtype=torch.float32).contiguous()
+        lo, hi = fed.local[0] if fed.local else 0, (fed.local[-1] + 1) if fed.local else 0
+        w_loc = weights[lo:hi].to(device=dev, dtype=torch.float32).contiguous()
         out = None
         passes = [(0, 0)] if A == 0 else [(a0, min(A, a0 + MAX_ATT)) for a0 in range(0, A, MAX_ATT)]
         for pi, (a0, a1) in enumerate(passes):
             self.epoch += 1
             n = a1 - a0
             if n:
-                mem = member[a0:a1].to(device=dev, dtype=torch.float32).contiguous()
-                kc = mem.sum(1).contiguous()
+                mem_all = member[a0:a1].to(dtype=torch.float32)
+                kc = mem_all.sum(1).to(dev).contiguous()                  # global subset sizes
+                mem = mem_all[:, lo:hi].to(dev).contiguous()             # membership of the local clients
                 zz = z[a0:a1].to(device=dev, dtype=torch.float32).contiguous()
                 lie_ptrs = (ctypes.c_void_p * self.world)(*[int(p) + a0 * fed.D * 4 for p in self.h_lie.buffer_ptrs])
             else:
                 mem = kc = zz = None
                 lie_ptrs = None
             rc = lib.afl_fedavg_fused(
-                ptr(self.row_ptrs), ptr(weights), ctypes.c_int(fed.C), ctypes.c_int64(fed.D), ctypes.c_int(self.world),
-                ctypes.c_int(self.rank), self.glob_ptrs, lie_ptrs, self.sig_ptrs, ctypes.c_uint32(self.epoch),
-                ctypes.c_int(n), ptr(ref), ptr(mem), ptr(kc), ptr(zz), ctypes.c_int(1 if strict_k1 else 0),
-                ptr(self.rows) if pi == len(passes) - 1 else ctypes.c_void_p(0), ctypes.c_int(fed.CL), ptr(self.ctrl),
-                stream_ptr(self.rows))
+                ptr(self.rows), ptr(w_loc), ctypes.c_int(fed.CL), ctypes.c_int64(fed.D), ctypes.c_int(self.world),
+                ctypes.c_int(self.rank), self.part_ptrs, self.glob_ptrs, lie_ptrs, self.sig_ptrs,
+                ctypes.c_uint32(self.epoch), ctypes.c_int(n), ptr(ref), ptr(mem), ptr(kc), ptr(zz),
+                ctypes.c_int(1 if strict_k1 else 0),
+                ptr(self.rows) if pi == len(passes) - 1 else ctypes.c_void_p(0), ptr(self.ctrl), stream_ptr(self.rows))
             check(lib, rc, "afl_fedavg_fused")
         if A:
             out = self.lie[:A].clone()

@@ -52,12 +52,13 @@ def main():
         rows = symm_mem.empty(R, D, dtype=torch.float32, device=dev)
         glob = symm_mem.empty(D, dtype=torch.float32, device=dev)
         sig = symm_mem.empty(64, dtype=torch.int32, device=dev)
+        partial = symm_mem.empty(D, dtype=torch.float32, device=dev)
         rows.normal_(); sig.zero_()
-        h_rows, h_glob, h_sig = (symm_mem.rendezvous(t, dist.group.WORLD) for t in (rows, glob, sig))
+        h_rows, h_glob, h_sig, h_part = (symm_mem.rendezvous(t, dist.group.WORLD) for t in (rows, glob, sig, partial))
         torch.cuda.synchronize(); dist.barrier()
-        row_ptrs = torch.tensor([int(h_rows.buffer_ptrs[c // R]) + (c % R) * D * 4 for c in range(C)], dtype=torch.int64, device=dev)
         PA = ctypes.c_void_p * G
         gp, sp = PA(*[int(p) for p in h_glob.buffer_ptrs]), PA(*[int(p) for p in h_sig.buffer_ptrs])
+        pp = PA(*[int(p) for p in h_part.buffer_ptrs])
         ctrl = torch.zeros(4, dtype=torch.int32, device=dev)
         w = torch.full((C,), 1.0 / C, device=dev)
         wl = torch.full((R,), 1.0 / C, device=dev)
@@ -65,9 +66,9 @@ def main():
 
         def fused():
             epoch[0] += 1
-            check(lib, lib.afl_fedavg_fused(ptr(row_ptrs), ptr(w), ctypes.c_int(C), ctypes.c_int64(D), ctypes.c_int(G),
-                                            ctypes.c_int(rank), gp, None, sp, ctypes.c_uint32(epoch[0]), ctypes.c_int(0),
-                                            None, None, None, None, ctypes.c_int(0), ptr(rows), ctypes.c_int(R), ptr(ctrl),
+            check(lib, lib.afl_fedavg_fused(ptr(rows), ptr(wl), ctypes.c_int(R), ctypes.c_int64(D), ctypes.c_int(G),
+                                            ctypes.c_int(rank), pp, gp, None, sp, ctypes.c_uint32(epoch[0]), ctypes.c_int(0),
+                                            None, None, None, None, ctypes.c_int(0), ptr(rows), ptr(ctrl),
                                             stream_ptr(rows)), "afl_fedavg_fused")
 
         part = torch.empty(D, device=dev)
@@ -103,9 +104,9 @@ def main():
         S = D * 4
         for name, fn in (("fused", fused), ("nccl", nccl)):
             t = timeit(fn)
-            nv_bytes = (G - 1) / G * S * R          # per direction per rank (reads of remote rows; writes are (G-1)/G*S)
-            hbm_bytes = (R * S / G * 1 + S + R * S) if name == "fused" else (R * S + S + 2 * S + R * S + S)
-            roof = max(max(nv_bytes, (G - 1) / G * S) / (NVLINK_GBS * 1e9), hbm_bytes / (hbm * 1e9))
+            nv_bytes = (G - 1) / G * S              # per direction per rank: partial slices in, result slices out
+            hbm_bytes = (R * S + S) + (S / G + S) + (S + R * S)     # pre-reduce, slice reduce + result, fan-out
+            roof = max(nv_bytes / (NVLINK_GBS * 1e9), hbm_bytes / (hbm * 1e9))
             rec = {"size_mb": mb, "gpus": G, "rows_per_rank": R, "path": name, "ms": round(t * 1e3, 4),
                    "alg_GBps": round(S / t / 1e9, 1), "bus_GBps": round(2 * (G - 1) / G * S / t / 1e9, 1),
                    "roofline_frac": round(roof / t, 3), "max_abs_diff_vs_other_path": err}
@@ -114,7 +115,7 @@ def main():
                 print(json.dumps(rec), flush=True)
         if int(ctrl[2].item()) != 0:
             raise RuntimeError("fused collective timed out")
-        del rows, glob, sig, part, keep, g1
+        del rows, glob, sig, part, keep, g1, partial
         torch.cuda.empty_cache()
     dist.barrier()
     dist.destroy_process_group()

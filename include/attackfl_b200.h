@@ -40,15 +40,16 @@ int afl_fedavg(const float* rows, const float* weights, int C, int64_t d_pad, fl
                float* sd, float* lie, int strict_k1, void* stream);
 
 /* K1-fused — multi-GPU FedAvg over NVLink peer memory in one kernel per rank (server.py:751-775 reduce +
- * :588-614 broadcast): rank r reduces coordinate slice r by loading it from every client's row in
- * place (row_ptrs [C], local or peer-mapped), stores the result into every rank's global buffer (glob [world]),
- * optionally the LIE rows of up to 4 attackers (lie [world], [A][d_pad]), crosses a st.release.sys/ld.acquire.sys
- * flag barrier (sig [world]: symmetric uint32 buffers) and fans the new global out to local_rows [CL][d_pad].
+ * :588-614 broadcast).  Two levels: local pre-reduce of this rank's rows (local_rows [CL][d_pad],
+ * weights/member for the LOCAL clients) into its symmetric partial buffer, flag barrier, then rank r sums slice r of
+ * the G partials through peer-mapped pointers (part [world], each [1+2A][d_pad]), stores the result into every
+ * rank's global buffer (glob [world]) and the LIE rows of up to 4 attackers (lie [world], [A][d_pad]), second barrier
+ * (sig [world]: symmetric uint32 buffers, st.release.sys / ld.acquire.sys) and fan-out to local_rows_out.
  * ctrl: 4 zero-initialised local uint32 {grid counter, go flag, error, pad}; epoch increases by 1 per call. */
-int afl_fedavg_fused(const float* const* row_ptrs, const float* weights, int C, int64_t d_pad, int world, int rank,
-                     float* const* glob, float* const* lie, uint32_t* const* sig, uint32_t epoch, int A,
-                     const float* ref, const float* member, const float* kcount, const float* z, int strict_k1,
-                     float* local_rows, int CL, uint32_t* ctrl, void* stream);
+int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int64_t d_pad, int world, int rank,
+                     float* const* part, float* const* glob, float* const* lie, uint32_t* const* sig, uint32_t epoch,
+                     int A, const float* ref, const float* member, const float* kcount, const float* z, int strict_k1,
+                     float* local_rows_out, uint32_t* ctrl, void* stream);
 
 /* K4 — gamma bisection on the (k+2)x(k+2) Gram matrix of [g_1-c..g_k-c, mu-c, p] (src/Utils.py:115-130;
  * rule 0 = Min-Max / Opt-Fang, 1 = Min-Sum; exclude_first reproduces the aliasing of genuine model 0,
