@@ -60,7 +60,10 @@ class FusedComm:
         self.part_ptrs = PtrArr(*[int(p) for p in self.h_part.buffer_ptrs])
         self.ctrl = torch.zeros(4, dtype=torch.int32, device=dev)
         self.epoch = 0
-        self.multicast = bool(getattr(self.h_glob, "multicast_ptr", 0))
+        import os
+        mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in (self.h_part, self.h_glob, self.h_lie)]
+        self.multicast = all(mc) and os.environ.get("ATTACKFL_NVLS", "1") != "0"
+        self.mc_part, self.mc_glob, self.mc_lie = mc if self.multicast else (0, 0, 0)
 
     def fedavg(self, weights: torch.Tensor, member: Optional[torch.Tensor] = None, z: Optional[torch.Tensor] = None,
                ref: Optional[torch.Tensor] = None, strict_k1: bool = False) -> Optional[torch.Tensor]:
@@ -92,7 +95,9 @@ class FusedComm:
                 ctypes.c_int(self.rank), self.part_ptrs, self.glob_ptrs, lie_ptrs, self.sig_ptrs,
                 ctypes.c_uint32(self.epoch), ctypes.c_int(n), ptr(ref), ptr(mem), ptr(kc), ptr(zz),
                 ctypes.c_int(1 if strict_k1 else 0),
-                ptr(self.rows) if pi == len(passes) - 1 else ctypes.c_void_p(0), ptr(self.ctrl), stream_ptr(self.rows))
+                ptr(self.rows) if pi == len(passes) - 1 else ctypes.c_void_p(0), ptr(self.ctrl),
+                ctypes.c_void_p(self.mc_part), ctypes.c_void_p(self.mc_glob),
+                ctypes.c_void_p(self.mc_lie + a0 * fed.D * 4 if self.mc_lie else 0), stream_ptr(self.rows))
             check(lib, rc, "afl_fedavg_fused")
         if A:
             out = self.lie[:A].clone()

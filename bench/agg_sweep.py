@@ -64,12 +64,15 @@ def main():
         wl = torch.full((R,), 1.0 / C, device=dev)
         epoch = [0]
 
-        def fused():
+        mc_part, mc_glob = int(getattr(h_part, "multicast_ptr", 0) or 0), int(getattr(h_glob, "multicast_ptr", 0) or 0)
+
+        def fused(nvls=False):
             epoch[0] += 1
             check(lib, lib.afl_fedavg_fused(ptr(rows), ptr(wl), ctypes.c_int(R), ctypes.c_int64(D), ctypes.c_int(G),
                                             ctypes.c_int(rank), pp, gp, None, sp, ctypes.c_uint32(epoch[0]), ctypes.c_int(0),
                                             None, None, None, None, ctypes.c_int(0), ptr(rows), ptr(ctrl),
-                                            stream_ptr(rows)), "afl_fedavg_fused")
+                                            ctypes.c_void_p(mc_part if nvls else 0), ctypes.c_void_p(mc_glob if nvls else 0),
+                                            ctypes.c_void_p(0), stream_ptr(rows)), "afl_fedavg_fused")
 
         part = torch.empty(D, device=dev)
 
@@ -102,14 +105,22 @@ def main():
         err = float((g1 - part).abs().max())
         rows.copy_(keep); torch.cuda.synchronize(); dist.barrier()
         S = D * 4
-        for name, fn in (("fused", fused), ("nccl", nccl)):
+        paths = [("fused", fused), ("nccl", nccl)]
+        if mc_part and mc_glob:
+            rows.copy_(keep); torch.cuda.synchronize(); dist.barrier()
+            fused(True); torch.cuda.synchronize(); dist.barrier()
+            err_nvls = float((glob - part).abs().max())
+            rows.copy_(keep); torch.cuda.synchronize(); dist.barrier()
+            paths.insert(1, ("fused_nvls", lambda: fused(True)))
+        for name, fn in paths:
             t = timeit(fn)
             nv_bytes = (G - 1) / G * S              # per direction per rank: partial slices in, result slices out
             hbm_bytes = (R * S + S) + (S / G + S) + (S + R * S)     # pre-reduce, slice reduce + result, fan-out
             roof = max(nv_bytes / (NVLINK_GBS * 1e9), hbm_bytes / (hbm * 1e9))
             rec = {"size_mb": mb, "gpus": G, "rows_per_rank": R, "path": name, "ms": round(t * 1e3, 4),
                    "alg_GBps": round(S / t / 1e9, 1), "bus_GBps": round(2 * (G - 1) / G * S / t / 1e9, 1),
-                   "roofline_frac": round(roof / t, 3), "max_abs_diff_vs_other_path": err}
+                   "roofline_frac": round(roof / t, 3),
+                   "max_abs_diff_vs_nccl_path": err_nvls if name == "fused_nvls" else err}
             results.append(rec)
             if rank == 0:
                 print(json.dumps(rec), flush=True)

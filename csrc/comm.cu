@@ -37,6 +37,9 @@ struct FusedArgs {
   float* glob[kMaxWorld];         // every rank's global-model buffer (peer-mapped)
   float* lie[kMaxWorld];          // every rank's LIE buffer [A][d_pad] (peer-mapped) or null
   uint32_t* sig[kMaxWorld];       // every rank's signal buffer (peer-mapped), [world] words used
+  float* part_mc;                 // NVLS multicast address of the partial buffers (null: use P2P loads)
+  float* glob_mc;                 // NVLS multicast address of the global buffers (null: use P2P stores)
+  float* lie_mc;                  // NVLS multicast address of the LIE buffers
   int world, rank;
   uint32_t epoch;                 // this call uses barrier epochs 2*epoch-1 and 2*epoch
   // moments (K2)
@@ -65,6 +68,19 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+
+// NVLS (NVSwitch in-network reduction / multicast): one load returns the SUM over all ranks' copies, one store
+// lands in all ranks' copies.  Both are weak operations; the flag barriers around phase 1 order them.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
 // Barrier across all blocks of all ranks: local grid barrier (atomic counter); the last local block signals every
@@ -173,31 +189,50 @@ __global__ void __launch_bounds__(kThreads) fedavg_fused_kernel(FusedArgs a) {
 #pragma unroll
       for (int q = 0; q < A; ++q) { s1[q] = afl_f4(0.f); s2[q] = afl_f4(0.f); }
     }
-    for (int r = 0; r < a.world; ++r) {
-      const float* pr = a.part[r];
-      float4 x[U];
+    if (a.part_mc) {
+      // in-switch reduction: one multimem.ld_reduce per column returns the sum of the G partials
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t i = i0 + (int64_t)u * 4 * nt;
-        x[u] = i < a.hi ? afl_ld4(pr + i) : afl_f4(0.f);
+        if (i < a.hi) acc[u] = multimem_ld_reduce_add(a.part_mc + i);
       }
-#pragma unroll
-      for (int u = 0; u < U; ++u) { acc[u].x += x[u].x; acc[u].y += x[u].y; acc[u].z += x[u].z; acc[u].w += x[u].w; }
       if (A > 0) {
 #pragma unroll
         for (int q = 0; q < A; ++q) {
-          const float4 p1 = afl_ld4(pr + (int64_t)(1 + 2 * q) * a.d_pad + i0);
-          const float4 p2 = afl_ld4(pr + (int64_t)(2 + 2 * q) * a.d_pad + i0);
-          s1[q].x += p1.x; s1[q].y += p1.y; s1[q].z += p1.z; s1[q].w += p1.w;
-          s2[q].x += p2.x; s2[q].y += p2.y; s2[q].z += p2.z; s2[q].w += p2.w;
+          s1[q] = multimem_ld_reduce_add(a.part_mc + (int64_t)(1 + 2 * q) * a.d_pad + i0);
+          s2[q] = multimem_ld_reduce_add(a.part_mc + (int64_t)(2 + 2 * q) * a.d_pad + i0);
+        }
+      }
+    } else {
+      for (int r = 0; r < a.world; ++r) {
+        const float* pr = a.part[r];
+        float4 x[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t i = i0 + (int64_t)u * 4 * nt;
+          x[u] = i < a.hi ? afl_ld4(pr + i) : afl_f4(0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) { acc[u].x += x[u].x; acc[u].y += x[u].y; acc[u].z += x[u].z; acc[u].w += x[u].w; }
+        if (A > 0) {
+#pragma unroll
+          for (int q = 0; q < A; ++q) {
+            const float4 p1 = afl_ld4(pr + (int64_t)(1 + 2 * q) * a.d_pad + i0);
+            const float4 p2 = afl_ld4(pr + (int64_t)(2 + 2 * q) * a.d_pad + i0);
+            s1[q].x += p1.x; s1[q].y += p1.y; s1[q].z += p1.z; s1[q].w += p1.w;
+            s2[q].x += p2.x; s2[q].y += p2.y; s2[q].z += p2.z; s2[q].w += p2.w;
+          }
         }
       }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t i = i0 + (int64_t)u * 4 * nt;
-      if (i < a.hi)
-        for (int r = 0; r < a.world; ++r) afl_st4(a.glob[r] + i, acc[u]);
+      if (i < a.hi) {
+        if (a.glob_mc) multimem_st(a.glob_mc + i, acc[u]);
+        else
+          for (int r = 0; r < a.world; ++r) afl_st4(a.glob[r] + i, acc[u]);
+      }
     }
     if (A > 0) {
       const float4 rf = afl_ld4(a.ref + i0);
@@ -211,7 +246,9 @@ __global__ void __launch_bounds__(kThreads) fedavg_fused_kernel(FusedArgs a) {
           l.c = mu + zz * sd; }
         AFL_LIE1(x) AFL_LIE1(y) AFL_LIE1(z) AFL_LIE1(w)
 #undef AFL_LIE1
-        for (int r = 0; r < a.world; ++r) afl_st4(a.lie[r] + (int64_t)q * a.d_pad + i0, l);
+        if (a.lie_mc) multimem_st(a.lie_mc + (int64_t)q * a.d_pad + i0, l);
+        else
+          for (int r = 0; r < a.world; ++r) afl_st4(a.lie[r] + (int64_t)q * a.d_pad + i0, l);
       }
     }
   }
@@ -233,11 +270,12 @@ extern "C" {
 // Fused multi-GPU FedAvg (+ LIE moments), two levels in one kernel.  local_rows [CL][d_pad] and weights/member cover
 // the LOCAL clients; part/glob/lie/sig are host arrays of `world` peer-mapped device pointers (part: [1+2A][d_pad]
 // per rank).  ctrl: local device memory, 4 x uint32 {grid_ctr, go_flag, err, pad}, zero-initialised once.  epoch must
-// increase by one per call on every rank.  A <= 4 per call.
+// increase by one per call on every rank.  A <= 4 per call.  part_mc / glob_mc / lie_mc: NVLS multicast addresses of the
+// same symmetric buffers (null => P2P loads / stores); with them phase 1 uses multimem.ld_reduce / multimem.st.
 int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int64_t d_pad, int world, int rank,
                      float* const* part, float* const* glob, float* const* lie, uint32_t* const* sig, uint32_t epoch,
                      int A, const float* ref, const float* member, const float* kcount, const float* z, int strict_k1,
-                     float* local_rows_out, uint32_t* ctrl, void* stream) {
+                     float* local_rows_out, uint32_t* ctrl, float* part_mc, float* glob_mc, float* lie_mc, void* stream) {
   AFL_CHECK_ARG(world >= 1 && world <= kMaxWorld, "afl_fedavg_fused: world size must be 1..16");
   AFL_CHECK_ARG(d_pad % (4 * (int64_t)world) == 0, "afl_fedavg_fused: d_pad must be divisible by 4*world");
   AFL_CHECK_ARG(A >= 0 && A <= AFL_MAX_ATT, "afl_fedavg_fused: at most 4 moment sets per call");
@@ -251,6 +289,7 @@ int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int6
     a.lie[r] = (r < world && lie) ? lie[r] : nullptr;
     a.sig[r] = r < world ? sig[r] : nullptr;
   }
+  a.part_mc = part_mc; a.glob_mc = glob_mc; a.lie_mc = (lie && A > 0) ? lie_mc : nullptr;
   a.world = world; a.rank = rank; a.epoch = epoch; a.A = A; a.ref = ref; a.member = member; a.kcount = kcount;
   a.z = z; a.strict_k1 = strict_k1; a.local_rows_out = local_rows_out;
   a.grid_ctr = ctrl; a.go_flag = ctrl + 1; a.err = reinterpret_cast<int*>(ctrl + 2);

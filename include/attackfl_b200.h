@@ -45,11 +45,13 @@ int afl_fedavg(const float* rows, const float* weights, int C, int64_t d_pad, fl
  * the G partials through peer-mapped pointers (part [world], each [1+2A][d_pad]), stores the result into every
  * rank's global buffer (glob [world]) and the LIE rows of up to 4 attackers (lie [world], [A][d_pad]), second barrier
  * (sig [world]: symmetric uint32 buffers, st.release.sys / ld.acquire.sys) and fan-out to local_rows_out.
- * ctrl: 4 zero-initialised local uint32 {grid counter, go flag, error, pad}; epoch increases by 1 per call. */
+ * ctrl: 4 zero-initialised local uint32 {grid counter, go flag, error, pad}; epoch increases by 1 per call.
+ * part_mc / glob_mc / lie_mc: NVLS multicast addresses of the same buffers (null: P2P); when given, the slice reduce is
+ * multimem.ld_reduce (in-switch sum) and the broadcast is multimem.st. */
 int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int64_t d_pad, int world, int rank,
                      float* const* part, float* const* glob, float* const* lie, uint32_t* const* sig, uint32_t epoch,
                      int A, const float* ref, const float* member, const float* kcount, const float* z, int strict_k1,
-                     float* local_rows_out, uint32_t* ctrl, void* stream);
+                     float* local_rows_out, uint32_t* ctrl, float* part_mc, float* glob_mc, float* lie_mc, void* stream);
 
 /* K4 — gamma bisection on the (k+2)x(k+2) Gram matrix of [g_1-c..g_k-c, mu-c, p] (src/Utils.py:115-130;
  * rule 0 = Min-Max / Opt-Fang, 1 = Min-Sum; exclude_first reproduces the aliasing of genuine model 0,
