@@ -515,6 +515,8 @@ AFL_DEV void afl_gru_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
 template <int L>
 AFL_DEV void afl_conv_fwd_t(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int Co = op.N, Ci = op.K, S = t.S;
+  constexpr int CB = 8;                      // input channels per weight chunk: 24 floats = 6 x 128-bit loads in flight
+  const bool vec = (Ci % CB) == 0 && (op.w & 3) == 0;
   for (int it = tid; it < S * Co; it += nt) {
     const int co = it % Co, s = it / Co;
     const float* wr = t.w + op.w + (int64_t)co * Ci * 3;
@@ -523,15 +525,32 @@ AFL_DEV void afl_conv_fwd_t(const AflOp& op, const AflTile& t, int tid, int nt) 
     const float bias = t.w[op.b + co];
 #pragma unroll
     for (int l = 0; l < L; ++l) acc[l] = bias;
-    for (int ci = 0; ci < Ci; ++ci) {
-      const float w0 = wr[ci * 3], w1 = wr[ci * 3 + 1], w2 = wr[ci * 3 + 2];
-      const float* xr = xs + ci * op.in_cs;
-      float xm = 0.f, xc = xr[0];
+    for (int c0 = 0; c0 < Ci; c0 += CB) {
+      float wv[3 * CB];
+      const int cn = AFL_MIN(CB, Ci - c0);
+      if (vec) {
 #pragma unroll
-      for (int l = 0; l < L; ++l) {
-        const float xp = (l + 1 < L) ? xr[l + 1] : 0.f;
-        acc[l] += w0 * xm + w1 * xc + w2 * xp;
-        xm = xc; xc = xp;
+        for (int q = 0; q < 3 * CB / 4; ++q) {
+          const float4 v = *reinterpret_cast<const float4*>(wr + c0 * 3 + 4 * q);
+          wv[4 * q] = v.x; wv[4 * q + 1] = v.y; wv[4 * q + 2] = v.z; wv[4 * q + 3] = v.w;
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 3 * CB; ++q) wv[q] = q < 3 * cn ? wr[c0 * 3 + q] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < CB; ++j) {
+        if (j < cn) {
+          const float w0 = wv[3 * j], w1 = wv[3 * j + 1], w2 = wv[3 * j + 2];
+          const float* xr = xs + (c0 + j) * op.in_cs;
+          float xm = 0.f, xc = xr[0];
+#pragma unroll
+          for (int l = 0; l < L; ++l) {
+            const float xp = (l + 1 < L) ? xr[l + 1] : 0.f;
+            acc[l] += w0 * xm + w1 * xc + w2 * xp;
+            xm = xc; xc = xp;
+          }
+        }
       }
     }
     float* yr = t.pool + op.out + s * op.out_ld + co * op.out_cs;
@@ -555,7 +574,7 @@ AFL_DEV void afl_conv_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt
   const int Co = op.N, Ci = op.K, S = t.S;
   const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
   const int n_dx = need_dx ? S * Ci : 0;
-  const int n_dw = Co * Ci;
+  const int n_dw = ((Co + 3) / 4) * Ci;
   const int total = n_dx + n_dw + Co;
   for (int it = tid; it < total; it += nt) {
     if (it < n_dx) {
@@ -565,40 +584,65 @@ AFL_DEV void afl_conv_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt
       float acc[L];
 #pragma unroll
       for (int l = 0; l < L; ++l) acc[l] = 0.f;
-      for (int co = 0; co < Co; ++co) {
-        const float* wr = t.w + op.w + ((int64_t)co * Ci + ci) * 3;
-        const float w0 = wr[0], w1 = wr[1], w2 = wr[2];
-        const float* dr = dzs + co * op.out_cs;
-        float dm = 0.f, dc = dr[0];
+      constexpr int CB = 8;                  // output channels per chunk: 24 scalar weight loads in flight
+      for (int co0 = 0; co0 < Co; co0 += CB) {
+        float wv[3 * CB];
+        const int cn = AFL_MIN(CB, Co - co0);
 #pragma unroll
-        for (int l = 0; l < L; ++l) {
-          const float dp = (l + 1 < L) ? dr[l + 1] : 0.f;
-          acc[l] += w0 * dp + w1 * dc + w2 * dm;
-          dm = dc; dc = dp;
+        for (int j = 0; j < CB; ++j) {
+          const float* wr = t.w + op.w + ((int64_t)(co0 + (j < cn ? j : 0)) * Ci + ci) * 3;
+          wv[3 * j] = wr[0]; wv[3 * j + 1] = wr[1]; wv[3 * j + 2] = wr[2];
+        }
+#pragma unroll
+        for (int j = 0; j < CB; ++j) {
+          if (j < cn) {
+            const float w0 = wv[3 * j], w1 = wv[3 * j + 1], w2 = wv[3 * j + 2];
+            const float* dr = dzs + (co0 + j) * op.out_cs;
+            float dm = 0.f, dc = dr[0];
+#pragma unroll
+            for (int l = 0; l < L; ++l) {
+              const float dp = (l + 1 < L) ? dr[l + 1] : 0.f;
+              acc[l] += w0 * dp + w1 * dc + w2 * dm;
+              dm = dc; dc = dp;
+            }
+          }
         }
       }
       float* gx = t.pool + op.g_in0 + s * op.in0_ld + ci * op.in_cs;
 #pragma unroll
       for (int l = 0; l < L; ++l) afl_store(gx + l, acc[l], op.flags & AFL_F_ACC0);
     } else if (it < n_dx + n_dw) {
-      // dW[co][ci][k] = sum_s sum_l dz[s][co][l] x[s][ci][l+k-1]
+      // dW[co0..co0+3][ci][k] = sum_s sum_l dz[s][co][l] x[s][ci][l+k-1]: one x row feeds 4 output channels
       const int j2 = it - n_dx;
-      const int ci = j2 % Ci, co = j2 / Ci;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+      const int ci = j2 % Ci, cq = j2 / Ci;
+      const int co0 = cq * 4;
+      float a[4][3];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { a[q][0] = 0.f; a[q][1] = 0.f; a[q][2] = 0.f; }
       for (int s = 0; s < S; ++s) {
-        const float* dr = t.pool + op.g_out + s * op.out_ld + co * op.out_cs;
         const float* xr = t.pool + op.in0 + s * op.in0_ld + ci * op.in_cs;
+        const float* d0 = t.pool + op.g_out + s * op.out_ld + co0 * op.out_cs;
         float xm = 0.f, xc = xr[0];
 #pragma unroll
         for (int l = 0; l < L; ++l) {
           const float xp = (l + 1 < L) ? xr[l + 1] : 0.f;
-          const float d = dr[l];
-          a0 += d * xm; a1 += d * xc; a2 += d * xp;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (co0 + q < Co) {
+              const float d = d0[q * op.out_cs + l];
+              a[q][0] += d * xm; a[q][1] += d * xc; a[q][2] += d * xp;
+            }
+          }
           xm = xc; xc = xp;
         }
       }
-      float* g = t.gw + op.w + ((int64_t)co * Ci + ci) * 3;
-      afl_store(g, a0, t.accumulate); afl_store(g + 1, a1, t.accumulate); afl_store(g + 2, a2, t.accumulate);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (co0 + q < Co) {
+          float* g = t.gw + op.w + ((int64_t)(co0 + q) * Ci + ci) * 3;
+          afl_store(g, a[q][0], t.accumulate); afl_store(g + 1, a[q][1], t.accumulate); afl_store(g + 2, a[q][2], t.accumulate);
+        }
+      }
     } else {
       const int co = it - n_dx - n_dw;
       float a = 0.f;
@@ -617,28 +661,37 @@ AFL_DEV void afl_pool_bounds(int L, int j, int& a, int& b) { a = (j * L) / 4; b 
 
 AFL_DEV void afl_pool_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int C = op.N, S = t.S, L = op.L;
-  for (int it = tid; it < S * C * 4; it += nt) {
-    const int j = it & 3, r = it >> 2, c = r % C, s = r / C;
-    int a, b; afl_pool_bounds(L, j, a, b);
+  for (int it = tid; it < S * C; it += nt) {
+    const int c = it % C, s = it / C;
     const float* xr = t.pool + op.in0 + s * op.in0_ld + c * op.in_cs;
-    float sum = 0.f;
-    for (int l = a; l < b; ++l) sum += xr[l];
-    const float y = sum / (float)(b - a) * afl_drop_scale(t, op, s, (uint32_t)(c * 4 + j));
-    t.pool[op.out + s * op.out_ld + c * 4 + j] = y;
+    const float4 d = afl_drop_scale4(t, op, s, (uint32_t)(c * 4));      // one Philox call for the 4 windows
+    const float ds[4] = {d.x, d.y, d.z, d.w};
+    float* y = t.pool + op.out + s * op.out_ld + c * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int a, b; afl_pool_bounds(L, j, a, b);
+      float sum = 0.f;
+      for (int l = a; l < b; ++l) sum += xr[l];
+      y[j] = sum / (float)(b - a) * ds[j];
+    }
   }
 }
 
 AFL_DEV void afl_pool_bwd(const AflOp& op, const AflTile& t, int tid, int nt) {
   const int C = op.N, S = t.S, L = op.L;
-  for (int it = tid; it < S * C * L; it += nt) {
-    const int l = it % L, r = it / L, c = r % C, s = r / C;
-    float g = 0.f;
+  for (int it = tid; it < S * C; it += nt) {
+    const int c = it % C, s = it / C;
+    const float4 d = afl_drop_scale4(t, op, s, (uint32_t)(c * 4));
+    const float* go = t.pool + op.g_out + s * op.out_ld + c * 4;
+    float gj[4] = {go[0] * d.x, go[1] * d.y, go[2] * d.z, go[3] * d.w};
+    float* gi = t.pool + op.g_in0 + s * op.in0_ld + c * op.in_cs;
+    for (int l = 0; l < L; ++l) gi[l] = 0.f;
+#pragma unroll
     for (int j = 0; j < 4; ++j) {
       int a, b; afl_pool_bounds(L, j, a, b);
-      if (l >= a && l < b)
-        g += t.pool[op.g_out + s * op.out_ld + c * 4 + j] * afl_drop_scale(t, op, s, (uint32_t)(c * 4 + j)) / (float)(b - a);
+      const float v = gj[j] / (float)(b - a);
+      for (int l = a; l < b; ++l) gi[l] += v;
     }
-    t.pool[op.g_in0 + s * op.in0_ld + c * op.in_cs + l] = g;
   }
 }
 
