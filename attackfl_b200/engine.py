@@ -370,6 +370,26 @@ class Federation:
                     self.crafted[sp.index] = atk.lie_attack(rows_all[subsets[sp.index]], float((sp.attack_args or [0.74])[0]),
                                                             a_cfg.strict_reference)
                     self.crafted_own[sp.index] = False
+        gram_specs = [sp for sp in attackers if sp.attack_mode in GRAM_MODES]
+        if gram_specs and rows_all is None:
+            # fused multi-GPU path: K-slice ownership, rows are read in place over NVLink (parallel/symm.py)
+            fc = self.fused_comm
+            fc._ensure_gram_buffers(len(gram_specs))
+            for slot, sp in enumerate(gram_specs):
+                sub_idx = subsets[sp.index]
+                if len(sub_idx) <= 1:
+                    self.crafted_own[sp.index] = True
+                    continue
+                cen = center if center is not None else self.global_row
+                fc.gram_attack(slot, sub_idx, sp.attack_mode, cen.contiguous(), a_cfg.search == "paper")
+                info[f"gamma_{sp.index}"] = fc._last_gamma
+                self.crafted_own[sp.index] = False
+            torch.cuda.synchronize(self.device)
+            self.ctx.barrier()                                  # every rank's slice has landed in every crafted row
+            for slot, sp in enumerate(gram_specs):
+                if not self.crafted_own.get(sp.index, False):
+                    self.crafted[sp.index] = fc.craft_sym[slot].clone()
+            return info
         for sp in attackers:
             if sp.attack_mode not in GRAM_MODES:
                 continue
@@ -654,7 +674,9 @@ class Federation:
         reporting = list(starting)
         info: Dict[str, object] = {}
         fused = self.fused_comm is not None and self.mode == "fedavg"
-        need_gather = (not fused) or any(sp.attack and sp.attack_mode in GRAM_MODES for sp in self.specs)
+        gram_sliced = fused and self.cfg.attack.metric == "flat" and self.have_global
+        need_gather = (not fused) or (any(sp.attack and sp.attack_mode in GRAM_MODES for sp in self.specs)
+                                      and not gram_sliced)
         rows_all = None
         if need_gather:
             with self.timer.phase("gather"):

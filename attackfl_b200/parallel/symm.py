@@ -106,6 +106,48 @@ class FusedComm:
             out = self.lie[:A].clone()
         return out
 
+    # ------------------------------------------------------------------ K3 multi-GPU: Gram attacks by K-slice ownership
+    def _ensure_gram_buffers(self, n_attackers: int) -> None:
+        import torch.distributed._symmetric_memory as symm_mem
+        if getattr(self, "craft_sym", None) is not None and self.craft_sym.shape[0] >= n_attackers:
+            return
+        fed = self.fed
+        self.craft_sym = symm_mem.empty(max(n_attackers, 1), fed.D, dtype=torch.float32, device=fed.device)
+        self.craft_sym.zero_()
+        self.h_craft = symm_mem.rendezvous(self.craft_sym, dist.group.WORLD)
+        torch.cuda.synchronize(fed.device)
+        dist.barrier()
+
+    def gram_attack(self, slot: int, subset: List[int], mode: str, center: torch.Tensor, paper: bool) -> torch.Tensor:
+        """Min-Max / Min-Sum / Opt-Fang for one attacker without gathering any row: every rank handles its K-slice
+        (rows pulled over NVLink inside the moments kernel, tcgen05 Gram on the slice), the (k+2)^2 partial Grams are
+        summed across ranks, the gamma search runs replicated on the device, and the crafted slice is stored into every
+        rank's copy of the attacker's crafted row.  Returns this rank's full crafted row (view of symmetric memory)."""
+        from ..ops import flat, gram_native
+        fed = self.fed
+        dev = fed.device
+        lib = native.cuda_lib()
+        D, G, k = fed.D, self.world, len(subset)
+        sl = D // G
+        lo, hi = self.rank * sl, (self.rank + 1) * sl
+        ptrs = torch.tensor([int(self.h_rows.buffer_ptrs[c // self.cpg]) + (c % self.cpg) * D * 4 for c in subset],
+                            dtype=torch.int64, device=dev)
+        ops = torch.empty(k + 2, sl, dtype=torch.float32, device=dev)
+        mu, p = torch.empty(sl, dtype=torch.float32, device=dev), torch.empty(sl, dtype=torch.float32, device=dev)
+        rc = lib.afl_slice_moments(ptr(ptrs), ctypes.c_int(k), ptr(center), ctypes.c_int64(lo), ctypes.c_int64(hi),
+                                   ctypes.c_int64(sl), ctypes.c_int(1 if mode == "Opt-Fang" else 0), ptr(ops), ptr(mu),
+                                   ptr(p), stream_ptr(ops))
+        check(lib, rc, "afl_slice_moments")
+        g = gram_native.gram_tcgen05(ops, fed.cfg.attack.gram_precision if fed.cfg.attack.gram_precision != "fp32" else "tf32")
+        dist.all_reduce(g)                                   # (k+2)^2 floats: the only cross-rank traffic besides the rows
+        g4 = flat.gamma_search(g, k, "sum" if mode == "Min-Sum" else "max", True, paper)
+        dst = (ctypes.c_void_p * G)(*[int(b) + slot * D * 4 for b in self.h_craft.buffer_ptrs])
+        rc = lib.afl_craft_scatter(dst, ctypes.c_int(G), ptr(mu), ptr(p), ptr(g4), ctypes.c_int64(lo), ctypes.c_int64(hi),
+                                   stream_ptr(ops))
+        check(lib, rc, "afl_craft_scatter")
+        self._last_gamma = g4
+        return self.craft_sym[slot]
+
     def check_error(self) -> None:
         if int(self.ctrl[2].item()) != 0:
             raise RuntimeError("fused collective timed out waiting for a peer rank")

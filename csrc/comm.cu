@@ -263,9 +263,82 @@ __global__ void __launch_bounds__(kThreads) fedavg_fused_kernel(FusedArgs a) {
   }
 }
 
+// K3 multi-GPU, step 1: for the owned K-slice [lo, hi) pull the k genuine rows from wherever they live (peer-mapped
+// pointers => P2P loads over NVLink), and in the same pass form mu, sigma (unbiased, shifted sums) and the centred
+// operand rows of the Gram GEMM:  out[j] = x_j - c (j < k), out[k] = mu - c, out[k+1] = p (sigma, or sign(mu)).
+// out: [k+2][ld] fp32 (ld >= hi-lo, multiple of 4); mu_out / p_out: [ld] (kept for the craft step).
+__global__ void __launch_bounds__(kThreads) slice_moments_kernel(const float* const* row_ptrs, int k, const float* center,
+                                                                 int64_t lo, int64_t hi, int64_t ld, int sign_mode,
+                                                                 float* out, float* mu_out, float* p_out) {
+  const int64_t n4 = (hi - lo) / 4;
+  for (int64_t q = (int64_t)blockIdx.x * kThreads + threadIdx.x; q < n4; q += (int64_t)gridDim.x * kThreads) {
+    const int64_t i = lo + 4 * q, o = 4 * q;
+    const float4 c = afl_ld4(center + i);
+    float4 s1 = afl_f4(0.f), s2 = afl_f4(0.f);
+    for (int j = 0; j < k; ++j) {
+      const float4 x = afl_ld4(row_ptrs[j] + i);
+      float4 d; AFL_F4_OP(d, x.x - c.x, x.y - c.y, x.z - c.z, x.w - c.w);
+      afl_st4(out + (int64_t)j * ld + o, d);
+      s1.x += d.x; s1.y += d.y; s1.z += d.z; s1.w += d.w;
+      s2.x += d.x * d.x; s2.y += d.y * d.y; s2.z += d.z * d.z; s2.w += d.w * d.w;
+    }
+    const float kf = (float)k;
+    float4 mc, sd, mu, p;
+#define AFL_M1(e) { mc.e = s1.e / kf; const float var = k > 1 ? (s2.e - s1.e * s1.e / kf) / (kf - 1.f) : 0.f; \
+      sd.e = sqrtf(var > 0.f ? var : 0.f); mu.e = c.e + mc.e; \
+      p.e = sign_mode ? (float)((mu.e > 0.f) - (mu.e < 0.f)) : sd.e; }
+    AFL_M1(x) AFL_M1(y) AFL_M1(z) AFL_M1(w)
+#undef AFL_M1
+    afl_st4(out + (int64_t)k * ld + o, mc);
+    afl_st4(out + (int64_t)(k + 1) * ld + o, p);
+    afl_st4(mu_out + o, mu);
+    afl_st4(p_out + o, p);
+  }
+}
+
+// step 3: crafted[lo:hi] = mu - gamma * p, stored into EVERY rank's crafted row (P2P stores); gamma from device memory
+struct ScatterArgs { float* dst[kMaxWorld]; int world; };
+__global__ void __launch_bounds__(kThreads) craft_scatter_kernel(ScatterArgs a, const float* mu, const float* p,
+                                                                 const float* gamma_ptr, int64_t lo, int64_t hi) {
+  const float gamma = gamma_ptr[0];
+  const int64_t n4 = (hi - lo) / 4;
+  for (int64_t q = (int64_t)blockIdx.x * kThreads + threadIdx.x; q < n4; q += (int64_t)gridDim.x * kThreads) {
+    const float4 m = afl_ld4(mu + 4 * q), d = afl_ld4(p + 4 * q);
+    float4 r; AFL_F4_OP(r, m.x - gamma * d.x, m.y - gamma * d.y, m.z - gamma * d.z, m.w - gamma * d.w);
+    for (int w = 0; w < a.world; ++w) afl_st4(a.dst[w] + lo + 4 * q, r);
+  }
+}
+
 }  // namespace
 
 extern "C" {
+
+int afl_slice_moments(const float* const* row_ptrs_dev, int k, const float* center, int64_t lo, int64_t hi, int64_t ld,
+                      int sign_mode, float* out, float* mu_out, float* p_out, void* stream) {
+  AFL_CHECK_ARG((hi - lo) % 4 == 0 && lo % 4 == 0 && ld % 4 == 0, "afl_slice_moments: slice bounds must be multiples of 4");
+  int64_t work = ((hi - lo) / 4 + kThreads - 1) / kThreads;
+  int grid = (int)(work < 4 * afl_rt::num_sms() ? work : 4 * afl_rt::num_sms());
+  if (grid < 1) grid = 1;
+  slice_moments_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(row_ptrs_dev, k, center, lo, hi, ld, sign_mode, out,
+                                                                    mu_out, p_out);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_slice_moments");
+}
+
+int afl_craft_scatter(float* const* dst, int world, const float* mu, const float* p, const float* gamma_dev, int64_t lo,
+                      int64_t hi, void* stream) {
+  AFL_CHECK_ARG(world >= 1 && world <= kMaxWorld, "afl_craft_scatter: world size must be 1..16");
+  ScatterArgs a;
+  for (int r = 0; r < kMaxWorld; ++r) a.dst[r] = r < world ? dst[r] : nullptr;
+  a.world = world;
+  int64_t work = ((hi - lo) / 4 + kThreads - 1) / kThreads;
+  int grid = (int)(work < 2 * afl_rt::num_sms() ? work : 2 * afl_rt::num_sms());
+  if (grid < 1) grid = 1;
+  craft_scatter_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(a, mu, p, gamma_dev, lo, hi);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_craft_scatter");
+}
+
 
 // Fused multi-GPU FedAvg (+ LIE moments), two levels in one kernel.  local_rows [CL][d_pad] and weights/member cover
 // the LOCAL clients; part/glob/lie/sig are host arrays of `world` peer-mapped device pointers (part: [1+2A][d_pad]

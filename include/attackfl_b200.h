@@ -53,6 +53,16 @@ int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int6
                      int A, const float* ref, const float* member, const float* kcount, const float* z, int strict_k1,
                      float* local_rows_out, uint32_t* ctrl, float* part_mc, float* glob_mc, float* lie_mc, void* stream);
 
+/* K3 multi-GPU — slice ownership of the Gram GEMM (src/Utils.py:83-98 mean/std + :108-113,142-147,176-185 pairwise
+ * distances): afl_slice_moments pulls the k genuine rows of the owned K-slice [lo,hi) through peer-mapped pointers
+ * (row_ptrs_dev [k], device array), forms mu / sigma / sign(mu) and writes the centred operand rows [k+2][ld] that
+ * feed afl_gram_tf32 on the slice; the (k+2)^2 partial Grams are summed across ranks; afl_craft_scatter then stores
+ * mu - gamma*p of the slice into every rank's crafted row (dst [world], peer-mapped). */
+int afl_slice_moments(const float* const* row_ptrs_dev, int k, const float* center, int64_t lo, int64_t hi, int64_t ld,
+                      int sign_mode, float* out, float* mu_out, float* p_out, void* stream);
+int afl_craft_scatter(float* const* dst, int world, const float* mu, const float* p, const float* gamma_dev, int64_t lo,
+                      int64_t hi, void* stream);
+
 /* K4 — gamma bisection on the (k+2)x(k+2) Gram matrix of [g_1-c..g_k-c, mu-c, p] (src/Utils.py:115-130;
  * rule 0 = Min-Max / Opt-Fang, 1 = Min-Sum; exclude_first reproduces the aliasing of genuine model 0,
  * paper=1 returns gamma_succ).  out4 = {gamma, gamma_succ, threshold, probes} in device memory. */
