@@ -161,6 +161,7 @@ def run_ours(args) -> dict:
     native.reset_launch_count()
     ev = []
     metrics = []
+    phases = {}
     for _ in range(args.steps):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -169,6 +170,8 @@ def run_ours(args) -> dict:
         e1.record()
         ev.append((e0, e1))
         metrics.append(r.metric)
+        for k, v in r.timings_ms.items():
+            phases[k] = phases.get(k, 0.0) + v / args.steps
         assert r.ok, "a timed round failed"
     torch.cuda.synchronize()
     launches = native.launch_count()
@@ -214,6 +217,7 @@ def run_ours(args) -> dict:
                 "h2d_bytes_per_step": int(pinned.numel() * 4),
                 "d2h_bytes_per_step": int(C * 3 * 4 + 8)},
         "gpu_launches": int(launches),
+        "phases_ms": {k: round(v, 3) for k, v in phases.items()},
         "roc_auc_last": metrics[-1],
     }
     fed.close()
