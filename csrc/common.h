@@ -20,6 +20,13 @@
 struct alignas(16) float4 { float x, y, z, w; };
 #endif
 
+// L2 -> L1 prefetch of one 128-byte line (device only; a no-op in the CPU twin)
+#if defined(__CUDA_ARCH__)
+#define AFL_PREFETCH_L1(ptr) asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr))
+#else
+#define AFL_PREFETCH_L1(ptr) ((void)0)
+#endif
+
 #define AFL_MIN(a, b) ((a) < (b) ? (a) : (b))
 #define AFL_MAX(a, b) ((a) > (b) ? (a) : (b))
 

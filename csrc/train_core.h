@@ -790,9 +790,36 @@ AFL_DEV void afl_bwd_phases(int kind, const AflOp& op, const AflTile& t, int tid
   }
 }
 
+// While a group computes, its threads pull the parameters of the group that runs next (forward: following group,
+// backward: preceding group) from L2 into L1, 128 bytes per thread-iteration, so that the next phase does not start
+// with a cold weight fetch (~600-800 cycles per dependent chunk).  L1 is only invalidated at the per-step barriers.
+// Measured on B200 (profiles/train_kernel_experiments.md): this made the step SLOWER (87 -> 102 us), the prefetch
+// instructions cost more issue slots than the latency they hide; it is compiled out unless AFL_ENABLE_PREFETCH is set.
+AFL_DEV void afl_prefetch_params(const AflOp* ops, int first, int count, const AflTile& t, int tid, int nt) {
+#if defined(__CUDA_ARCH__) && defined(AFL_ENABLE_PREFETCH)
+  for (int j = 0; j < count; ++j) {
+    const AflOp& op = ops[first + j];
+    int n_w = 0;
+    if (op.kind == AFL_OP_LINEAR) n_w = op.N * op.K;
+    else if (op.kind == AFL_OP_CONV) n_w = op.N * op.K * 3;
+    else if (op.kind == AFL_OP_LN) n_w = op.N;
+    if (op.w >= 0 && n_w > 0)
+      for (int l = tid; l * 32 < n_w; l += nt) AFL_PREFETCH_L1(t.w + op.w + l * 32);
+    if (op.b >= 0 && tid < (op.N + 31) / 32) AFL_PREFETCH_L1(t.w + op.b + tid * 32);
+    if (op.w2 >= 0 && tid < 4) AFL_PREFETCH_L1(t.w + op.w2 + tid * 32);
+  }
+#else
+  (void)ops; (void)first; (void)count; (void)t; (void)tid; (void)nt;
+#endif
+}
+
 AFL_DEV void afl_run_forward(const AflOp* ops, int n_ops, const AflTile& t, int tid, int nt) {
   for (int i = 0; i < n_ops;) {
     const int g = ops[i].grp_size > 1 ? ops[i].grp_size : 1;
+    if (i + g < n_ops) {
+      const int ng = ops[i + g].grp_size > 1 ? ops[i + g].grp_size : 1;
+      afl_prefetch_params(ops, i + g, ng, t, tid, nt);
+    }
     const int per = nt / g > 0 ? nt / g : 1;                 // threads per member (nt = 1 on the CPU twin)
     if (nt >= g) {
       const int sub = tid / per;
@@ -810,6 +837,11 @@ AFL_DEV void afl_run_backward(const AflOp* ops, int n_ops, const AflTile& t, int
   for (int i = n_ops - 1; i >= 0;) {
     const int st = ops[i].grp_start;
     const int g = ops[st].grp_size > 1 ? ops[st].grp_size : 1;
+    if (st > 0) {
+      const int pst = ops[st - 1].grp_start;
+      const int pg = ops[pst].grp_size > 1 ? ops[pst].grp_size : 1;
+      afl_prefetch_params(ops, pst, pg, t, tid, nt);
+    }
     const int per = nt / g > 0 ? nt / g : 1;
     if (nt >= g) {
       const int sub = tid / per;
