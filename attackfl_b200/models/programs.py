@@ -67,18 +67,20 @@ class Program:
     train: bool
     act_floats: int = 0
     grad_floats: int = 0
+    chain: bool = False          # planned for chain mode (no gradient-buffer reuse)
 
     def to(self, device) -> "Program":
         return Program(self.ops.to(device), self.n_ops, self.pool_floats, self.S, self.rec, self.model,
-                       self.train, self.act_floats, self.grad_floats)
+                       self.train, self.act_floats, self.grad_floats, self.chain)
 
     def smem_bytes(self, threads: int = 512) -> int:
-        return 4 * self.pool_floats + 4 * OP_WORDS * self.n_ops + 4 * (threads + 4)
+        table = 4 * OP_WORDS * self.n_ops * (1 + (self.S if self.chain else 0))
+        return 4 * self.pool_floats + table + 4 * (threads + 4)
 
 
 class Builder:
-    def __init__(self, layout: FlatLayout, S: int, train: bool = True):
-        self.layout, self.S, self.train = layout, S, train
+    def __init__(self, layout: FlatLayout, S: int, train: bool = True, reuse_grads: bool = True):
+        self.layout, self.S, self.train, self.reuse_grads = layout, S, train, reuse_grads
         self.roots: List[_Root] = []
         self.ops: List[Dict] = []
         self._sink: List[Dict] = self.ops
@@ -221,6 +223,10 @@ class Builder:
                 hi_t = hi_op["_group"][-1]["_idx"] if hi_op.get("_group") else hi_op["_idx"]
                 lo_t = lo_op["_group"][0]["_idx"] if lo_op.get("_group") else lo_op["_idx"]
                 live.append((hi_t, lo_t, rid))
+            if not self.reuse_grads:
+                # chain mode defers the parameter gradients to the end of the tile, so every gradient buffer must
+                # survive until then: give all of them the whole program as lifetime
+                live = [(len(self.ops), 0, rid) for _, _, rid in live]
             live.sort(reverse=True)
             placed: List[Tuple[int, int, int, int]] = []      # (goff, size, lo, hi)
             for hi, lo, rid in live:
@@ -374,12 +380,12 @@ SUPPORTED = tuple(DEFAULT_TILE)
 
 
 def build_program(model_name: str, layout: FlatLayout, S: Optional[int] = None, train: bool = True,
-                  dropout: bool = True, module: Optional[torch.nn.Module] = None) -> Program:
+                  dropout: bool = True, module: Optional[torch.nn.Module] = None, chain: bool = False) -> Program:
     """Program for one of the ICU models; ``module`` supplies non-default widths (scaled Transformer)."""
     if model_name not in SUPPORTED:
         raise ValueError(f"no native program for model '{model_name}'")
     S = S or DEFAULT_TILE[model_name]
-    bd = Builder(layout, S, train)
+    bd = Builder(layout, S, train, reuse_grads=not chain)
     use_dropout = dropout and train
     if model_name == "TransformerModel":
         d = layout.by_name["vitals_dense.weight"].shape[0]
@@ -391,4 +397,6 @@ def build_program(model_name: str, layout: FlatLayout, S: Optional[int] = None, 
         _rnn(bd, H, use_dropout)
     else:
         _cnn(bd, use_dropout)
-    return bd.finish(model_name)
+    prog = bd.finish(model_name)
+    prog.chain = bool(chain and train)
+    return prog

@@ -32,7 +32,8 @@ def capacity(program: Program, device) -> int:
         return 1 << 30
     lib = native.cuda_lib()
     with torch.cuda.device(device):
-        cap = int(lib.afl_train_capacity(c_i(program.pool_floats), c_i(program.n_ops)))
+        cap = int(lib.afl_train_capacity(c_i(program.pool_floats), c_i(program.n_ops),
+                                         c_i(program.S if program.chain else 0)))
     if cap <= 0:
         raise RuntimeError("training program does not fit in shared memory: "
                            + lib.afl_last_error().decode(errors="replace"))
@@ -118,7 +119,7 @@ def train_round(program: Program, plan: TrainPlan, w: torch.Tensor, m: torch.Ten
             c_i(batch), c_i(epochs), c_i(0 if optimizer == "adam" else 1), c_f(lr), c_f(betas[0]), c_f(betas[1]),
             c_f(eps), c_f(momentum), c_i(1 if clip_proper else 0), c_f(clip), c_u64(seed & (2 ** 64 - 1)),
             c_i(1 if dropout else 0), ptr(loss[c0:c1]), ptr(steps[c0:c1]), ptr(bar[c0:c1]), ptr(gnorm[c0:c1]),
-            stream_ptr(w))
+            c_i(1 if program.chain else 0), stream_ptr(w))
         check(lib, rc, "afl_train_round")
     return loss, steps
 

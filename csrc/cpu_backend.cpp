@@ -189,20 +189,25 @@ int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb
 }
 
 // ---------------------------------------------------------------------------------------- training
-int afl_train_capacity(int, int) { return 1 << 30; }
+int afl_train_capacity(int, int, int) { return 1 << 30; }
 
 int afl_train_round(const int32_t* ops_i, int n_ops, int pool_floats, float* w_all, float* m_all, float* v_all,
                     float* gpart_all, int64_t d_pad, const float* data, int rec, const int32_t* idx,
                     int64_t idx_stride_c, int64_t idx_stride_e, const int32_t* n_data, const int32_t* client_ids,
                     int n_clients, int G, int M, int S, int batch, int epochs, int opt_kind, float lr, float beta1,
                     float beta2, float eps, float momentum, int clip_proper, float clip, uint64_t seed, int dropout,
-                    float* loss_out, int32_t* steps_out, uint32_t*, float*, void*) {
+                    float* loss_out, int32_t* steps_out, uint32_t*, float*, int chain, void*) {
   CHECK_ARG(sizeof(AflOp) == 4 * AFL_OP_WORDS, "AflOp layout mismatch");
   CHECK_ARG(G >= 1 && M >= 1 && S >= 1 && G * M * S >= batch, "afl_train_round: G*M*S must cover the batch");
   CHECK_ARG(d_pad % (4 * (int64_t)G) == 0, "afl_train_round: d_pad must be divisible by 4*G");
   const AflOp* ops = reinterpret_cast<const AflOp*>(ops_i);
   float* pool = alloc_pool((size_t)pool_floats);
   if (!pool) { set_error("out of memory"); return -4; }
+  std::vector<AflOp> ops_s;
+  if (chain) {
+    ops_s.resize((size_t)S * n_ops);
+    for (int i = 0; i < S * n_ops; ++i) afl_shift_op(ops[i % n_ops], i / n_ops, ops_s[i]);
+  }
   for (int c = 0; c < n_clients; ++c) {
     float* w = w_all + (int64_t)c * d_pad;
     float* m = m_all + (int64_t)c * d_pad;
@@ -234,8 +239,12 @@ int afl_train_round(const int32_t* ops_i, int n_ops, int pool_floats, float* w_a
             if (nv == 0 && mt > 0) break;
             t.idx = idx_e + (int64_t)s * batch + base;
             t.n_valid = nv; t.sample_base = base; t.accumulate = mt > 0;
-            afl_run_forward(ops, n_ops, t, 0, 1);
-            afl_run_backward(ops, n_ops, t, 0, 1);
+            if (chain) {
+              afl_run_tile_chain(ops, ops_s.data(), n_ops, t, 0, 1);
+            } else {
+              afl_run_forward(ops, n_ops, t, 0, 1);
+              afl_run_backward(ops, n_ops, t, 0, 1);
+            }
           }
         }
         ++opt_steps;

@@ -31,6 +31,7 @@ struct TrainParams {
   uint32_t* bar;          // [C]
   float* gnorm;           // [C][2]
   int use_cluster;        // 1: the G blocks of a client form one thread-block cluster (hardware barrier)
+  int chain;              // 1: chain mode (per-sample warp teams + deferred parameter gradients)
 };
 
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
@@ -65,7 +66,8 @@ __global__ void __launch_bounds__(kThreads, 1) train_kernel(TrainParams P) {
   extern __shared__ float4 smem4[];
   float* pool = reinterpret_cast<float*>(smem4);
   AflOp* ops = reinterpret_cast<AflOp*>(pool + P.pool_floats);
-  float* red = reinterpret_cast<float*>(ops + P.n_ops);      // [kThreads] scratch, then loss_acc[2]
+  AflOp* ops_s = ops + P.n_ops;                               // chain mode: [S][n_ops] per-sample shifted programs
+  float* red = reinterpret_cast<float*>(ops_s + (P.chain ? P.S * P.n_ops : 0));   // [kThreads] scratch, loss_acc[2]
   float* loss_acc = red + kThreads;
   const int tid = threadIdx.x;
   const int c = blockIdx.x / P.G, g = blockIdx.x - c * P.G;
@@ -76,6 +78,10 @@ __global__ void __launch_bounds__(kThreads, 1) train_kernel(TrainParams P) {
     for (int i = tid; i < P.n_ops * AFL_OP_WORDS; i += kThreads) dst[i] = src[i];
     for (int i = tid; i < P.pool_floats; i += kThreads) pool[i] = 0.f;
     if (tid < 2) loss_acc[tid] = 0.f;
+    if (P.chain) {
+      __syncthreads();
+      for (int i = tid; i < P.S * P.n_ops; i += kThreads) afl_shift_op(ops[i % P.n_ops], i / P.n_ops, ops_s[i]);
+    }
   }
   float* gw = P.gpart + ((int64_t)c * P.G + g) * P.d_pad;
   for (int64_t i = tid; i < P.d_pad; i += kThreads) gw[i] = 0.f;
@@ -112,8 +118,12 @@ __global__ void __launch_bounds__(kThreads, 1) train_kernel(TrainParams P) {
         if (nv == 0 && mt > 0) break;            // tile 0 always runs so stale partials are overwritten
         t.idx = idx_e + (int64_t)s * P.batch + base;
         t.n_valid = nv; t.sample_base = base; t.accumulate = mt > 0;
-        afl_run_forward(ops, P.n_ops, t, tid, kThreads);
-        afl_run_backward(ops, P.n_ops, t, tid, kThreads);
+        if (P.chain) {
+          afl_run_tile_chain(ops, ops_s, P.n_ops, t, tid, kThreads);
+        } else {
+          afl_run_forward(ops, P.n_ops, t, tid, kThreads);
+          afl_run_backward(ops, P.n_ops, t, tid, kThreads);
+        }
       }
       if (P.G > 1) AFL_CLIENT_BARRIER();
 
@@ -188,8 +198,9 @@ __global__ void __launch_bounds__(kThreads, 1) infer_kernel(InferParams P) {
   }
 }
 
-size_t train_smem(int pool_floats, int n_ops) {
-  return sizeof(float) * (size_t)pool_floats + sizeof(AflOp) * (size_t)n_ops + sizeof(float) * (kThreads + 4);
+size_t train_smem(int pool_floats, int n_ops, int chain_S = 0) {
+  return sizeof(float) * (size_t)pool_floats + sizeof(AflOp) * (size_t)n_ops * (size_t)(1 + chain_S) +
+         sizeof(float) * (kThreads + 4);
 }
 
 }  // namespace
@@ -197,8 +208,8 @@ size_t train_smem(int pool_floats, int n_ops) {
 extern "C" {
 
 // Number of training blocks that can be co-resident on the current device for this program.
-int afl_train_capacity(int pool_floats, int n_ops) {
-  const size_t smem = train_smem(pool_floats, n_ops);
+int afl_train_capacity(int pool_floats, int n_ops, int chain_S) {
+  const size_t smem = train_smem(pool_floats, n_ops, chain_S);
   if ((int)smem > afl_rt::max_smem_optin()) { afl_rt::set_error("training pool needs %zu B shared memory", smem); return 0; }
   if (cudaFuncSetAttribute(train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
   int per_sm = 0;
@@ -211,12 +222,13 @@ int afl_train_round(const int32_t* ops_dev, int n_ops, int pool_floats, float* w
                     int64_t idx_stride_e, const int32_t* n_data, const int32_t* client_ids, int n_clients, int G,
                     int M, int S, int batch, int epochs, int opt_kind, float lr, float beta1, float beta2, float eps,
                     float momentum, int clip_proper, float clip, uint64_t seed, int dropout, float* loss_out,
-                    int32_t* steps_out, uint32_t* bar, float* gnorm, void* stream) {
+                    int32_t* steps_out, uint32_t* bar, float* gnorm, int chain, void* stream) {
   AFL_CHECK_ARG(sizeof(AflOp) == 4 * AFL_OP_WORDS, "AflOp layout mismatch");
+  AFL_CHECK_ARG(!chain || ((kThreads / 32) % S == 0 && S <= 15), "afl_train_round: chain mode needs S | 16 warps, S <= 15");
   AFL_CHECK_ARG(G >= 1 && M >= 1 && S >= 1 && G * M * S >= batch, "afl_train_round: G*M*S must cover the batch");
   AFL_CHECK_ARG(d_pad % (4 * (int64_t)G) == 0, "afl_train_round: d_pad must be divisible by 4*G");
-  const size_t smem = train_smem(pool_floats, n_ops);
-  const int cap = afl_train_capacity(pool_floats, n_ops);
+  const size_t smem = train_smem(pool_floats, n_ops, chain ? S : 0);
+  const int cap = afl_train_capacity(pool_floats, n_ops, chain ? S : 0);
   if (cap <= 0) return -2;
   if (n_clients * G > cap) {
     afl_rt::set_error("afl_train_round: %d blocks requested but only %d can be co-resident (chunk the clients)",
@@ -231,6 +243,7 @@ int afl_train_round(const int32_t* ops_dev, int n_ops, int pool_floats, float* w
   P.opt_kind = opt_kind; P.lr = lr; P.beta1 = beta1; P.beta2 = beta2; P.eps = eps; P.momentum = momentum;
   P.clip_proper = clip_proper; P.clip = clip; P.seed_lo = (uint32_t)seed; P.seed_hi = (uint32_t)(seed >> 32);
   P.dropout = dropout; P.loss_out = loss_out; P.steps_out = steps_out; P.bar = bar; P.gnorm = gnorm;
+  P.chain = chain ? 1 : 0;
   cudaStream_t st = (cudaStream_t)stream;
   AFL_CUDA(cudaMemsetAsync(bar, 0, sizeof(uint32_t) * (size_t)n_clients, st));
   AFL_CUDA(cudaMemsetAsync(gnorm, 0, sizeof(float) * 2 * (size_t)n_clients, st));

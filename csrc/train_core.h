@@ -32,6 +32,9 @@ enum AflFlags { AFL_F_ACC0 = 1, AFL_F_ACC1 = 2, AFL_F_NEED_GIN0 = 4, AFL_F_MASK_
 #define AFL_OP_WORDS 32
 #define AFL_LN_PARTS 8
 #define AFL_LN_EPS 1e-5f
+#define AFL_LN_ROW (2 * AFL_LN_PARTS + 1)   // per-sample scratch row of LN: 2P partial sums, then rstd
+#define AFL_PART_ACT 1     // backward parts: activation gradients (dX / dx) ...
+#define AFL_PART_PARAM 2   // ... and parameter gradients (dW, db, dgamma, dbeta, db_hh)
 
 // One instruction; 32 x int32 so Python can pack programs as a plain int32 array.
 struct AflOp {
@@ -198,7 +201,9 @@ AFL_DEV void afl_linear_fwd_t(const AflOp& op, const AflTile& t, int tid, int nt
 
 AFL_DEV void afl_linear_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
   // small tiles: 2 samples per thread so that every thread of the block has an item
-  if (t.S >= 16) afl_linear_fwd_t<4>(op, t, tid, nt); else afl_linear_fwd_t<2>(op, t, tid, nt);
+  if (t.S >= 16) afl_linear_fwd_t<4>(op, t, tid, nt);
+  else if (t.S >= 2) afl_linear_fwd_t<2>(op, t, tid, nt);
+  else afl_linear_fwd_t<1>(op, t, tid, nt);
 }
 
 // Phase A: turn dL/dout into dL/dz in place (dropout mask, activation derivative).
@@ -221,21 +226,22 @@ AFL_DEV void afl_linear_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt
 
 // Phase B: dX, dW, db from dz (three independent item ranges, one flat loop).
 template <int TS>
-AFL_DEV void afl_linear_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt) {
+AFL_DEV void afl_linear_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt, int parts) {
   const int N = op.N, K = op.K, S = t.S;
   const float* dz = t.pool + op.g_out;        // [S][.], row stride = out_ld (same layout as out)
   const int ldz = op.out_ld;
   const float* x = t.pool + op.in0;
   const int ldx = op.in0_ld;
   const int SG = (S + TS - 1) / TS;
-  const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
+  const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0 && (parts & AFL_PART_ACT);
   const int n_dx = need_dx ? K * SG : 0;
   const bool nvec = (N & 3) == 0 && (op.g_out & 3) == 0 && (ldz & 3) == 0;
   const bool kvec = (K & 3) == 0 && (op.in0 & 3) == 0 && (ldx & 3) == 0 && (op.w & 3) == 0;
   const bool tile44 = nvec && kvec;                       // 4(n) x 4(k) register tile for dW
   const int KQ = K >> 2;
-  const int n_dw = tile44 ? (N >> 2) * KQ : (nvec ? (N >> 2) * K : N * K);
-  const int n_db = op.b >= 0 ? N : 0;
+  const bool do_par = (parts & AFL_PART_PARAM) != 0;
+  const int n_dw = !do_par ? 0 : tile44 ? (N >> 2) * KQ : (nvec ? (N >> 2) * K : N * K);
+  const int n_db = (do_par && op.b >= 0) ? N : 0;
   const int total = n_dx + n_dw + n_db;
   for (int it = tid; it < total; it += nt) {
     if (it < n_dx) {
@@ -323,8 +329,11 @@ AFL_DEV void afl_linear_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int 
   }
 }
 
-AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
-  if (t.S >= 16) afl_linear_bwd_b_t<4>(op, t, tid, nt); else afl_linear_bwd_b_t<2>(op, t, tid, nt);
+AFL_DEV void afl_linear_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt,
+                              int parts = AFL_PART_ACT | AFL_PART_PARAM) {
+  if (t.S >= 16) afl_linear_bwd_b_t<4>(op, t, tid, nt, parts);
+  else if (t.S >= 2) afl_linear_bwd_b_t<2>(op, t, tid, nt, parts);
+  else afl_linear_bwd_b_t<1>(op, t, tid, nt, parts);
 }
 
 // ----------------------------------------------------------------------------------------- LAYERNORM
@@ -358,8 +367,8 @@ AFL_DEV void afl_ln_fwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
         sum += x; sq += x * x;
       }
     }
-    t.pool[op.aux2 + s * 2 * P + 2 * part] = sum;
-    t.pool[op.aux2 + s * 2 * P + 2 * part + 1] = sq;
+    t.pool[op.aux2 + s * AFL_LN_ROW + 2 * part] = sum;
+    t.pool[op.aux2 + s * AFL_LN_ROW + 2 * part + 1] = sq;
   }
 }
 
@@ -373,8 +382,8 @@ AFL_DEV void afl_ln_fwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
     float sum = 0.f, sq = 0.f;
 #pragma unroll
     for (int q = 0; q < P; ++q) {
-      sum += t.pool[op.aux2 + s * 2 * P + 2 * q];
-      sq += t.pool[op.aux2 + s * 2 * P + 2 * q + 1];
+      sum += t.pool[op.aux2 + s * AFL_LN_ROW + 2 * q];
+      sq += t.pool[op.aux2 + s * AFL_LN_ROW + 2 * q + 1];
     }
     const float mean = sum / (float)N;
     float var = sq / (float)N - mean * mean;
@@ -393,16 +402,17 @@ AFL_DEV void afl_ln_fwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
       t.pool[op.aux + s * N + n] = xh;
       t.pool[op.out + s * op.out_ld + n] = xh * t.w[op.w + n] + t.w[op.b + n];
     }
-    if (n == 0) t.pool[op.aux2 + S * 2 * P + s] = rstd;
+    if (n == 0) t.pool[op.aux2 + s * AFL_LN_ROW + 2 * P] = rstd;
   }
 }
 
 // backward phase A: per-row partial sums of dxhat and dxhat*xhat, plus dgamma / dbeta
-AFL_DEV void afl_ln_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
+AFL_DEV void afl_ln_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt, int parts = AFL_PART_ACT | AFL_PART_PARAM) {
   const int N = op.N, S = t.S, P = AFL_LN_PARTS;
   const int chunk = (N + P - 1) / P;
-  const int n_part = S * P;
-  for (int it = tid; it < n_part + N; it += nt) {
+  const int n_part = (parts & AFL_PART_ACT) ? S * P : 0;
+  const int n_par = (parts & AFL_PART_PARAM) ? N : 0;
+  for (int it = tid; it < n_part + n_par; it += nt) {
     if (it < n_part) {
       const int s = it / P, part = it - s * P;
       const int n0 = part * chunk, n1 = AFL_MIN(N, n0 + chunk);
@@ -411,8 +421,8 @@ AFL_DEV void afl_ln_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) {
         const float dxh = t.pool[op.g_out + s * op.out_ld + n] * t.w[op.w + n];
         a += dxh; b += dxh * t.pool[op.aux + s * N + n];
       }
-      t.pool[op.aux2 + s * 2 * P + 2 * part] = a;
-      t.pool[op.aux2 + s * 2 * P + 2 * part + 1] = b;
+      t.pool[op.aux2 + s * AFL_LN_ROW + 2 * part] = a;
+      t.pool[op.aux2 + s * AFL_LN_ROW + 2 * part + 1] = b;
     } else {
       const int n = it - n_part;
       float dg = 0.f, db = 0.f;
@@ -437,10 +447,10 @@ AFL_DEV void afl_ln_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
     float a = 0.f, b = 0.f;
 #pragma unroll
     for (int q = 0; q < P; ++q) {
-      a += t.pool[op.aux2 + s * 2 * P + 2 * q];
-      b += t.pool[op.aux2 + s * 2 * P + 2 * q + 1];
+      a += t.pool[op.aux2 + s * AFL_LN_ROW + 2 * q];
+      b += t.pool[op.aux2 + s * AFL_LN_ROW + 2 * q + 1];
     }
-    const float rstd = t.pool[op.aux2 + S * 2 * P + s];
+    const float rstd = t.pool[op.aux2 + s * AFL_LN_ROW + 2 * P];
     const float m1 = a / (float)N, m2 = b / (float)N;
     if (v4) {
       const float4 g = *reinterpret_cast<const float4*>(t.pool + op.g_out + s * op.out_ld + n);
@@ -570,12 +580,13 @@ AFL_DEV void afl_conv_bwd_a(const AflOp& op, const AflTile& t, int tid, int nt) 
 }
 
 template <int L>
-AFL_DEV void afl_conv_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt) {
+AFL_DEV void afl_conv_bwd_b_t(const AflOp& op, const AflTile& t, int tid, int nt, int parts) {
   const int Co = op.N, Ci = op.K, S = t.S;
-  const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0;
+  const bool need_dx = (op.flags & AFL_F_NEED_GIN0) != 0 && (parts & AFL_PART_ACT);
+  const bool do_par = (parts & AFL_PART_PARAM) != 0;
   const int n_dx = need_dx ? S * Ci : 0;
-  const int n_dw = ((Co + 3) / 4) * Ci;
-  const int total = n_dx + n_dw + Co;
+  const int n_dw = do_par ? ((Co + 3) / 4) * Ci : 0;
+  const int total = n_dx + n_dw + (do_par ? Co : 0);
   for (int it = tid; it < total; it += nt) {
     if (it < n_dx) {
       // dx[s][ci][j] = sum_co sum_k w[co][ci][k] dz[s][co][j-k+1]
@@ -756,9 +767,9 @@ AFL_DEV void afl_conv_fwd(const AflOp& op, const AflTile& t, int tid, int nt) {
   if (op.L == 7) afl_conv_fwd_t<7>(op, t, tid, nt);
   else if (op.L == 16) afl_conv_fwd_t<16>(op, t, tid, nt);
 }
-AFL_DEV void afl_conv_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt) {
-  if (op.L == 7) afl_conv_bwd_b_t<7>(op, t, tid, nt);
-  else if (op.L == 16) afl_conv_bwd_b_t<16>(op, t, tid, nt);
+AFL_DEV void afl_conv_bwd_b(const AflOp& op, const AflTile& t, int tid, int nt, int parts = AFL_PART_ACT | AFL_PART_PARAM) {
+  if (op.L == 7) afl_conv_bwd_b_t<7>(op, t, tid, nt, parts);
+  else if (op.L == 16) afl_conv_bwd_b_t<16>(op, t, tid, nt, parts);
 }
 
 // Ops of one *group* are mutually independent (e.g. the vitals and labs branches); the block's threads are split
@@ -853,6 +864,148 @@ AFL_DEV void afl_run_backward(const AflOp* ops, int n_ops, const AflTile& t, int
     AFL_SYNC();
     i = st - 1;
   }
+}
+
+// ----------------------------------------------------------------------------------------- chain mode
+// Every forward op and every activation-gradient op works on one sample at a time, so a *team* (the warps assigned to
+// one sample) can carry that sample through the whole layer chain with team-local synchronisation only: one warp per
+// branch while the program is in a 2-member group (vitals | labs), the whole team for the single ops (LOAD, head, BCE).
+// Only parameter gradients need all samples; they are computed afterwards in one barrier-free block-wide pass
+// (afl_param_grads).  Block mode needs ~45 block-wide barrier intervals per optimiser step; chain mode needs 2.
+// ops_s: per-sample copy of the program with every pool offset shifted to that sample (afl_shift_op), so the unchanged
+// op functions run on a 1-sample tile.
+AFL_DEV void afl_shift_op(const AflOp& src, int s, AflOp& o) {
+  o = src;
+  if (src.in0 >= 0) o.in0 += s * src.in0_ld;
+  if (src.in1 >= 0) o.in1 += s * src.in1_ld;
+  if (src.out >= 0) o.out += s * src.out_ld;
+  o.g_out += s * src.out_ld;
+  o.g_in0 += s * src.in0_ld;
+  o.g_in1 += s * src.in1_ld;
+  if (src.kind == AFL_OP_LOAD) { if (src.aux >= 0) o.aux += s * src.aux2; }
+  else {
+    if (src.aux >= 0) o.aux += s * src.N;
+    if (src.kind == AFL_OP_LN && src.aux2 >= 0) o.aux2 += s * AFL_LN_ROW;
+  }
+}
+
+// team barrier: one warp => __syncwarp; several warps => named barrier `bar_id` (1..15) over `team` threads
+AFL_DEV void afl_team_sync(int team, int bar_id) {
+#if defined(__CUDA_ARCH__)
+  if (team <= 32) __syncwarp();
+  else asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(team) : "memory");
+#else
+  (void)team; (void)bar_id;
+#endif
+}
+
+AFL_DEV void afl_chain_fwd_op(const AflOp& op, const AflTile& t, int tid, int nt, int bar_id) {
+  switch (op.kind) {
+    case AFL_OP_LOAD: afl_load_fwd(op, t, tid, nt); break;
+    case AFL_OP_LINEAR: afl_linear_fwd(op, t, tid, nt); break;
+    case AFL_OP_LN: afl_ln_fwd_a(op, t, tid, nt); afl_team_sync(nt, bar_id); afl_ln_fwd_b(op, t, tid, nt); break;
+    case AFL_OP_GRU: afl_gru_fwd(op, t, tid, nt); break;
+    case AFL_OP_CONV: afl_conv_fwd(op, t, tid, nt); break;
+    case AFL_OP_POOL: afl_pool_fwd(op, t, tid, nt); break;
+    case AFL_OP_DROPOUT: afl_dropout_fwd(op, t, tid, nt); break;
+    case AFL_OP_BCE: afl_bce(op, t, tid, nt); break;          // loss summed later by afl_param_grads
+    default: break;
+  }
+}
+
+AFL_DEV void afl_chain_bwd_op(const AflOp& op, const AflTile& t, int tid, int nt, int bar_id) {
+  switch (op.kind) {
+    case AFL_OP_LINEAR: afl_linear_bwd_a(op, t, tid, nt); afl_team_sync(nt, bar_id);
+                        afl_linear_bwd_b(op, t, tid, nt, AFL_PART_ACT); break;
+    case AFL_OP_LN: afl_ln_bwd_a(op, t, tid, nt, AFL_PART_ACT); afl_team_sync(nt, bar_id); afl_ln_bwd_b(op, t, tid, nt); break;
+    case AFL_OP_GRU: afl_gru_bwd_a(op, t, tid, nt); break;
+    case AFL_OP_CONV: afl_conv_bwd_a(op, t, tid, nt); afl_team_sync(nt, bar_id);
+                      afl_conv_bwd_b(op, t, tid, nt, AFL_PART_ACT); break;
+    case AFL_OP_POOL: afl_pool_bwd(op, t, tid, nt); break;
+    case AFL_OP_DROPOUT: afl_dropout_bwd(op, t, tid, nt); break;
+    default: break;
+  }
+}
+
+// One sample's forward + backward chain, executed by a team of `tw` warps (tw = group size of the branch groups).
+// ops: this sample's shifted program; ts: 1-sample tile; wteam: warp index inside the team; lane: lane in the warp.
+AFL_DEV void afl_chain_sample(const AflOp* ops, int n_ops, const AflTile& ts, int wteam, int tw, int lane, int lanes,
+                              int bar_id) {
+  const int team = tw * lanes;
+  // ---- forward
+  for (int i = 0; i < n_ops;) {
+    const int g = ops[i].grp_size > 1 ? ops[i].grp_size : 1;
+    if (g > 1 && tw >= g) {
+      if (wteam < g) afl_chain_fwd_op(ops[i + wteam], ts, lane, lanes, bar_id);
+      const int ng = (i + g < n_ops && ops[i + g].grp_size > 1) ? 1 : 0;
+      if (ng) afl_team_sync(lanes, bar_id); else afl_team_sync(team, bar_id);     // join before a single op
+    } else {
+      for (int j = 0; j < g; ++j) {
+        afl_chain_fwd_op(ops[i + j], ts, wteam * lanes + lane, team, bar_id);
+        afl_team_sync(team, bar_id);
+      }
+    }
+    i += g;
+  }
+  // ---- backward (activation gradients only)
+  for (int i = n_ops - 1; i >= 0;) {
+    const int st = ops[i].grp_start;
+    const int g = ops[st].grp_size > 1 ? ops[st].grp_size : 1;
+    if (g > 1 && tw >= g) {
+      if (wteam < g) afl_chain_bwd_op(ops[st + wteam], ts, lane, lanes, bar_id);
+      const int pg = (st > 0 && ops[ops[st - 1].grp_start].grp_size > 1) ? 1 : 0;
+      if (pg) afl_team_sync(lanes, bar_id); else afl_team_sync(team, bar_id);
+    } else {
+      for (int j = g - 1; j >= 0; --j) {
+        afl_chain_bwd_op(ops[st + j], ts, wteam * lanes + lane, team, bar_id);
+        afl_team_sync(team, bar_id);
+      }
+    }
+    i = st - 1;
+  }
+}
+
+// Deferred parameter gradients over all S samples of the tile: no barriers, every op's items are independent.
+AFL_DEV void afl_param_grads(const AflOp* ops, int n_ops, const AflTile& t, int tid, int nt) {
+  for (int i = 0; i < n_ops; ++i) {
+    const AflOp& op = ops[i];
+    switch (op.kind) {
+      case AFL_OP_LINEAR: afl_linear_bwd_b(op, t, tid, nt, AFL_PART_PARAM); break;
+      case AFL_OP_LN: afl_ln_bwd_a(op, t, tid, nt, AFL_PART_PARAM); break;
+      case AFL_OP_GRU: afl_gru_bwd_b(op, t, tid, nt); break;
+      case AFL_OP_CONV: afl_conv_bwd_b(op, t, tid, nt, AFL_PART_PARAM); break;
+      case AFL_OP_BCE: afl_bce_reduce(op, t, tid, nt); break;
+      default: break;
+    }
+  }
+}
+
+// Chain-mode tile step.  ops_s: [S][n_ops] shifted programs; the block's warps are split into S teams of `tw` warps.
+// On the CPU twin (nt = 1) the samples and team members simply run one after the other.
+AFL_DEV void afl_run_tile_chain(const AflOp* ops, const AflOp* ops_s, int n_ops, const AflTile& t, int tid, int nt) {
+  AflTile ts = t;
+  ts.S = 1;
+#if defined(__CUDA_ARCH__)
+  const int warps = nt >> 5, tw = warps / t.S;          // caller guarantees warps == tw * S, tw >= 1
+  const int w = tid >> 5, lane = tid & 31;
+  const int s = w / tw, wteam = w - s * tw;
+  ts.n_valid = s < t.n_valid ? 1 : 0;
+  ts.sample_base = t.sample_base + s;
+  ts.idx = t.idx ? t.idx + s : nullptr;
+  ts.row0 = t.row0 + s;
+  afl_chain_sample(ops_s + (size_t)s * n_ops, n_ops, ts, wteam, tw, lane, 32, 1 + s);
+  __syncthreads();
+#else
+  for (int s = 0; s < t.S; ++s) {
+    ts.n_valid = s < t.n_valid ? 1 : 0;
+    ts.sample_base = t.sample_base + s;
+    ts.idx = t.idx ? t.idx + s : nullptr;
+    ts.row0 = t.row0 + s;
+    afl_chain_sample(ops_s + (size_t)s * n_ops, n_ops, ts, 0, 1, 0, 1, 0);
+  }
+#endif
+  afl_param_grads(ops, n_ops, t, tid, nt);
+  AFL_SYNC();
 }
 
 // ----------------------------------------------------------------------------------------- optimiser phase

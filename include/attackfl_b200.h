@@ -119,14 +119,16 @@ int afl_hyper_step_noalloc(float* head_w, float* head_b, float* mw, float* vw, f
  * models src/Model.py:27-246).  ops: int32 program [n_ops][32] (attackfl_b200/models/programs.py);
  * w,m,v [C][d_pad]; gpart [C][G][d_pad]; data [rows][rec]; idx [C][epochs][>=n] int32; G blocks per client,
  * M tiles of S samples per block (G*M*S >= batch).  loss_out [C][2] = {sum of per-sample losses, #NaN losses},
- * steps_out [C]; bar [C] and gnorm [C][2] are scratch.  opt_kind 0 Adam / 1 SGD-momentum. */
-int afl_train_capacity(int pool_floats, int n_ops);
+ * steps_out [C]; bar [C] and gnorm [C][2] are scratch.  opt_kind 0 Adam / 1 SGD-momentum.  chain=1 runs each sample's
+ * forward/backward chain on its own warp team with a deferred parameter-gradient pass (program must be planned without
+ * gradient-buffer reuse; chain_S = S for afl_train_capacity, 0 otherwise). */
+int afl_train_capacity(int pool_floats, int n_ops, int chain_S);
 int afl_train_round(const int32_t* ops_dev, int n_ops, int pool_floats, float* w, float* m, float* v, float* gpart,
                     int64_t d_pad, const float* data, int rec, const int32_t* idx, int64_t idx_stride_c,
                     int64_t idx_stride_e, const int32_t* n_data, const int32_t* client_ids, int n_clients, int G,
                     int M, int S, int batch, int epochs, int opt_kind, float lr, float beta1, float beta2, float eps,
                     float momentum, int clip_proper, float clip, uint64_t seed, int dropout, float* loss_out,
-                    int32_t* steps_out, uint32_t* bar, float* gnorm, void* stream);
+                    int32_t* steps_out, uint32_t* bar, float* gnorm, int chain, void* stream);
 /* Batched inference of n_models rows over the same records (src/Validation.py:92-122,178-213); probs [n_models][n_rows]. */
 int afl_infer(const int32_t* ops_dev, int n_ops, int pool_floats, const float* w, int64_t d_pad, int n_models,
               const float* data, int rec, int64_t n_rows, float* probs, int S, void* stream);

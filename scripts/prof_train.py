@@ -16,7 +16,7 @@ dev = "cuda"
 torch.manual_seed(0)
 lay = FlatLayout.from_module(models.build(name))
 S_env = int(os.environ.get("PROF_S", "0"))
-prog = build_program(name, lay, S=S_env or None, train=True, dropout=True).to(dev)
+prog = build_program(name, lay, S=S_env or None, train=True, dropout=True, chain=bool(int(os.environ.get("PROF_CHAIN", "0")))).to(dev)
 plan = T.make_plan(prog, 128, C, lay.padded, dev, int(os.environ.get("PROF_G", "0")))
 print("plan", plan, "pool KB", prog.pool_floats * 4 / 1024)
 rows = torch.stack([lay.flatten(models.build(name).state_dict()) for _ in range(C)]).to(dev)

@@ -171,8 +171,8 @@ def _torch_round(name, lay, row, ds, idx, n, batch, epochs, lr, opt="adam", mome
     return lay.flatten(m.state_dict()), tot, steps
 
 
-def _native_round(name, lay, rows, ds, idx, n_data, batch, epochs, device, G, M, S, **kw):
-    prog = build_program(name, lay, S=S, train=True, dropout=False).to(device)
+def _native_round(name, lay, rows, ds, idx, n_data, batch, epochs, device, G, M, S, chain=False, **kw):
+    prog = build_program(name, lay, S=S, train=True, dropout=False, chain=chain).to(device)
     C = rows.shape[0]
     w = rows.clone().to(device)
     m, v = torch.zeros_like(w), torch.zeros_like(w)
@@ -185,9 +185,10 @@ def _native_round(name, lay, rows, ds, idx, n_data, batch, epochs, device, G, M,
 
 
 @pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("chain", [False, True])
 @pytest.mark.parametrize("name,S,G,M,batch", [("TransformerModel", 8, 2, 2, 32), ("TransformerModel", 16, 1, 1, 16),
                                               ("RNNModel", 8, 4, 1, 32), ("CNNModel", 4, 2, 2, 16)])
-def test_round_matches_torch_adam(device, name, S, G, M, batch):
+def test_round_matches_torch_adam(device, name, S, G, M, batch, chain):
     m0, lay = _setup(name, seed=2)
     ds = synthetic_icu(300, 9)
     n_data = [batch * 2 + 1, batch * 2 + 5, batch * 3]     # first client ends on a batch of 1 (skipped)
@@ -195,7 +196,7 @@ def test_round_matches_torch_adam(device, name, S, G, M, batch):
     g = torch.Generator().manual_seed(0)
     idx = make_round_indices(300, n_data, epochs, g)
     rows = torch.stack([lay.flatten(models.build(name).state_dict()) for _ in n_data])
-    got, loss, steps = _native_round(name, lay, rows, ds, idx, n_data, batch, epochs, device, G, M, S, lr=0.004)
+    got, loss, steps = _native_round(name, lay, rows, ds, idx, n_data, batch, epochs, device, G, M, S, chain=chain, lr=0.004)
     for c, n in enumerate(n_data):
         want, tot, st = _torch_round(name, lay, rows[c], ds, idx[c], n, batch, epochs, 0.004)
         assert int(steps[c]) == st
@@ -232,8 +233,8 @@ def test_split_invariance_with_dropout(device):
     idx = make_round_indices(150, n_data, epochs, torch.Generator().manual_seed(2))
     rows = torch.stack([lay.flatten(models.build(name).state_dict()) for _ in n_data])
     res = []
-    for (S, G, M) in ((16, 2, 1), (8, 1, 4), (8, 4, 1)):
-        prog = build_program(name, lay, S=S, train=True, dropout=True).to(device)
+    for (S, G, M, chain) in ((16, 2, 1, False), (8, 1, 4, False), (8, 4, 1, False), (8, 4, 1, True), (16, 1, 2, True)):
+        prog = build_program(name, lay, S=S, train=True, dropout=True, chain=chain).to(device)
         w = rows.clone().to(device)
         m, v = torch.zeros_like(w), torch.zeros_like(w)
         gpart = torch.zeros(2 * G, lay.padded, device=device)
@@ -242,7 +243,8 @@ def test_split_invariance_with_dropout(device):
                       torch.arange(2, dtype=torch.int32, device=device), batch, epochs, seed=99, dropout=True)
         res.append(w.cpu())
     assert not torch.allclose(res[0], rows, atol=1e-4)
-    assert torch.allclose(res[0], res[1], atol=1e-5) and torch.allclose(res[0], res[2], atol=1e-5)
+    for r in res[1:]:
+        assert torch.allclose(res[0], r, atol=1e-5)
 
 
 @pytest.mark.parametrize("device", DEVICES)
