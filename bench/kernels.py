@@ -83,11 +83,15 @@ def main():
     if not only or "gram" in only:
         for R, D in ((18, 48128), (66, 98304), (130, 98304), (256, 203776), (66, 25_000_000), (130, 25_000_000)):
             a = torch.randn(R, D, device=dev) * 0.05
-            gram_native.gram_tcgen05(a)
-            s_all = timeit(lambda: gram_native.gram_tcgen05(a))
             rb = 128 if R <= 128 else 256
             ncol = (R + 15) // 16 * 16
-            rec("K3 gram tcgen05 (cast+mma+reduce)", f"R={R} D={D}", s_all, bytes_=R * D * 4 + rb * D * 2 * 2,
+            gram_native.gram_tcgen05(a, "tf32")
+            s_tf = timeit(lambda: gram_native.gram_tcgen05(a, "tf32"))
+            rec("K3 gram tcgen05 tf32 (TMA on fp32 rows + mma + reduce)", f"R={R} D={D}", s_tf, bytes_=R * D * 4,
+                flops=2.0 * rb * ncol * D, note="one pass over the fp32 rows; FLOPs on the padded tile actually issued")
+            gram_native.gram_tcgen05(a, "bf16")
+            s_all = timeit(lambda: gram_native.gram_tcgen05(a, "bf16"))
+            rec("K3 gram tcgen05 bf16 (cast+mma+reduce)", f"R={R} D={D}", s_all, bytes_=R * D * 4 + rb * D * 2 * 2,
                 flops=2.0 * rb * ncol * D, note="FLOPs counted on the padded 128/256 x N tile actually issued")
             s_t = timeit(lambda: (a @ a.t()))
             rec("torch fp32 matmul A A^T (library baseline)", f"R={R} D={D}", s_t, bytes_=R * D * 4, flops=2.0 * R * R * D)

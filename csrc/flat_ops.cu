@@ -58,6 +58,87 @@ __global__ void __launch_bounds__(128) select_kernel(const float* rows, int C, i
   afl_select_core(rows, C, d_pad, out, mode, trim, 0, d_pad, blockIdx.x * 128 + threadIdx.x, gridDim.x * 128);
 }
 
+// K6, warp-cooperative version: a block stages a [C][32-coordinate] tile through shared memory (coalesced 128-byte row
+// segments), then each warp sorts one coordinate's C values held VPT per lane in registers with a bitonic network:
+// compare-exchange distances < VPT stay inside a lane, larger ones use shfl.xor.  No local memory, no global re-reads.
+template <int VPT>
+__global__ void __launch_bounds__(256) select_warp_kernel(const float* __restrict__ rows, int C, int64_t d_pad,
+                                                          float* __restrict__ out, int mode, int trim) {
+  extern __shared__ float tile[];                    // [C][33]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int P = 32 * VPT;                        // padded element count (power of two >= C)
+  const int64_t n_tiles = (d_pad + 31) / 32;
+  for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
+    const int64_t d0 = tIdx * 32;
+    __syncthreads();
+    for (int i = threadIdx.x; i < C * 32; i += 256) {
+      const int c = i >> 5, x = i & 31;
+      tile[c * 33 + x] = (d0 + x < d_pad) ? rows[(int64_t)c * d_pad + d0 + x] : 0.f;
+    }
+    __syncthreads();
+    for (int col = warp; col < 32; col += 8) {
+      if (d0 + col >= d_pad) break;
+      float v[VPT];
+#pragma unroll
+      for (int r = 0; r < VPT; ++r) {
+        const int e = lane * VPT + r;
+        v[r] = e < C ? tile[e * 33 + col] : INFINITY;
+      }
+#pragma unroll
+      for (int k = 2; k <= P; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          if (j >= VPT) {
+            const int lj = j / VPT;                   // partner lane distance
+#pragma unroll
+            for (int r = 0; r < VPT; ++r) {
+              const int e = lane * VPT + r;
+              const float o = __shfl_xor_sync(0xffffffffu, v[r], lj);
+              const bool up = (e & k) == 0;
+              const bool lower = (lane & lj) == 0;   // this lane holds the smaller index of the pair
+              const bool take_min = (up == lower);
+              const float mn = fminf(v[r], o), mx = fmaxf(v[r], o);
+              // NaNs: fminf/fmaxf drop them; keep the original value when both compare false
+              v[r] = take_min ? mn : mx;
+            }
+          } else {
+#pragma unroll
+            for (int r = 0; r < VPT; ++r) {
+              const int r2 = r ^ j;
+              if (r2 > r) {
+                const int e = lane * VPT + r;
+                const bool up = (e & k) == 0;
+                const float a = v[r], b = v[r2];
+                const bool sw = up ? (a > b) : (a < b);
+                if (sw) { v[r] = b; v[r2] = a; }
+              }
+            }
+          }
+        }
+      }
+      float res;
+      if (mode == 0) {
+        const int idx = (C - 1) / 2;
+        float mine = 0.f;
+#pragma unroll
+        for (int r = 0; r < VPT; ++r) if ((idx % VPT) == r) mine = v[r];
+        res = __shfl_sync(0xffffffffu, mine, idx / VPT);
+      } else {
+        float sum = 0.f;
+#pragma unroll
+        for (int r = 0; r < VPT; ++r) {
+          const int e = lane * VPT + r;
+          if (e >= trim && e < C - trim) sum += v[r];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        res = sum / (float)(C - 2 * trim);
+      }
+      if (lane == 0) out[d0 + col] = res;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ hyper kernels
 // Tile of TR rows of W_h staged in shared memory with a padded row (H+1) so both access patterns
 // (lane = row, lane = column) are bank-conflict free.  W_h is read from HBM exactly once per pass.
@@ -351,7 +432,13 @@ int afl_craft_random(float* out, const float* w, const float* valid, float pertu
 int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mode, int trim, void* stream) {
   AFL_CHECK_ARG(C >= 1 && C <= AFL_SEL_MAX, "afl_coord_select: 1 <= C <= 256");
   AFL_CHECK_ARG(mode == 0 || 2 * trim < C, "afl_coord_select: 2*trim must be < C");
-  select_kernel<<<grid_for(d_pad, 128, 16), 128, 0, (cudaStream_t)stream>>>(rows, C, d_pad, out, mode, trim);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = sizeof(float) * (size_t)C * 33;
+  const int grid = grid_for((d_pad + 31) / 32, 1, 8);
+  if (C <= 32) select_warp_kernel<1><<<grid, 256, smem, st>>>(rows, C, d_pad, out, mode, trim);
+  else if (C <= 64) select_warp_kernel<2><<<grid, 256, smem, st>>>(rows, C, d_pad, out, mode, trim);
+  else if (C <= 128) select_warp_kernel<4><<<grid, 256, smem, st>>>(rows, C, d_pad, out, mode, trim);
+  else select_warp_kernel<8><<<grid, 256, smem, st>>>(rows, C, d_pad, out, mode, trim);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_coord_select");
 }

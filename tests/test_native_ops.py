@@ -92,7 +92,7 @@ def test_fedavg_k1_guard(device):
 
 
 @pytest.mark.parametrize("device", DEVICES)
-@pytest.mark.parametrize("c", [3, 10, 11, 37, 128])
+@pytest.mark.parametrize("c", [3, 10, 11, 32, 37, 64, 65, 128, 200, 256])
 def test_coord_select(device, c):
     rows = _rand_rows(c, 2048, device, seed=c, spread=1.0)
     assert torch.equal(flat.coord_select(rows, "median").cpu(), agg.median(rows.cpu()))
