@@ -124,32 +124,19 @@ def scion_quantize(vec: torch.Tensor, generator: Optional[torch.Generator] = Non
 
 def scionfl(rows: torch.Tensor, sizes: Sequence[float], valid: Optional[torch.Tensor] = None,
             generator: Optional[torch.Generator] = None, keep: str = "reference",
-            mu_threshold: float = 3.0, topk_ratio: float = 0.5) -> Tuple[torch.Tensor, List[int]]:
+            mu_threshold: float = 3.0, topk_ratio: float = 0.5,
+            scores: Optional[Sequence[float]] = None) -> Tuple[torch.Tensor, List[int]]:
     """ScionFL-style filter then size-weighted FedAvg of the kept clients (server.py:436-492).
 
     ``keep='reference'`` keeps clients whose cosine *distance* to the aggregate is above the
     median, i.e. the most dissimilar half (likely inverted in the reference, SURVEY Q14);
-    ``keep='similar'`` keeps the closest half.
+    ``keep='similar'`` keeps the closest half.  ``scores``: cosine distances already computed by the
+    bit-packed native pass (``ops.flat.scion_cosine_distances``); otherwise the plain torch restatement below.
     """
     n = rows.shape[0]
-    dense = rows if valid is None else rows[:, valid]
-    quant = [scion_quantize(dense[i], generator) for i in range(n)]
-    d = dense.shape[1]
-    l2 = []
-    for sigma, smin, smax in quant:
-        c1 = sigma.sum().item()
-        l2.append(float(np.sqrt((d - c1) * smin ** 2 + c1 * smax ** 2)))
-    l2_avg = float(np.mean(l2))
-    deq = []
-    for (sigma, smin, smax), l in zip(quant, l2):
-        if l > mu_threshold * l2_avg:
-            fct = (mu_threshold * l2_avg) / l
-            smin, smax = smin * fct, smax * fct
-        deq.append(smin + sigma * (smax - smin))
-    deq = torch.stack(deq)
-    agg = deq.mean(0)
-    cosd = 1 - torch.nn.functional.cosine_similarity(deq, agg[None], dim=1)
-    scores = cosd.tolist()
+    if scores is None:
+        scores = scion_scores_torch(rows, valid, generator, mu_threshold)
+    scores = [float(x) for x in scores]
     thr = sorted(scores, reverse=True)[int(topk_ratio * n)]
     if keep == "reference":
         kept = [i for i, s in enumerate(scores) if s > thr]
@@ -160,6 +147,34 @@ def scionfl(rows: torch.Tensor, sizes: Sequence[float], valid: Optional[torch.Te
     sz = torch.as_tensor([sizes[i] for i in kept], dtype=torch.float32, device=rows.device)
     out = (rows[kept] * sz[:, None]).sum(0) / sz.sum()
     return out, kept
+
+
+def scion_dequant_scores(sigma: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor) -> torch.Tensor:
+    """Cosine distances of dequantised rows ``lo + sigma (hi - lo)`` to their mean (server.py:455-466)."""
+    deq = lo[:, None] + sigma * (hi - lo)[:, None]
+    agg = deq.mean(0)
+    return 1 - torch.nn.functional.cosine_similarity(deq, agg[None], dim=1)
+
+
+def scion_scores_torch(rows: torch.Tensor, valid: Optional[torch.Tensor] = None,
+                       generator: Optional[torch.Generator] = None, mu_threshold: float = 3.0) -> List[float]:
+    n = rows.shape[0]
+    dense = rows if valid is None else rows[:, valid]
+    quant = [scion_quantize(dense[i], generator) for i in range(n)]
+    d = dense.shape[1]
+    l2 = []
+    for sigma, smin, smax in quant:
+        c1 = sigma.sum().item()
+        l2.append(float(np.sqrt((d - c1) * smin ** 2 + c1 * smax ** 2)))
+    l2_avg = float(np.mean(l2))
+    lo, hi = [], []
+    for (sigma, smin, smax), l in zip(quant, l2):
+        if l > mu_threshold * l2_avg:
+            fct = (mu_threshold * l2_avg) / l
+            smin, smax = smin * fct, smax * fct
+        lo.append(smin); hi.append(smax)
+    sig = torch.stack([q[0] for q in quant])
+    return scion_dequant_scores(sig, torch.tensor(lo, device=rows.device), torch.tensor(hi, device=rows.device)).tolist()
 
 
 # ---------------------------------------------------------------------------- P2: gmm / fltracer / byzantine

@@ -51,6 +51,8 @@ def server_parser() -> argparse.ArgumentParser:
                    help="with --local-clients: mark client IDX as an attacker, e.g. 7:LIE:2:0.74")
     p.add_argument("--register-timeout", type=float, default=None, help="seconds to wait for registrations")
     p.add_argument("--gpus", type=int, default=0, help="ranks to launch (one per GPU); default runtime.gpus")
+    p.add_argument("--profile", type=int, default=0, metavar="ROUND",
+                   help="bracket round attempt ROUND with cudaProfilerStart/Stop (ncu/nsys capture-range hook)")
     return p
 
 

@@ -96,6 +96,10 @@ class RuntimeCfg:
     synthetic_train_rows: int = 16384
     synthetic_test_rows: int = 4096
     metrics_file: str = "metrics.jsonl"
+    nvtx: bool = True                # NVTX range per phase (train / craft / aggregate / validate ...)
+    profile_round: int = 0           # >0: bracket that attempt with cudaProfilerStart/Stop (ncu/nsys --capture-range)
+    round_timeout_s: float = 0.0     # >0: rank-health watchdog, aborts the process if one round exceeds it
+    fault_inject: List[Dict[str, Any]] = field(default_factory=list)   # test-only: [{attempt, client, kind}]
 
 
 @dataclass
@@ -185,6 +189,9 @@ def validate(cfg: Config) -> None:
         raise ValueError(f"attack.search '{cfg.attack.search}' is not valid")
     if s.hyper_update not in ("sequential", "batched"):
         raise ValueError(f"server.hyper-update '{s.hyper_update}' is not valid")
+    for f in cfg.runtime.fault_inject:
+        if f.get("kind") not in ("nan-loss", "nan-weights", "stall"):
+            raise ValueError(f"runtime.fault-inject kind '{f.get('kind')}' is not valid (nan-loss|nan-weights|stall)")
     if l.batch_size < 1 or l.epoch < 1:
         raise ValueError("learning.batch-size and learning.epoch must be >= 1")
 

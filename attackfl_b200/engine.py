@@ -36,7 +36,7 @@ from .log import Logger, MetricsWriter, NullLogger, print_with_color
 from .models.hyper import FusedHyperNet, HyperNetwork
 from .models.programs import SUPPORTED as NATIVE_MODELS, build_program
 from .parallel.ctx import ParallelContext, single
-from .utils.timers import PhaseTimer
+from .utils.timers import PhaseTimer, Watchdog
 from .validation import Validator, roc_auc
 
 GRAM_MODES = ("Min-Max", "Min-Sum", "Opt-Fang")
@@ -155,7 +155,8 @@ class Federation:
         self.training_round = [0] * self.C                   # RpcClient.training_round
         self.sizes = [0] * self.C
         self.genuine_prev: Optional[List[int]] = None        # indices of last round's genuine reporters
-        self.timer = PhaseTimer(self.device)
+        self.timer = PhaseTimer(self.device, nvtx=cfg.runtime.nvtx)
+        self.watchdog = Watchdog(cfg.runtime.round_timeout_s)
         self.validator = Validator(self.data_name, self.logger if ctx.rank == 0 else None, quiet=ctx.rank != 0)
         self.metrics = MetricsWriter(os.path.join(workdir, cfg.runtime.metrics_file) if (save and ctx.rank == 0) else None)
         self.history: List[RoundResult] = []
@@ -488,7 +489,13 @@ class Federation:
             else:
                 self.global_row.copy_(agg.weighted_sum(sel, w))
         elif self.mode == "scionfl":
-            out, kept = agg.scionfl(sel, sizes, valid=self.valid.bool(), generator=None, keep=s.scionfl_keep)
+            scores = None
+            if self.backend == "native":                          # bit-packed pass: deq rows are never built
+                from .ops import flat
+                scores, _ = flat.scion_cosine_distances(sel.contiguous(), self.valid, seed=int(self.cfg.server.random_seed or 0) * 7919 + self.attempt)
+                scores = scores.tolist()
+            out, kept = agg.scionfl(sel, sizes, valid=self.valid.bool(), generator=None, keep=s.scionfl_keep,
+                                    scores=scores)
             info["scionfl_kept"] = [reporting[i] for i in kept]
             self.global_row.copy_(out)
         elif self.mode == "FLTrust":
@@ -631,10 +638,37 @@ class Federation:
 
     # ================================================================================== one round
     def run_round(self) -> RoundResult:
-        s, l = self.cfg.server, self.cfg.learning
+        """One START -> train -> UPDATE -> aggregate -> validate cycle (``server.py:205-275,277-567``).
+
+        Observability / robustness hooks around it: an NVTX range per phase, an optional
+        ``cudaProfilerStart/Stop`` bracket on attempt ``runtime.profile-round`` (so ``ncu --profile-from-start off``
+        captures exactly one round), the rank-health watchdog, and the test-only fault injectors."""
         self.attempt += 1
+        rt = self.cfg.runtime
+        profiling = rt.profile_round > 0 and self.attempt == rt.profile_round and self.device.type == "cuda"
+        if profiling:
+            torch.cuda.synchronize(self.device)
+            torch.cuda.cudart().cudaProfilerStart()
+        self.watchdog.arm(f"round attempt {self.attempt}")
+        try:
+            return self._run_round()
+        finally:
+            self.watchdog.disarm()
+            if profiling:
+                torch.cuda.synchronize(self.device)
+                torch.cuda.cudart().cudaProfilerStop()
+
+    def _faults(self, kind: str) -> List[int]:
+        """Clients hit by a ``runtime.fault-inject`` entry of ``kind`` on this attempt (test-only hook)."""
+        return [int(f["client"]) for f in self.cfg.runtime.fault_inject
+                if f.get("kind") == kind and int(f.get("attempt", -1)) == self.attempt]
+
+    def _run_round(self) -> RoundResult:
+        s, l = self.cfg.server, self.cfg.learning
         round_no = self.num_round - self.remaining + 1
         t_wall = time.perf_counter()
+        for _ in self._faults("stall"):                           # exercises the watchdog
+            time.sleep(max(self.cfg.runtime.round_timeout_s * 2, 0.2))
         if self.host_train is not None:
             with self.timer.phase("h2d"):
                 self.train_dev.copy_(self.host_train, non_blocking=True)
@@ -663,6 +697,12 @@ class Federation:
                 loss = self._train_native(sizes_local) if self.backend == "native" else self._train_torch(sizes_local)
             else:
                 loss = torch.zeros(1, 2, device=self.device)
+        for c in self._faults("nan-loss"):                        # client c reports result=False (client.py:100-102)
+            if c in self.local:
+                loss[self.local.index(c), 1] = 1.0
+        for c in self._faults("nan-weights"):                     # a diverged update: caught by the NaN validation
+            if c in self.local:
+                self.rows[self.local.index(c)].fill_(float("nan"))
         # ---- UPDATE: result flags + losses (the only per-client scalars that reach the host)
         flags = torch.zeros(self.C, 3, device=self.device)
         for j, c in enumerate(self.local):

@@ -114,6 +114,55 @@ def coord_select(rows: torch.Tensor, mode: str, trim: int = 0, out: Optional[tor
     return out
 
 
+def scion_quantize(rows: torch.Tensor, valid: Optional[torch.Tensor], seed: int):
+    """ScionFL 1-bit stochastic quantisation of every row (``src/Utils.py:372-376``), packed 32 coordinates per word.
+
+    Returns ``(bits [C, d_pad/32] int32, counts [C] int32, minmax [C, 2])``; ``valid`` is the layout's 0/1 float mask."""
+    C, d_pad = rows.shape
+    lib = lib_for(rows)
+    dev = rows.device
+    minmax = torch.empty(C, 2, dtype=torch.float32, device=dev)
+    bits = torch.empty(C, d_pad // 32, dtype=torch.int32, device=dev)
+    counts = torch.empty(C, dtype=torch.int32, device=dev)
+    check(lib, lib.afl_scion_minmax(ptr(rows), ptr(valid), c_i(C), c_i64(d_pad), ptr(minmax), stream_ptr(rows)),
+          "afl_scion_minmax")
+    check(lib, lib.afl_scion_quantize(ptr(rows), ptr(valid), ptr(minmax), c_i(C), c_i64(d_pad), c_u64(seed), ptr(bits),
+                                      ptr(counts), stream_ptr(rows)), "afl_scion_quantize")
+    return bits, counts, minmax
+
+
+def scion_scores(bits: torch.Tensor, valid: Optional[torch.Tensor], lohi: torch.Tensor) -> torch.Tensor:
+    """``out[:C] = sum_j sigma_cj agg_j``, ``out[C] = sum_j agg_j``, ``out[C+1] = sum_j agg_j^2`` for the mean ``agg`` of
+    the dequantised rows ``lo_c + sigma_cj (hi_c - lo_c)`` — computed from the packed bits only."""
+    C, words = bits.shape
+    lib = lib_for(bits)
+    out = torch.empty(C + 2, dtype=torch.float32, device=bits.device)
+    lohi = lohi.to(torch.float32).contiguous()
+    check(lib, lib.afl_scion_scores(ptr(bits), ptr(valid), ptr(lohi), c_i(C), c_i64(words * 32), ptr(out),
+                                    stream_ptr(bits)), "afl_scion_scores")
+    return out
+
+
+def scion_cosine_distances(rows: torch.Tensor, valid: Optional[torch.Tensor], seed: int, mu_threshold: float = 3.0):
+    """The whole ScionFL scoring pass (``server.py:443-466``): quantise, L2 from bit counts, clip at
+    ``mu_threshold`` x mean, cosine distance of every dequantised row to their mean.  Returns ``(cosd [C], aux)``."""
+    C, d_pad = rows.shape
+    bits, counts, minmax = scion_quantize(rows, valid, seed)
+    d = float(valid.sum().item()) if valid is not None else float(d_pad)
+    c1 = counts.to(torch.float64)
+    lo, hi = minmax[:, 0].to(torch.float64), minmax[:, 1].to(torch.float64)
+    l2 = torch.sqrt((d - c1) * lo * lo + c1 * hi * hi)
+    cap = mu_threshold * l2.mean()
+    fct = torch.where(l2 > cap, cap / l2, torch.ones_like(l2))
+    lo, hi = lo * fct, hi * fct
+    out = scion_scores(bits, valid, torch.stack([lo, hi], dim=1)).to(torch.float64)
+    s, a_sum, a_sq = out[:C], out[C], out[C + 1]
+    dots = lo * a_sum + (hi - lo) * s
+    n_deq = torch.sqrt((d - c1) * lo * lo + c1 * hi * hi)
+    cos = dots / (n_deq.clamp_min(1e-8) * torch.sqrt(a_sq).clamp_min(1e-8))
+    return (1.0 - cos).to(torch.float32), {"bits": bits, "counts": counts, "minmax": minmax, "lohi": torch.stack([lo, hi], 1)}
+
+
 # ---------------------------------------------------------------------------------------- hyper-network
 class NativeHyper:
     """Device-side state of a ``FusedHyperNet`` in the layout the K5 kernels expect.

@@ -94,6 +94,55 @@ int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mo
   return 0;
 }
 
+int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void*) {
+  CHECK_ARG(C >= 1 && d_pad % 32 == 0, "afl_scion_minmax: C >= 1, d_pad % 32 == 0");
+  for (int c = 0; c < C; ++c) {
+    float mn = INFINITY, mx = -INFINITY;
+    for (int64_t j = 0; j < d_pad; ++j)
+      if (!valid || valid[j] != 0.f) { const float x = rows[(int64_t)c * d_pad + j]; mn = fminf(mn, x); mx = fmaxf(mx, x); }
+    minmax[2 * c] = mn; minmax[2 * c + 1] = mx;
+  }
+  return 0;
+}
+
+int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                       uint32_t* bits, int* counts, void*) {
+  CHECK_ARG(C >= 1 && d_pad % 32 == 0, "afl_scion_quantize: C >= 1, d_pad % 32 == 0");
+  const int64_t words = d_pad / 32;
+  for (int c = 0; c < C; ++c) {
+    const float mn = minmax[2 * c], inv = 1.0f / (minmax[2 * c + 1] - mn + 1e-6f);
+    int cnt = 0;
+    for (int64_t w = 0; w < words; ++w) {
+      uint32_t word = 0;
+      for (int b = 0; b < 32; ++b) {
+        const int64_t j = w * 32 + b;
+        if ((!valid || valid[j] != 0.f) &&
+            afl_scion_bit(rows[(int64_t)c * d_pad + j], mn, inv, (uint32_t)seed, (uint32_t)(seed >> 32), (uint32_t)c, (uint32_t)j)) {
+          word |= 1u << b; ++cnt;
+        }
+      }
+      bits[(int64_t)c * words + w] = word;
+    }
+    counts[c] = cnt;
+  }
+  return 0;
+}
+
+int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out, void*) {
+  CHECK_ARG(C >= 1 && C <= 4096 && d_pad % 32 == 0, "afl_scion_scores: 1 <= C <= 4096, d_pad % 32 == 0");
+  const int64_t words = d_pad / 32;
+  std::vector<double> acc((size_t)C + 2, 0.0);
+  for (int64_t w = 0; w < words; ++w)
+    for (int b = 0; b < 32; ++b) {
+      if (valid && valid[w * 32 + b] == 0.f) continue;
+      const float a = afl_scion_agg(bits, lohi, C, words, w, b);
+      acc[C] += a; acc[C + 1] += (double)a * a;
+      for (int i = 0; i < C; ++i) if ((bits[(int64_t)i * words + w] >> b) & 1u) acc[i] += a;
+    }
+  for (int i = 0; i < C + 2; ++i) out[i] = (float)acc[i];
+  return 0;
+}
+
 // ---------------------------------------------------------------------------------------- hyper (host loops)
 static size_t small_total(int n_nodes, int E, int H) { return (size_t)n_nodes * E + (size_t)H * E + H + 2 * ((size_t)H * H + H); }
 static size_t off_w(int n_nodes, int E, int H, int layer) {

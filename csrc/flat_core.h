@@ -183,6 +183,27 @@ AFL_DEV void afl_craft_random_core(float* out, const float* w, const float* vali
   }
 }
 
+// ----------------------------------------------------------------------------------------- ScionFL (S7)
+// 1-bit stochastic quantisation of a row: sigma_j ~ Bernoulli((x_j - min) / (max - min + 1e-6)), one Philox stream
+// per (seed, row).  The dequantised rows  lo_i + sigma_ij (hi_i - lo_i)  are never materialised: everything the filter
+// needs (bit counts, <deq_i, agg>, |agg|^2) is computed from the packed bits.
+AFL_HD bool afl_scion_bit(float x, float mn, float inv_range, uint32_t seed_lo, uint32_t seed_hi, uint32_t row,
+                          uint32_t j) {
+  AflU4 r = afl_philox(j >> 2, row, 0x5C10u, 0u, seed_lo, seed_hi);
+  const uint32_t v = (j & 3u) == 0 ? r.x : (j & 3u) == 1 ? r.y : (j & 3u) == 2 ? r.z : r.w;
+  return (float)(v >> 8) * (1.0f / 16777216.0f) < (x - mn) * inv_range;
+}
+
+// agg_j = mean_i (lo_i + sigma_ij * (hi_i - lo_i)) for the 32 coordinates of word `w`, lane `b`
+AFL_HD float afl_scion_agg(const uint32_t* bits, const float* lohi, int C, int64_t words, int64_t w, int b) {
+  float a = 0.f;
+  for (int i = 0; i < C; ++i) {
+    const float lo = lohi[2 * i], hi = lohi[2 * i + 1];
+    a += ((bits[(int64_t)i * words + w] >> b) & 1u) ? hi : lo;
+  }
+  return a / (float)C;
+}
+
 // ----------------------------------------------------------------------------------------- K6
 #define AFL_SEL_MAX 256
 // mode 0: lower median; mode 1: trimmed mean dropping `trim` values at each end.

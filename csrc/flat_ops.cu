@@ -5,6 +5,9 @@
 #include <stdio.h>
 
 #include "../include/attackfl_b200.h"
+#include <algorithm>
+#include <vector>
+
 #include "flat_core.h"
 #include "runtime.h"
 
@@ -56,6 +59,86 @@ __global__ void __launch_bounds__(kThreads) craft_random_kernel(float* out, cons
 __global__ void __launch_bounds__(128) select_kernel(const float* rows, int C, int64_t d_pad, float* out, int mode,
                                                      int trim) {
   afl_select_core(rows, C, d_pad, out, mode, trim, 0, d_pad, blockIdx.x * 128 + threadIdx.x, gridDim.x * 128);
+}
+
+// ---- ScionFL: min/max per row (one block per (chunk, row); partials merged with ordered-int atomics)
+__device__ __forceinline__ unsigned f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__device__ __forceinline__ float ord2f(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u); }
+
+__global__ void __launch_bounds__(256) scion_minmax_kernel(const float* __restrict__ rows, const float* __restrict__ valid,
+                                                           int64_t d_pad, unsigned* __restrict__ ord /* [C][2] */) {
+  const int c = blockIdx.y;
+  const float* row = rows + (int64_t)c * d_pad;
+  float mn = INFINITY, mx = -INFINITY;
+  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < d_pad; j += (int64_t)gridDim.x * 256)
+    if (!valid || valid[j] != 0.f) { const float x = row[j]; mn = fminf(mn, x); mx = fmaxf(mx, x); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(ord + 2 * c, f2ord(mn)); atomicMax(ord + 2 * c + 1, f2ord(mx)); }
+}
+
+// ordered-int encodings of +inf / -inf so atomicMin / atomicMax start from the identity
+__global__ void scion_minmax_init_kernel(unsigned* ord, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) ord[i] = (i & 1) ? 0x007FFFFFu : 0xFF800000u;
+}
+
+__global__ void scion_minmax_finish_kernel(unsigned* ord, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) reinterpret_cast<float*>(ord)[i] = ord2f(ord[i]);
+}
+
+// one thread per coordinate, a warp's ballot is the packed word
+__global__ void __launch_bounds__(256) scion_quantize_kernel(const float* __restrict__ rows, const float* __restrict__ valid,
+                                                             const float* __restrict__ minmax, int64_t d_pad,
+                                                             uint32_t s0, uint32_t s1, uint32_t* __restrict__ bits,
+                                                             int* __restrict__ counts) {
+  const int c = blockIdx.y;
+  const float mn = minmax[2 * c], inv = 1.0f / (minmax[2 * c + 1] - mn + 1e-6f);
+  const float* row = rows + (int64_t)c * d_pad;
+  const int64_t words = d_pad / 32;
+  int cnt = 0;
+  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < d_pad; j += (int64_t)gridDim.x * 256) {
+    const bool ok = !valid || valid[j] != 0.f;
+    const bool bit = ok && afl_scion_bit(row[j], mn, inv, s0, s1, (uint32_t)c, (uint32_t)j);
+    const unsigned w = __ballot_sync(0xffffffffu, bit);
+    if ((threadIdx.x & 31) == 0) { bits[(int64_t)c * words + (j >> 5)] = w; cnt += __popc(w); }
+  }
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(counts + c, cnt);
+}
+
+// one warp per 32-coordinate word; S_c partials live in shared memory until the block is done
+__global__ void __launch_bounds__(256) scion_scores_kernel(const uint32_t* __restrict__ bits, const float* __restrict__ valid,
+                                                           const float* __restrict__ lohi, int C, int64_t d_pad,
+                                                           float* __restrict__ out) {
+  extern __shared__ float acc[];                     // [C + 2]
+  for (int i = threadIdx.x; i < C + 2; i += 256) acc[i] = 0.f;
+  __syncthreads();
+  const int64_t words = d_pad / 32;
+  const int lane = threadIdx.x & 31;
+  float sa = 0.f, sq = 0.f;
+  for (int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < words; w += (int64_t)gridDim.x * 8) {
+    const bool ok = !valid || valid[w * 32 + lane] != 0.f;
+    const float a = ok ? afl_scion_agg(bits, lohi, C, words, w, lane) : 0.f;
+    sa += a; sq += a * a;
+    for (int i = 0; i < C; ++i) {
+      float v = ((bits[(int64_t)i * words + w] >> lane) & 1u) ? a : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && v != 0.f) atomicAdd(acc + i, v);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sa += __shfl_xor_sync(0xffffffffu, sa, o);
+    sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  }
+  if (lane == 0) { atomicAdd(acc + C, sa); atomicAdd(acc + C + 1, sq); }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C + 2; i += 256) if (acc[i] != 0.f) atomicAdd(out + i, acc[i]);
 }
 
 // K6, warp-cooperative version: a block stages a [C][32-coordinate] tile through shared memory (coalesced 128-byte row
@@ -441,6 +524,40 @@ int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mo
   else select_warp_kernel<8><<<grid, 256, smem, st>>>(rows, C, d_pad, out, mode, trim);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_coord_select");
+}
+
+int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && d_pad % 32 == 0, "afl_scion_minmax: C >= 1, d_pad % 32 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  scion_minmax_init_kernel<<<(2 * C + 127) / 128, 128, 0, st>>>(reinterpret_cast<unsigned*>(minmax), 2 * C);
+  const int gx = (int)std::min<int64_t>((d_pad + 4095) / 4096, 64);
+  scion_minmax_kernel<<<dim3(gx, C), 256, 0, st>>>(rows, valid, d_pad, reinterpret_cast<unsigned*>(minmax));
+  scion_minmax_finish_kernel<<<(2 * C + 127) / 128, 128, 0, st>>>(reinterpret_cast<unsigned*>(minmax), 2 * C);
+  afl_rt::count_launch(); afl_rt::count_launch(); afl_rt::count_launch();
+  return afl_rt::check_last("afl_scion_minmax");
+}
+
+int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                       uint32_t* bits, int* counts, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && d_pad % 32 == 0, "afl_scion_quantize: C >= 1, d_pad % 32 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)C, st);
+  const int gx = (int)std::min<int64_t>((d_pad + 2047) / 2048, 128);
+  scion_quantize_kernel<<<dim3(gx, C), 256, 0, st>>>(rows, valid, minmax, d_pad, (uint32_t)seed, (uint32_t)(seed >> 32),
+                                                     bits, counts);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_scion_quantize");
+}
+
+int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out,
+                     void* stream) {
+  AFL_CHECK_ARG(C >= 1 && C <= 4096 && d_pad % 32 == 0, "afl_scion_scores: 1 <= C <= 4096, d_pad % 32 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(out, 0, sizeof(float) * (size_t)(C + 2), st);
+  const int grid = grid_for(d_pad / 32, 8, 4);
+  scion_scores_kernel<<<grid, 256, sizeof(float) * (size_t)(C + 2), st>>>(bits, valid, lohi, C, d_pad, out);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_scion_scores");
 }
 
 // ---- hyper-network (K5a / K5b).  `small`: params | m | v, each hs_total floats (see HyperSmall).

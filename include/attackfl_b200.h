@@ -78,6 +78,20 @@ int afl_craft_random(float* out, const float* w, const float* valid, float pertu
  * dropping `trim` values per side (src/Utils.py:267-302). */
 int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mode, int trim, void* stream);
 
+/* ScionFL building blocks (server.py:436-492, src/Utils.py:372-387) on rows of the flat arena.  `valid` is the 0/1
+ * padding mask of the layout (NULL = every coordinate counts); words = d_pad / 32.
+ *   afl_scion_minmax   : minmax[c] = {min, max} of row c over valid coordinates.
+ *   afl_scion_quantize : bits[c][w] packs sigma ~ Bernoulli((x - min) / (max - min + 1e-6)) (Philox keyed by seed, c,
+ *                        coordinate); counts[c] = number of set bits.
+ *   afl_scion_scores   : from the packed bits and the (possibly L2-clipped) levels lohi[c] = {lo, hi}:
+ *                        out[c] = sum_j sigma_cj * agg_j, out[C] = sum_j agg_j, out[C+1] = sum_j agg_j^2, where
+ *                        agg_j = mean_c (lo_c + sigma_cj (hi_c - lo_c)); the dequantised rows are never built. */
+int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void* stream);
+int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                       uint32_t* bits, int* counts, void* stream);
+int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out,
+                     void* stream);
+
 /* K5a — hyper-network emit: theta[c] = W_h . MLP(E[clients[c]]) + b_h for n clients (src/Model.py:285-304,
  * server.py:589-590,674-678).  small = params|m|v of {emb, mlp}; acts [E+5H] (n==1 only); f_scratch [n*H]. */
 int afl_hyper_emit(const float* head_w, const float* head_b, float* small, int n_nodes, int E, int H,

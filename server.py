@@ -21,6 +21,8 @@ def main(argv=None) -> int:
     cfg = load_config(args.config)
     if args.gpus:
         cfg.runtime.gpus = args.gpus
+    if args.profile:
+        cfg.runtime.profile_round = args.profile
     from attackfl_b200.parallel import launch
     rc = launch.maybe_relaunch(cfg.runtime.gpus)           # one process per GPU (re-exec under torchrun)
     if rc is not None:

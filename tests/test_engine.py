@@ -125,3 +125,26 @@ def test_har_round(tmp_path):
     fed = Federation(from_dict(d), _specs(2), device="cpu", workdir=str(tmp_path), verbose=False)
     res = fed.run()
     assert res[0].ok and 0.0 <= res[0].metric <= 1.0
+
+
+def test_fault_injection_retries_the_round(tmp_path):
+    """SURVEY 5.3: a NaN loss (client.py:100-102) or a diverged update discards the round and re-issues it;
+    ``round`` only advances on success (server.py:555)."""
+    from attackfl_b200.utils.timers import Watchdog
+    cfg = _cfg("fedavg", "TransformerModel", 3, rounds=3)
+    cfg.runtime.fault_inject = [{"attempt": 2, "client": 1, "kind": "nan-loss"},
+                                {"attempt": 4, "client": 0, "kind": "nan-weights"}]
+    fed = Federation(cfg, [ClientSpec(i) for i in range(3)], device="cpu", workdir=str(tmp_path), verbose=False)
+    res = fed.run()
+    assert [r.ok for r in res] == [True, False, True, False, True]
+    assert [r.round for r in res] == [1, 2, 2, 3, 3]
+    assert fed.remaining == 0
+    fired = []
+    wd = Watchdog(0.05, on_expire=fired.append)
+    wd.arm("round attempt 1")
+    import time
+    time.sleep(0.2)
+    assert fired == ["round attempt 1"] and wd.expired
+    wd2 = Watchdog(0.05, on_expire=fired.append)
+    wd2.arm("x"); wd2.disarm(); time.sleep(0.1)
+    assert len(fired) == 1

@@ -161,3 +161,36 @@ def test_hyper_emit_and_step_match_torch(device):
     for k in exp:
         assert torch.allclose(got[k], exp[k], atol=3e-6, rtol=1e-4), k
     assert fused.step == ref.step == n
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_scion_quantize_and_scores(device):
+    """ScionFL pieces (src/Utils.py:372-387, server.py:443-466): the packed-bit pass against the plain fp32 maths
+    evaluated on the very same bits, plus the Bernoulli statistics of the quantiser."""
+    c, d_pad = 9, 4096
+    rows = _rand_rows(c, d_pad, device, seed=4, spread=0.5)
+    rows[3] *= 25.0                                            # one client far above the 3x mean L2 cap
+    valid = torch.ones(d_pad, device=device)
+    valid[-70:] = 0
+    rows[:, -70:] = 0
+    cosd, aux = flat.scion_cosine_distances(rows, valid, seed=11)
+    bits, counts, minmax = aux["bits"].cpu(), aux["counts"].cpu(), aux["minmax"].cpu()
+    dense = rows.cpu()[:, :-70]
+    assert torch.equal(minmax[:, 0], dense.min(1).values) and torch.equal(minmax[:, 1], dense.max(1).values)
+    sigma = ((bits[:, :, None] >> torch.arange(32)) & 1).reshape(c, d_pad).float()
+    assert float(sigma[:, -70:].sum()) == 0.0
+    sigma = sigma[:, :-70]
+    assert torch.equal(sigma.sum(1).int(), counts)
+    probs = (dense - minmax[:, :1]) / (minmax[:, 1:] - minmax[:, :1] + 1e-6)
+    dev = (sigma.sum(1) - probs.sum(1)).abs() / (probs * (1 - probs)).sum(1).sqrt()
+    assert float(dev.max()) < 4.5                              # counts within 4.5 sigma of their expectation
+    assert abs(float(((sigma - probs) * (probs - 0.5)).mean())) < 0.01
+    lohi = aux["lohi"].cpu().float()
+    want = agg.scion_dequant_scores(sigma, lohi[:, 0], lohi[:, 1])
+    assert torch.allclose(cosd.cpu(), want, atol=2e-5)
+    assert lohi[3, 1] < minmax[3, 1] * 0.9                     # the outlier was clipped
+    again, _ = flat.scion_cosine_distances(rows, valid, seed=11)
+    other, _ = flat.scion_cosine_distances(rows, valid, seed=12)
+    assert torch.allclose(cosd, again, atol=1e-6) and not torch.allclose(cosd, other, atol=1e-7)
+    out, kept = agg.scionfl(rows, [1.0] * c, valid=valid.bool(), scores=cosd.tolist())
+    assert 1 <= len(kept) < c and out.shape == (d_pad,)
