@@ -78,6 +78,22 @@ int afl_craft_random(float* out, const float* w, const float* valid, float pertu
  * dropping `trim` values per side (src/Utils.py:267-302). */
 int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mode, int trim, void* stream);
 
+/* HAR linear layers on tcgen05 (kind::tf32 on fp32 data, fp32 accumulate): nn.Linear inside nn.TransformerEncoderLayer
+ * and its autograd (src/Model.py:435-458, client.py:114-131).  All matrices row-major and contiguous, N and K multiples
+ * of 32 in [32, 256], pointers 16-byte aligned.
+ *   fwd : Y[M,N] = dropout(relu?(X[M,K] . W[N,K]^T + bias)); dropout keep decision = afl_dropout_keep's Philox stream
+ *         (seed, rng_client, rng_step, sample = row, rng_id, elem = column).
+ *   dx  : dX[M,K] (+)= (dY[M,N] . W[N,K]) * (mask_src[M,K] > 0 ? mask_scale : 0)   (mask_src NULL = no mask)
+ *   dw  : dW[N,K] (+)= dY^T . X, db[N] (+)= column sums of dY (db NULL = skip); partials: scratch of
+ *         afl_tc_linear_dw_workspace floats. */
+int afl_tc_linear_fwd(const float* X, int64_t M, int K, const float* W, int N, const float* bias, int relu, float drop_p,
+                      uint64_t seed, uint32_t rng_client, uint32_t rng_step, uint32_t rng_id, float* Y, void* stream);
+int afl_tc_linear_dx(const float* dY, int64_t M, int N, const float* W, int K, const float* mask_src, float mask_scale,
+                     int accumulate, float* dX, void* stream);
+int afl_tc_linear_dw_workspace(int N, int K, int64_t* partial_floats);
+int afl_tc_linear_dw(const float* dY, const float* X, int64_t M, int N, int K, float* partials, float* dW, float* db,
+                     int accumulate, void* stream);
+
 /* ScionFL building blocks (server.py:436-492, src/Utils.py:372-387) on rows of the flat arena.  `valid` is the 0/1
  * padding mask of the layout (NULL = every coordinate counts); words = d_pad / 32.
  *   afl_scion_minmax   : minmax[c] = {min, max} of row c over valid coordinates.

@@ -1,0 +1,75 @@
+"""tcgen05 linear kernels (csrc/gemm_tcgen05.cu) against plain fp32 PyTorch; TF32 operands => ~1e-3 relative."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(64, 64), (192, 64), (256, 64), (64, 256), (32, 32), (128, 96)]     # (N, K): out_proj, in_proj, ffn1, ffn2
+
+
+def _close(got, want, tol=4e-3):
+    scale = want.abs().max().item() + 1e-12
+    err = (got - want).abs().max().item() / scale
+    assert err < tol, f"relative error {err:.3e}"
+
+
+def _mk(m, n, k, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(m, k, device="cuda", generator=g)
+    w = torch.randn(n, k, device="cuda", generator=g) / k ** 0.5
+    b = torch.randn(n, device="cuda", generator=g)
+    dy = torch.randn(m, n, device="cuda", generator=g)
+    return x, w, b, dy
+
+
+@pytest.mark.parametrize("n,k", SHAPES)
+@pytest.mark.parametrize("m", [128, 1000, 5 * 561])
+def test_linear_fwd(m, n, k):
+    from attackfl_b200.ops import tc_linear as tc
+    x, w, b, _ = _mk(m, n, k)
+    _close(tc.linear_fwd(x, w, b), x @ w.t() + b)
+    _close(tc.linear_fwd(x, w, None, relu=True), torch.relu(x @ w.t()))
+
+
+@pytest.mark.parametrize("n,k", SHAPES)
+@pytest.mark.parametrize("m", [128, 1000, 5 * 561])
+def test_linear_dx_dw(m, n, k):
+    from attackfl_b200.ops import tc_linear as tc
+    x, w, b, dy = _mk(m, n, k, seed=1)
+    _close(tc.linear_dx(dy, w), dy @ w)
+    mask = torch.randn(m, k, device="cuda")
+    _close(tc.linear_dx(dy, w, mask_src=mask, mask_scale=1.25), (dy @ w) * (mask > 0) * 1.25)
+    acc = torch.randn(m, k, device="cuda")
+    want = acc + dy @ w
+    _close(tc.linear_dx(dy, w, out=acc, accumulate=True), want)
+    dw, db = tc.linear_dw(dy, x)
+    _close(dw, dy.t() @ x)
+    _close(db, dy.sum(0), tol=1e-4)
+    dw2, db2 = tc.linear_dw(dy, x, dw=dw.clone(), db=db.clone(), accumulate=True)
+    _close(dw2, 2 * (dy.t() @ x))
+    _close(db2, 2 * dy.sum(0), tol=1e-4)
+
+
+def test_linear_dropout_matches_philox_stream():
+    from attackfl_b200.ops import tc_linear as tc
+    from attackfl_b200.ops import train as nt
+    m, n, k = 300, 64, 64
+    x, w, b, _ = _mk(m, n, k, seed=2)
+    y = tc.linear_fwd(x, w, b, relu=True, drop_p=0.25, seed=99, rng=(3, 7, 11))
+    ref = torch.relu(x @ w.t() + b)
+    keep = torch.tensor([[float(nt.dropout_keep(99, 3, 7, r, 11, c, 0.25)) for c in range(n)] for r in range(4)],
+                        device="cuda")
+    _close(y[:4], ref[:4] * keep / 0.75)
+    frac = (y != 0).float().sum() / (ref != 0).float().sum()
+    assert abs(frac.item() - 0.75) < 0.02
+
+
+def test_autograd_function_matches_linear():
+    from attackfl_b200.ops.tc_linear import TcLinear
+    x, w, b, dy = _mk(640, 256, 64, seed=3)
+    xs = [t.clone().requires_grad_(True) for t in (x, w, b)]
+    xr = [t.clone().requires_grad_(True) for t in (x, w, b)]
+    TcLinear.apply(xs[0], xs[1], xs[2], True).backward(dy)
+    torch.relu(torch.nn.functional.linear(*xr)).backward(dy)
+    for a, r in zip(xs, xr):
+        _close(a.grad, r.grad)
