@@ -94,6 +94,37 @@ int afl_tc_linear_dw_workspace(int N, int K, int64_t* partial_floats);
 int afl_tc_linear_dw(const float* dY, const float* X, int64_t M, int N, int K, float* partials, float* dW, float* db,
                      int accumulate, void* stream);
 
+/* HAR TransformerClassifier training kernels (src/Model.py:420-458, client.py:114-131); activations are [B*T, 64]
+ * row-major with row = b*T + t; d_model 64, 4 heads of 16.  Dropout masks are Philox functions of
+ * (seed, client, step, row, site, column) and are recomputed in the backward kernels.
+ *   embed_fwd : out = Conv1d(1->64, k3, p1)(x) + pe[t]          embed_bwd : dconv_w, dconv_b += ...
+ *   add_ln_fwd: y = LayerNorm(x + dropout(r)); saves xhat, rstd   (r NULL: plain LayerNorm)
+ *   ln_bwd    : dres = d/d(x + dropout(r)); dr = dres * mask (NULL: skip); dgamma, dbeta += ...;
+ *               dy_bcast [B,64] with bscale: dy[row] = dy_bcast[row / T] * bscale (mean-pool backward fused)
+ *   attn_fwd  : softmax(q k^T / 4) with attention-weight dropout, times v, per (sample, head); lse in base-2 units
+ *   attn_bwd  : dqkv [B*T,192] from dout (two kernels: dQ per query, dK/dV per key)
+ *   pool_fwd  : pooled[b] = mean_t h[b,t]
+ *   head      : Linear(64,64)-ReLU-Dropout-Linear(64,n_cls) + mean cross-entropy, forward and backward in one
+ *               kernel; out3 += {sum of per-sample losses, NaN/Inf count, correct predictions}. */
+int afl_har_embed_fwd(const float* x, const float* conv_w, const float* conv_b, const float* pe, int B, int T, float* out,
+                      void* stream);
+int afl_har_embed_bwd(const float* dh, const float* x, int B, int T, float* dconv_w, float* dconv_b, void* stream);
+int afl_har_add_ln_fwd(const float* x, const float* r, float drop_p, uint64_t seed, uint32_t client, uint32_t step,
+                       uint32_t site, const float* gamma, const float* beta, int64_t M, float* y, float* xhat, float* rstd,
+                       void* stream);
+int afl_har_ln_bwd(const float* dy, const float* dy_bcast, int T, float bscale, const float* xhat, const float* rstd,
+                   const float* gamma, float drop_p, uint64_t seed, uint32_t client, uint32_t step, uint32_t site, int64_t M,
+                   float* dres, float* dr, float* dgamma, float* dbeta, void* stream);
+int afl_har_attn_fwd(const float* qkv, int B, int T, float drop_p, uint64_t seed, uint32_t client, uint32_t step,
+                     uint32_t site, float* out, float* lse, void* stream);
+int afl_har_attn_bwd(const float* qkv, const float* out, const float* dout, const float* lse, int B, int T, float drop_p,
+                     uint64_t seed, uint32_t client, uint32_t step, uint32_t site, float* dqkv, void* stream);
+int afl_har_pool_fwd(const float* h, int B, int T, float* pooled, void* stream);
+int afl_har_head(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
+                 const int64_t* labels, int B, int n_cls, float drop_p, uint64_t seed, uint32_t client, uint32_t step,
+                 uint32_t site, int train, float* logits, float* out3, float* dpooled, float* dw1, float* db1, float* dw2,
+                 float* db2, void* stream);
+
 /* ScionFL building blocks (server.py:436-492, src/Utils.py:372-387) on rows of the flat arena.  `valid` is the 0/1
  * padding mask of the layout (NULL = every coordinate counts); words = d_pad / 32.
  *   afl_scion_minmax   : minmax[c] = {min, max} of row c over valid coordinates.

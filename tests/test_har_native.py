@@ -1,0 +1,148 @@
+"""Native HAR trainer (tcgen05 linears + har_kernels.cu) against the PyTorch module (fp32 autograd)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
+
+
+def _setup(B=6, seed=0):
+    from attackfl_b200 import FlatLayout, models
+    from attackfl_b200.ops.har import HarNativeTrainer
+    torch.manual_seed(seed)
+    mod = models.TransformerClassifier().cuda()
+    for m in mod.modules():                       # dropout off: masks of the two implementations are different streams
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+        if isinstance(m, torch.nn.MultiheadAttention):
+            m.dropout = 0.0
+    mod.train()
+    lay = FlatLayout.from_module(mod) if hasattr(FlatLayout, "from_module") else FlatLayout(mod.state_dict())
+    row = lay.flatten(mod.state_dict(), device="cuda")
+    tr = HarNativeTrainer(lay, "cuda", max_batch=max(B, 8))
+    x = torch.randn(B, 561, device="cuda")
+    y = torch.randint(0, 6, (B,), device="cuda")
+    return mod, lay, row, tr, x, y
+
+
+def test_attention_kernels_match_sdpa():
+    from attackfl_b200.ops import har
+    from attackfl_b200.ops.native import cuda_lib, ptr, check
+    import ctypes
+    B, T = 3, 561
+    lib = cuda_lib()
+    qkv = torch.randn(B * T, 192, device="cuda")
+    out = torch.empty(B * T, 64, device="cuda"); lse = torch.empty(B * 4 * T, device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    check(lib, lib.afl_har_attn_fwd(ptr(qkv), B, T, ctypes.c_float(0.0), ctypes.c_uint64(0), 0, 0, 0, ptr(out), ptr(lse), st))
+    q, k, v = (qkv[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2) for i in range(3))
+    qr, kr, vr = (t.detach().clone().requires_grad_(True) for t in (q, k, v))
+    ref = torch.nn.functional.scaled_dot_product_attention(qr, kr, vr)
+    assert _rel(out.reshape(B, T, 4, 16).transpose(1, 2), ref) < 1e-4
+    dout = torch.randn(B * T, 64, device="cuda")
+    dqkv = torch.zeros(B * T, 192, device="cuda")
+    check(lib, lib.afl_har_attn_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), B, T, ctypes.c_float(0.0), ctypes.c_uint64(0), 0,
+                                    0, 0, ptr(dqkv), st))
+    ref.backward(dout.reshape(B, T, 4, 16).transpose(1, 2))
+    for i, gr in enumerate((qr.grad, kr.grad, vr.grad)):
+        got = dqkv[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2)
+        assert _rel(got, gr) < 2e-4, i
+
+
+def test_attention_dropout_is_consistent():
+    """With dropout the three kernels must agree on the mask: finite differences of the forward output against the
+    analytic gradients, and the kept fraction."""
+    from attackfl_b200.ops.native import cuda_lib, ptr, check
+    import ctypes
+    B, T, p = 1, 100, 0.3
+    lib = cuda_lib()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    qkv = torch.randn(B * T, 192, device="cuda")
+    dout = torch.randn(B * T, 64, device="cuda")
+
+    def fwd(t):
+        o = torch.empty(B * T, 64, device="cuda"); l = torch.empty(B * 4 * T, device="cuda")
+        check(lib, lib.afl_har_attn_fwd(ptr(t), B, T, ctypes.c_float(p), ctypes.c_uint64(5), 1, 2, 3, ptr(o), ptr(l), st))
+        return o, l
+    out, lse = fwd(qkv)
+    dqkv = torch.zeros_like(qkv)
+    check(lib, lib.afl_har_attn_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), B, T, ctypes.c_float(p), ctypes.c_uint64(5), 1, 2,
+                                    3, ptr(dqkv), st))
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for _ in range(6):
+        d = torch.randn(qkv.shape, device="cuda", generator=g)
+        eps = 1e-2
+        fd = ((fwd(qkv + eps * d)[0] - fwd(qkv - eps * d)[0]) * dout).sum() / (2 * eps)
+        an = (dqkv * d).sum()
+        assert abs(fd.item() - an.item()) < 2e-2 * max(1.0, abs(an.item())), (fd.item(), an.item())
+    # v = 1 => output = kept mass / (1 - p): mean 1, so the kept fraction is ~ 1 - p
+    ones = qkv.clone(); ones[:, 128:] = 1.0
+    assert abs(fwd(ones)[0].mean().item() - 1.0) < 0.05
+
+
+def test_forward_logits_match_module():
+    mod, lay, row, tr, x, y = _setup()
+    mod.eval()
+    with torch.no_grad():
+        want = mod(x[:, None, :])
+    got = tr.logits_of(row, x)
+    assert _rel(got, want) < 5e-3
+
+
+def test_grad_step_matches_autograd():
+    mod, lay, row, tr, x, y = _setup(B=5, seed=1)
+    loss = torch.nn.functional.cross_entropy(mod(x[:, None, :]), y)
+    loss.backward()
+    want = {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in mod.named_parameters()}
+    grad = torch.zeros_like(row)
+    tr.out3.zero_()
+    out3 = tr.grad_step(row, grad, x, y, dropout=False)
+    assert abs(out3[0].item() / 5 - loss.item()) < 2e-3 * max(1.0, abs(loss.item()))
+    assert out3[1].item() == 0
+    got = lay.views(grad)
+    worst = {}
+    for k, w in want.items():
+        worst[k] = _rel(got[k], w)
+    bad = {k: round(v, 4) for k, v in worst.items() if v > 2e-2}
+    assert not bad, bad
+
+
+def test_training_trajectory_matches_torch():
+    """Six Adam steps (dropout off): the loss sequence of the native trainer follows PyTorch's."""
+    from attackfl_b200.ops import flat
+    mod, lay, row, tr, x, y = _setup(B=8, seed=2)
+    opt = torch.optim.Adam(mod.parameters(), lr=2e-3)
+    grad, m, v = torch.zeros_like(row), torch.zeros_like(row), torch.zeros_like(row)
+    got, want = [], []
+    for step in range(1, 7):
+        tr.out3.zero_()
+        tr.grad_step(row, grad, x, y, dropout=False)
+        got.append(tr.out3[0].item() / 8)
+        flat.adam_flat(row, grad, m, v, 2e-3, step)
+        opt.zero_grad()
+        loss = torch.nn.functional.cross_entropy(mod(x[:, None, :]), y)
+        loss.backward()
+        opt.step()
+        want.append(loss.item())
+    assert want[-1] < want[0]
+    for a, b in zip(got, want):
+        assert abs(a - b) < 3e-2 * max(1.0, abs(b)), (got, want)
+
+
+def test_dropout_step_is_deterministic_per_seed():
+    mod, lay, row, tr, x, y = _setup(B=4, seed=3)
+    grad = torch.zeros_like(row)
+
+    def run(seed, step):
+        tr.out3.zero_()
+        tr.grad_step(row, grad, x, y, seed=seed, client=1, step=step, dropout=True)
+        return tr.out3[0].item(), grad.clone()
+    l1, g1 = run(7, 1)
+    l2, g2 = run(7, 1)
+    l3, g3 = run(7, 2)
+    assert l1 == l2 and torch.equal(g1, g2)
+    assert l1 != l3 and not torch.equal(g1, g3)
+    assert torch.isfinite(g1).all() and tr.out3[1].item() == 0

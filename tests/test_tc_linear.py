@@ -68,8 +68,10 @@ def test_autograd_function_matches_linear():
     from attackfl_b200.ops.tc_linear import TcLinear
     x, w, b, dy = _mk(640, 256, 64, seed=3)
     xs = [t.clone().requires_grad_(True) for t in (x, w, b)]
-    xr = [t.clone().requires_grad_(True) for t in (x, w, b)]
-    TcLinear.apply(xs[0], xs[1], xs[2], True).backward(dy)
-    torch.relu(torch.nn.functional.linear(*xr)).backward(dy)
-    for a, r in zip(xs, xr):
-        _close(a.grad, r.grad)
+    y = TcLinear.apply(xs[0], xs[1], xs[2], True)
+    y.backward(dy)
+    _close(y, torch.relu(torch.nn.functional.linear(x, w, b)))
+    g = dy * (y > 0)              # same ReLU mask: pre-activations within TF32 error of 0 may flip in the fp32 oracle
+    _close(xs[0].grad, g @ w)
+    _close(xs[1].grad, g.t() @ x)
+    _close(xs[2].grad, g.sum(0), tol=1e-4)
