@@ -104,6 +104,14 @@ class Federation:
             raise ValueError(f"no native training program for {self.model_name}/{self.data_name}")
         self.backend = backend
         self.train_prog = self.infer_prog = None
+        # HAR: native trainer (tcgen05 linears + attention / LayerNorm kernels) on CUDA unless backend: torch is forced
+        self.har_trainer = None
+        if (self.data_name == "HAR" and self.model_name == "TransformerClassifier" and self.device.type == "cuda"
+                and cfg.runtime.backend in ("auto", "native")):
+            from .ops.har import HarNativeTrainer
+            self.har_trainer = HarNativeTrainer(self.layout, self.device, max_batch=min(max(cfg.learning.batch_size, 1), 128))
+            if cfg.learning.batch_size > 128:
+                self.har_trainer = None                           # buffers are sized for the reference's batch (<= 128)
         if backend == "native":
             from .ops import train as T
             self.T = T
@@ -327,6 +335,44 @@ class Federation:
                         for k, v in self.layout.views(row).items():
                             params[k].copy_(v)
                     loss_out[j, 0] += loss.detach() * ii.numel()
+        return loss_out
+
+    def _train_har_native(self, sizes_local: List[int]) -> torch.Tensor:
+        """HAR local training (``train_HAR``, client.py:114-131) with the native step: per batch one forward + backward
+        through ``ops.har`` (gradients written in arena layout) and one fused flat Adam / SGD launch; no host sync."""
+        from .ops import flat
+        l = self.cfg.learning
+        tr = self.har_trainer
+        loss_out = torch.zeros(self.CL, 2, device=self.device)
+        idx = make_round_indices(self.n_train, [max(s, 1) for s in sizes_local], l.epoch, self.dev_gen, self.device)
+        seed = (int(self.cfg.server.random_seed or 0) << 20) ^ (self.attempt * 2654435761 & 0xFFFFFFFF)
+        if not hasattr(self, "_har_grad"):
+            self._har_grad = torch.zeros(self.D, device=self.device)
+        g = self._har_grad
+        x_all = self.train_x.reshape(self.train_x.shape[0], -1)
+        for j in range(self.CL):
+            n = sizes_local[j]
+            if n == 0:
+                continue
+            row = self.rows[j]
+            self.m[j].zero_(); self.v[j].zero_()
+            tr.out3.zero_()
+            step = 0
+            for e in range(l.epoch):
+                for s0 in range(0, n, l.batch_size):
+                    ii = idx[j, e, s0:min(n, s0 + l.batch_size)].long()
+                    step += 1
+                    tr.grad_step(row, g, x_all[ii], self.train_y[ii], seed=seed, client=self.local[j], step=step,
+                                 dropout=l.dropout)
+                    gs = None
+                    if l.clip_mode == "proper" and l.clip_grad_norm > 0:
+                        gs = torch.clamp(l.clip_grad_norm / (g.norm() + 1e-6), max=1.0).reshape(1)
+                    if l.optimizer == "adam":
+                        flat.adam_flat(row, g, self.m[j], self.v[j], l.learning_rate, step, gscale=gs)
+                    else:
+                        flat.sgdm_flat(row, g, self.m[j], l.learning_rate, l.momentum, step == 1, gscale=gs)
+            loss_out[j, 0] = tr.out3[0]
+            loss_out[j, 1] = tr.out3[1]
         return loss_out
 
     # ================================================================================== attacks
@@ -630,6 +676,12 @@ class Federation:
                 probs = torch.stack(outs)
             labels = self.test_labels[None].expand(probs.shape[0], -1)
             return self.validator.score_icu(probs.reshape(-1), labels.reshape(-1))
+        if self.har_trainer is not None:
+            tx = self.test_x.reshape(self.test_x.shape[0], -1)
+            mb = self.har_trainer.max_batch
+            logits = torch.cat([self.har_trainer.logits_of(self.global_row, tx[i:i + mb]).clone()
+                                for i in range(0, tx.shape[0], mb)])
+            return self.validator.score_har(logits, self.test_y)
         mod = self.module.to(self.device).eval()
         with torch.no_grad():
             logits = torch.cat([torch.func.functional_call(mod, dict(self.layout.views(self.global_row)), (self.test_x[i:i + 256],))
@@ -694,7 +746,10 @@ class Federation:
         sizes_local = [0 if (c in active_attackers or c not in starting) else self.sizes[c] for c in self.local]
         with self.timer.phase("train"):
             if self.CL > 0:
-                loss = self._train_native(sizes_local) if self.backend == "native" else self._train_torch(sizes_local)
+                if self.har_trainer is not None:
+                    loss = self._train_har_native(sizes_local)
+                else:
+                    loss = self._train_native(sizes_local) if self.backend == "native" else self._train_torch(sizes_local)
             else:
                 loss = torch.zeros(1, 2, device=self.device)
         for c in self._faults("nan-loss"):                        # client c reports result=False (client.py:100-102)
