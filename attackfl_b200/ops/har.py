@@ -14,6 +14,7 @@ count and the number of correct predictions accumulate in a 3-float device buffe
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, Optional
 
 import torch
@@ -40,6 +41,8 @@ class HarNativeTrainer:
         self.layout, self.device = layout, torch.device(device)
         self.lib = cuda_lib()
         self.T, self.n_cls, self.max_batch = seq_len, n_classes, max_batch
+        # attention forward: tcgen05 kernel when K/V of a head pair fit in shared memory, else the FFMA kernel
+        self.attn_tc = bool(self.lib.afl_har_attn_tc_supported(c_i(seq_len))) and os.environ.get("ATTACKFL_HAR_ATTN", "tc") != "ffma"
         m = max_batch * seq_len
         z = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.device)          # noqa: E731
         self.h0 = z(m, D_MODEL)
@@ -76,8 +79,9 @@ class HarNativeTrainer:
             pre = f"transformer.layers.{l}."
             rng = (client, step)
             tc.linear_fwd(h[:M], w[pre + "self_attn.in_proj_weight"], w[pre + "self_attn.in_proj_bias"], out=a["qkv"][:M])
-            self._ck(lib.afl_har_attn_fwd(ptr(a["qkv"]), c_i(B), c_i(T), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
-                                          c_u32(16 * l + SITE_ATTN), ptr(a["att"]), ptr(a["lse"]), st), "afl_har_attn_fwd")
+            attn = lib.afl_har_attn_fwd_tc if self.attn_tc else lib.afl_har_attn_fwd
+            self._ck(attn(ptr(a["qkv"]), c_i(B), c_i(T), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
+                          c_u32(16 * l + SITE_ATTN), ptr(a["att"]), ptr(a["lse"]), st), "afl_har_attn_fwd")
             tc.linear_fwd(a["att"][:M], w[pre + "self_attn.out_proj.weight"], w[pre + "self_attn.out_proj.bias"],
                           out=a["sa"][:M])
             self._ck(lib.afl_har_add_ln_fwd(ptr(h), ptr(a["sa"]), c_f(p), c_u64(seed), c_u32(client), c_u32(step),

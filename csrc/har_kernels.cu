@@ -13,6 +13,7 @@
 
 #include "../include/attackfl_b200.h"
 #include "common.h"
+#include "har_rng.cuh"
 #include "runtime.h"
 
 namespace {
@@ -22,12 +23,7 @@ constexpr int NH = 4;          // heads
 constexpr int DH = 16;         // head dim
 constexpr float kLnEps = 1e-5f;
 
-struct Rng { uint32_t s0, s1, client, step, site; float p; };
-
-__device__ __forceinline__ AflU4 rng4(const Rng& r, uint32_t row, uint32_t col) {
-  return afl_philox(col >> 2, (r.site & 0xFFFFu) | (r.client << 16), r.step, row, r.s0, r.s1);
-}
-__device__ __forceinline__ float u01(uint32_t v) { return (float)(v >> 8) * (1.0f / 16777216.0f); }
+using namespace afl_har;
 
 // ------------------------------------------------------------------------------------------ conv embedding + PE
 __global__ void __launch_bounds__(256) embed_fwd_kernel(const float* __restrict__ x, const float* __restrict__ cw,
@@ -214,6 +210,7 @@ __global__ void __launch_bounds__(kQB) attn_fwd_kernel(const float* __restrict__
   float m = -INFINITY, l = 0.f;
   const float inv_keep = rng.p > 0.f ? 1.0f / (1.0f - rng.p) : 1.f;
   Rng hr = rng; hr.site = rng.site + (uint32_t)h;
+  const uint32_t thr = attn_thr(rng.p);
   for (int k0 = 0; k0 < T; k0 += kKC) {
     const int nv = min(kKC, T - k0);
     __syncthreads();
@@ -238,17 +235,13 @@ __global__ void __launch_bounds__(kQB) attn_fwd_kernel(const float* __restrict__
         for (int d = 0; d < DH; ++d) o[d] *= c;
         m = mx;
       }
-      uint32_t rw[8];
-      if (rng.p > 0.f) {
-        const AflU4 r0 = rng4(hr, (uint32_t)(base + qi), (uint32_t)(k0 + j0));
-        const AflU4 r1 = rng4(hr, (uint32_t)(base + qi), (uint32_t)(k0 + j0 + 4));
-        rw[0] = r0.x; rw[1] = r0.y; rw[2] = r0.z; rw[3] = r0.w; rw[4] = r1.x; rw[5] = r1.y; rw[6] = r1.z; rw[7] = r1.w;
-      }
+      AflU4 rw; rw.x = rw.y = rw.z = rw.w = 0u;
+      if (rng.p > 0.f) rw = attn_call(hr, (uint32_t)(base + qi), (uint32_t)(k0 + j0));
 #pragma unroll
       for (int jj = 0; jj < 8; ++jj) {
         float p = exp2f(s[jj] - m);
         l += p;
-        if (rng.p > 0.f) p = u01(rw[jj]) >= rng.p ? p * inv_keep : 0.f;
+        if (rng.p > 0.f) p = attn_bits(rw.x, rw.y, rw.z, rw.w, (uint32_t)jj) >= thr ? p * inv_keep : 0.f;
 #pragma unroll
         for (int d = 0; d < DH; ++d) o[d] = fmaf(p, vs[j0 + jj][d], o[d]);
       }
@@ -293,26 +286,24 @@ __global__ void __launch_bounds__(kQB) attn_bwd_dq_kernel(const float* __restric
   }
   const float inv_keep = rng.p > 0.f ? 1.0f / (1.0f - rng.p) : 1.f;
   Rng hr = rng; hr.site = rng.site + (uint32_t)h;
+  const uint32_t thr = attn_thr(rng.p);
   for (int k0 = 0; k0 < T; k0 += kKC) {
     const int nv = min(kKC, T - k0);
     __syncthreads();
     load_kv_chunk(qkv, base + k0, nv, h, ks, vs);
     __syncthreads();
     if (!live) continue;
-    for (int j0 = 0; j0 < nv; j0 += 4) {
-      uint32_t rw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      if (rng.p > 0.f) {
-        const AflU4 r0 = rng4(hr, (uint32_t)(base + qi), (uint32_t)(k0 + j0));
-        rw[0] = r0.x; rw[1] = r0.y; rw[2] = r0.z; rw[3] = r0.w;
-      }
+    for (int j0 = 0; j0 < nv; j0 += 8) {
+      AflU4 rw; rw.x = rw.y = rw.z = rw.w = 0u;
+      if (rng.p > 0.f) rw = attn_call(hr, (uint32_t)(base + qi), (uint32_t)(k0 + j0));
 #pragma unroll
-      for (int jj = 0; jj < 4; ++jj) {
+      for (int jj = 0; jj < 8; ++jj) {
         if (j0 + jj >= nv) break;
         float s = 0.f, dpd = 0.f;
 #pragma unroll
         for (int d = 0; d < DH; ++d) { s = fmaf(q[d], ks[j0 + jj][d], s); dpd = fmaf(go[d], vs[j0 + jj][d], dpd); }
         const float p = exp2f(s - L);
-        const float keep = (rng.p > 0.f) ? (u01(rw[jj]) >= rng.p ? inv_keep : 0.f) : 1.f;
+        const float keep = (rng.p > 0.f) ? (attn_bits(rw.x, rw.y, rw.z, rw.w, (uint32_t)jj) >= thr ? inv_keep : 0.f) : 1.f;
         const float ds = p * (keep * dpd - delta);
 #pragma unroll
         for (int d = 0; d < DH; ++d) dq[d] = fmaf(ds, ks[j0 + jj][d], dq[d]);
@@ -354,6 +345,7 @@ __global__ void __launch_bounds__(kQB) attn_bwd_dkv_kernel(const float* __restri
   }
   const float inv_keep = rng.p > 0.f ? 1.0f / (1.0f - rng.p) : 1.f;
   Rng hr = rng; hr.site = rng.site + (uint32_t)h;
+  const uint32_t thr = attn_thr(rng.p);
   for (int q0 = 0; q0 < T; q0 += kKC) {
     const int nv = min(kKC, T - q0);
     __syncthreads();
@@ -383,24 +375,23 @@ __global__ void __launch_bounds__(kQB) attn_bwd_dkv_kernel(const float* __restri
       dsm[j] = de; lsm[j] = Lv;
     }
     __syncthreads();
-    // The dropout word of (query i, key j) is component j&3 of the Philox call (row i, j>>2): the four lanes that share
-    // j>>2 each evaluate the call for one of four consecutive queries and exchange the words with shuffles.
-    for (int i0 = 0; i0 < nv; i0 += 4) {
+    // The dropout bits of (query i, key j) come from the Philox call (row i, j>>3): the eight lanes that share j>>3 each
+    // evaluate the call for one of eight consecutive queries and exchange the words with shuffles.
+    for (int i0 = 0; i0 < nv; i0 += 8) {
       AflU4 mine; mine.x = mine.y = mine.z = mine.w = 0xffffffffu;
-      if (rng.p > 0.f) mine = rng4(hr, (uint32_t)(base + q0 + i0 + (lane & 3)), (uint32_t)(kj & ~3));
+      if (rng.p > 0.f) mine = attn_call(hr, (uint32_t)(base + q0 + i0 + (lane & 7)), (uint32_t)kj);
 #pragma unroll
-      for (int ii = 0; ii < 4; ++ii) {
-        const int src = (lane & ~3) | ii;
+      for (int ii = 0; ii < 8; ++ii) {
+        const int src = (lane & ~7) | ii;
         const uint32_t wx = __shfl_sync(0xffffffffu, mine.x, src), wy = __shfl_sync(0xffffffffu, mine.y, src);
         const uint32_t wz = __shfl_sync(0xffffffffu, mine.z, src), ww = __shfl_sync(0xffffffffu, mine.w, src);
         const int i = i0 + ii;
         if (i >= nv || !live) continue;
-        const uint32_t word = (kj & 3) == 0 ? wx : (kj & 3) == 1 ? wy : (kj & 3) == 2 ? wz : ww;
         float s = 0.f, dpd = 0.f;
 #pragma unroll
         for (int d = 0; d < DH; ++d) { s = fmaf(qsm[i][d], k[d], s); dpd = fmaf(gsm[i][d], v[d], dpd); }
         const float p = exp2f(s - lsm[i]);
-        const float keep = (rng.p > 0.f) ? (u01(word) >= rng.p ? inv_keep : 0.f) : 1.f;
+        const float keep = (rng.p > 0.f) ? (attn_bits(wx, wy, wz, ww, (uint32_t)kj) >= thr ? inv_keep : 0.f) : 1.f;
         const float pd = p * keep;
         const float ds = p * (keep * dpd - dsm[i]);
 #pragma unroll

@@ -119,6 +119,12 @@ int afl_har_attn_fwd(const float* qkv, int B, int T, float drop_p, uint64_t seed
                      uint32_t site, float* out, float* lse, void* stream);
 int afl_har_attn_bwd(const float* qkv, const float* out, const float* dout, const float* lse, int B, int T, float drop_p,
                      uint64_t seed, uint32_t client, uint32_t step, uint32_t site, float* dqkv, void* stream);
+/* attn_fwd on the tensor cores (csrc/attn_tcgen05.cu): same contract and same dropout stream as afl_har_attn_fwd, scores
+ * and probabilities as TF32 tcgen05 operands; afl_har_attn_tc_supported(T) says whether K/V of one (sample, head pair)
+ * fit in shared memory (T <= 568 with the 227 KB limit). */
+int afl_har_attn_tc_supported(int T);
+int afl_har_attn_fwd_tc(const float* qkv, int B, int T, float drop_p, uint64_t seed, uint32_t client, uint32_t step,
+                        uint32_t site, float* out, float* lse, void* stream);
 int afl_har_pool_fwd(const float* h, int B, int T, float* pooled, void* stream);
 int afl_har_head(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                  const int64_t* labels, int B, int n_cls, float drop_p, uint64_t seed, uint32_t client, uint32_t step,

@@ -52,6 +52,31 @@ def test_attention_kernels_match_sdpa():
         assert _rel(got, gr) < 2e-4, i
 
 
+@pytest.mark.parametrize("T,B", [(561, 3), (200, 2), (128, 1), (37, 2)])
+def test_attention_tensor_core_forward(T, B):
+    """tcgen05 attention forward against SDPA (no dropout) and against the FFMA kernel with the same dropout stream."""
+    from attackfl_b200.ops.native import cuda_lib, ptr, check
+    import ctypes
+    lib = cuda_lib()
+    assert lib.afl_har_attn_tc_supported(T)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    qkv = torch.randn(B * T, 192, device="cuda")
+
+    def run(fn, p):
+        o = torch.full((B * T, 64), float("nan"), device="cuda"); l = torch.full((B * 4 * T,), float("nan"), device="cuda")
+        check(lib, fn(ptr(qkv), B, T, ctypes.c_float(p), ctypes.c_uint64(9), 2, 3, 4, ptr(o), ptr(l), st))
+        return o, l
+    o_tc, l_tc = run(lib.afl_har_attn_fwd_tc, 0.0)
+    q, k, v = (qkv[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2) for i in range(3))
+    ref = torch.nn.functional.scaled_dot_product_attention(q, k, v)
+    assert _rel(o_tc.reshape(B, T, 4, 16).transpose(1, 2), ref) < 4e-3
+    o_ff, l_ff = run(lib.afl_har_attn_fwd, 0.0)
+    assert (l_tc - l_ff).abs().max().item() < 2e-2
+    o_tc, _ = run(lib.afl_har_attn_fwd_tc, 0.2)
+    o_ff, _ = run(lib.afl_har_attn_fwd, 0.2)
+    assert _rel(o_tc, o_ff) < 6e-3
+
+
 def test_attention_dropout_is_consistent():
     """With dropout the three kernels must agree on the mask: finite differences of the forward output against the
     analytic gradients, and the kept fraction."""
