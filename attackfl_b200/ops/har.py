@@ -42,11 +42,18 @@ class HarNativeTrainer:
         self.lib = cuda_lib()
         self.T, self.n_cls, self.max_batch = seq_len, n_classes, max_batch
         # attention forward: tcgen05 kernel when K/V of a head pair fit in shared memory, else the FFMA kernel
-        self.attn_tc = bool(self.lib.afl_har_attn_tc_supported(c_i(seq_len))) and os.environ.get("ATTACKFL_HAR_ATTN", "tc") != "ffma"
+        mode = os.environ.get("ATTACKFL_HAR_ATTN", "tc")            # tc | tc-fwd (FFMA backward) | ffma
+        self.attn_tc = bool(self.lib.afl_har_attn_tc_supported(c_i(seq_len))) and mode != "ffma"
+        self.attn_bwd_tc = mode == "tc"
         m = max_batch * seq_len
         z = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.device)          # noqa: E731
         self.h0 = z(m, D_MODEL)
-        self.layers = [{"qkv": z(m, 3 * D_MODEL), "att": z(m, D_MODEL), "lse": z(max_batch * N_HEADS * seq_len),
+        self.Tp = int(self.lib.afl_har_lse_stride(c_i(seq_len)))
+        self.mask_words = int(self.lib.afl_har_attn_mask_words(c_i(seq_len)))
+        zz = lambda n, dt=torch.float32: torch.zeros(n, dtype=dt, device=self.device)       # noqa: E731
+        self.delta = zz(max_batch * N_HEADS * self.Tp)
+        self.layers = [{"qkv": z(m, 3 * D_MODEL), "att": z(m, D_MODEL), "lse": zz(max_batch * N_HEADS * self.Tp),
+                        "mask": zz(max_batch * N_HEADS * self.mask_words * self.Tp, torch.int32) if self.attn_tc else None,
                         "sa": z(m, D_MODEL), "h1": z(m, D_MODEL), "xhat1": z(m, D_MODEL), "rstd1": z(m),
                         "f1": z(m, FF), "f2": z(m, D_MODEL), "h2": z(m, D_MODEL), "xhat2": z(m, D_MODEL), "rstd2": z(m)}
                        for _ in range(N_LAYERS)]
@@ -79,9 +86,13 @@ class HarNativeTrainer:
             pre = f"transformer.layers.{l}."
             rng = (client, step)
             tc.linear_fwd(h[:M], w[pre + "self_attn.in_proj_weight"], w[pre + "self_attn.in_proj_bias"], out=a["qkv"][:M])
-            attn = lib.afl_har_attn_fwd_tc if self.attn_tc else lib.afl_har_attn_fwd
-            self._ck(attn(ptr(a["qkv"]), c_i(B), c_i(T), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
-                          c_u32(16 * l + SITE_ATTN), ptr(a["att"]), ptr(a["lse"]), st), "afl_har_attn_fwd")
+            if self.attn_tc:
+                self._ck(lib.afl_har_attn_fwd_tc(ptr(a["qkv"]), c_i(B), c_i(T), c_f(p), c_u64(seed), c_u32(client),
+                                                 c_u32(step), c_u32(16 * l + SITE_ATTN), ptr(a["att"]), ptr(a["lse"]),
+                                                 ptr(a["mask"]) if train else None, st), "afl_har_attn_fwd_tc")
+            else:
+                self._ck(lib.afl_har_attn_fwd(ptr(a["qkv"]), c_i(B), c_i(T), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
+                                              c_u32(16 * l + SITE_ATTN), ptr(a["att"]), ptr(a["lse"]), st), "afl_har_attn_fwd")
             tc.linear_fwd(a["att"][:M], w[pre + "self_attn.out_proj.weight"], w[pre + "self_attn.out_proj.bias"],
                           out=a["sa"][:M])
             self._ck(lib.afl_har_add_ln_fwd(ptr(h), ptr(a["sa"]), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
@@ -155,9 +166,13 @@ class HarNativeTrainer:
                                         ptr(g[pre + "norm1.bias"]), st), "afl_har_ln_bwd")
             tc.linear_dw(dD[:M], a["att"][:M], dw=g[pre + "self_attn.out_proj.weight"], db=g[pre + "self_attn.out_proj.bias"])
             tc.linear_dx(dD[:M], w[pre + "self_attn.out_proj.weight"], out=dB[:M])
-            self._ck(lib.afl_har_attn_bwd(ptr(a["qkv"]), ptr(a["att"]), ptr(dB), ptr(a["lse"]), c_i(B), c_i(T), c_f(p),
-                                          c_u64(seed), c_u32(client), c_u32(step), c_u32(16 * l + SITE_ATTN), ptr(self.d192),
-                                          st), "afl_har_attn_bwd")
+            if self.attn_tc and self.attn_bwd_tc:
+                self._ck(lib.afl_har_attn_bwd_tc(ptr(a["qkv"]), ptr(a["att"]), ptr(dB), ptr(a["lse"]), ptr(a["mask"]), c_i(B),
+                                                 c_i(T), c_f(p), ptr(self.delta), ptr(self.d192), st), "afl_har_attn_bwd_tc")
+            else:
+                self._ck(lib.afl_har_attn_bwd(ptr(a["qkv"]), ptr(a["att"]), ptr(dB), ptr(a["lse"]), c_i(B), c_i(T), c_f(p),
+                                              c_u64(seed), c_u32(client), c_u32(step), c_u32(16 * l + SITE_ATTN),
+                                              ptr(self.d192), st), "afl_har_attn_bwd")
             tc.linear_dw(self.d192[:M], h_in[:M], dw=g[pre + "self_attn.in_proj_weight"],
                          db=g[pre + "self_attn.in_proj_bias"])
             tc.linear_dx(self.d192[:M], w[pre + "self_attn.in_proj_weight"], out=dC[:M], accumulate=True)

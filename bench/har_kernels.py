@@ -34,15 +34,18 @@ def main():
     lib = cuda_lib()
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     z = lambda *s: torch.randn(*s, device="cuda")                  # noqa: E731
-    qkv, att, dout, lse, dqkv = z(M, 192), z(M, 64), z(M, 64), torch.empty(B * 4 * T, device="cuda"), z(M, 192)
+    qkv, att, dout, lse, dqkv = z(M, 192), z(M, 64), z(M, 64), torch.zeros(B * 4 * lib.afl_har_lse_stride(T), device="cuda"), z(M, 192)
+    mask = torch.zeros(B * 4 * lib.afl_har_attn_mask_words(T) * lib.afl_har_lse_stride(T), dtype=torch.int32, device="cuda")
+    delta = torch.zeros(B * 4 * lib.afl_har_lse_stride(T), device="cuda")
     x64, r64, y64, xh, rs = z(M, 64), z(M, 64), z(M, 64), z(M, 64), torch.rand(M, device="cuda")
     ga, be, dg, db = z(64), z(64), torch.zeros(64, device="cuda"), torch.zeros(64, device="cuda")
     out = {"batch": B}
     for p in (0.0, 0.1):
         tag = f"p{p}"
         out[f"attn_fwd_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_attn_fwd(ptr(qkv), B, T, c_f(p), c_u64(1), 0, 1, 0, ptr(att), ptr(lse), st)))
-        out[f"attn_fwd_tc_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_attn_fwd_tc(ptr(qkv), B, T, c_f(p), c_u64(1), 0, 1, 0, ptr(att), ptr(lse), st)))
+        out[f"attn_fwd_tc_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_attn_fwd_tc(ptr(qkv), B, T, c_f(p), c_u64(1), 0, 1, 0, ptr(att), ptr(lse), ptr(mask), st)))
         out[f"attn_bwd_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_attn_bwd(ptr(qkv), ptr(att), ptr(dout), ptr(lse), B, T, c_f(p), c_u64(1), 0, 1, 0, ptr(dqkv), st)))
+        out[f"attn_bwd_tc_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_attn_bwd_tc(ptr(qkv), ptr(att), ptr(dout), ptr(lse), ptr(mask), B, T, c_f(p), ptr(delta), ptr(dqkv), st)))
         out[f"add_ln_fwd_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_add_ln_fwd(ptr(x64), ptr(r64), c_f(p), c_u64(1), 0, 1, 8, ptr(ga), ptr(be), c_i64(M), ptr(y64), ptr(xh), ptr(rs), st)))
         out[f"ln_bwd_{tag}_us"] = timeit(lambda: check(lib, lib.afl_har_ln_bwd(ptr(x64), None, T, c_f(1.0), ptr(xh), ptr(rs), ptr(ga), c_f(p), c_u64(1), 0, 1, 8, c_i64(M), ptr(y64), ptr(r64), ptr(dg), ptr(db), st)))
     xin, cw, cb, pe = z(B, T), z(64, 1, 3), z(64), z(1, 600, 64)

@@ -42,10 +42,39 @@ struct AttnParams {
   int tail_rows;       // rows of the last key block actually loaded (multiple of 8)
   Rng rng;
   float* out;          // [B*T][64]
-  float* lse;          // [B][4][T], base-2 log-sum-exp of the scaled scores
+  float* lse;          // [B][4][lse_stride(T)], base-2 log-sum-exp of the scaled scores
+  uint32_t* mask;      // [B][4][4*n_kb][lse_stride(T)] keep bits (NULL: not wanted), see attn_bwd_tcgen05.cu
 };
 
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// v[16] (raw scores of keys kc .. kc+15) -> probabilities exp2(s c - m) with dropped entries zeroed (the kept ones are
+// scaled by 1/(1-p) once, on the output row); returns the sum of the un-dropped probabilities.
+template <bool MASK, bool DROP>
+__device__ __forceinline__ float probs16(float* v, float c, float mx, int kc, int T, const Rng& hr, uint32_t row, uint32_t thr,
+                                         uint32_t& keep_bits) {
+  float sum = 0.f;
+  keep_bits = 0xFFFFu;
+#pragma unroll
+  for (int g8 = 0; g8 < 2; ++g8) {
+    AflU4 rw; rw.x = rw.y = rw.z = rw.w = 0u;
+    if (DROP) rw = attn_call(hr, row, (uint32_t)(kc + 8 * g8));
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float p = ex2_approx(fmaf(v[8 * g8 + j], c, -mx));
+      if (MASK && kc + 8 * g8 + j >= T) p = 0.f;
+      sum += p;
+      if (DROP && attn_bits(rw.x, rw.y, rw.z, rw.w, (uint32_t)j) < thr) { p = 0.f; keep_bits &= ~(1u << (8 * g8 + j)); }
+      v[8 * g8 + j] = p;
+    }
+  }
+  return sum;
+}
 
 __global__ void __launch_bounds__(kThreads, 1)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_kt,
@@ -166,8 +195,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
       for (int c0 = 0; c0 < 64; c0 += 16) {
         float v[16];
         tmem_ld16(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64 + c0), v);
+        if (key0 + 64 <= P.T) {                 // every key of this half is real: no masking
 #pragma unroll
-        for (int j = 0; j < 16; ++j) if (key0 + c0 + j < P.T) mx = fmaxf(mx, v[j]);
+          for (int j = 0; j < 16; ++j) mx = fmaxf(mx, v[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) if (key0 + c0 + j < P.T) mx = fmaxf(mx, v[j]);
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -183,26 +217,31 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
       const int n = n_kb + kb, buf = n & 1;
       mbar_wait(s_full + buf, ((uint32_t)n >> 1) & 1u);
       tc_fence_after();
-      mbar_wait(p_empty, ((uint32_t)kb & 1u) ^ 1u);       // previous block's P V has consumed the P buffer
       const int key0 = kb * kBlk + half * 64;
+      const bool full = key0 + 64 <= P.T;
+      uint32_t keep_lo = 0;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 16) {
         float v[16];
         tmem_ld16(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64 + c0), v);
-#pragma unroll
-        for (int g8 = 0; g8 < 2; ++g8) {
-          AflU4 rw; rw.x = rw.y = rw.z = rw.w = 0u;
-          if (P.rng.p > 0.f) rw = attn_call(hr, (uint32_t)(row0 + qi), (uint32_t)(key0 + c0 + 8 * g8));
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int key = key0 + c0 + 8 * g8 + j;
-            float p = key < P.T ? exp2f(fmaf(v[8 * g8 + j], c, -mx)) : 0.f;
-            l += p;
-            if (P.rng.p > 0.f) p = attn_bits(rw.x, rw.y, rw.z, rw.w, (uint32_t)j) >= thr ? p * inv_keep : 0.f;
-            v[8 * g8 + j] = p;
-          }
+        const int kc = key0 + c0;
+        uint32_t kb16;
+        if (full) {
+          if (P.rng.p > 0.f) l += probs16<false, true>(v, c, mx, kc, P.T, hr, (uint32_t)(row0 + qi), thr, kb16);
+          else l += probs16<false, false>(v, c, mx, kc, P.T, hr, (uint32_t)(row0 + qi), thr, kb16);
+        } else {
+          if (P.rng.p > 0.f) l += probs16<true, true>(v, c, mx, kc, P.T, hr, (uint32_t)(row0 + qi), thr, kb16);
+          else l += probs16<true, false>(v, c, mx, kc, P.T, hr, (uint32_t)(row0 + qi), thr, kb16);
+        }
+        // keep-mask words for the backward kernels: bit (key & 31) of word [b][h][key >> 5][query]
+        if (c0 & 16) {
+          if (P.mask && qi < P.T)
+            P.mask[(((size_t)b * kNH + h) * (size_t)(n_kb * 4) + (size_t)(kc >> 5)) * lse_stride(P.T) + qi] = keep_lo | (kb16 << 16);
+        } else {
+          keep_lo = kb16;
         }
         // keys (half*64 + c0 .. +15) of this block: k-block (32 keys) index and 16-byte chunk inside the 128-byte row
+        if (c0 == 0) mbar_wait(p_empty, ((uint32_t)kb & 1u) ^ 1u);   // previous block's P V has consumed the P buffer
         const int kcol = half * 64 + c0;
         uint8_t* rowp = p_ptr + (size_t)(kcol >> 5) * kBlkBytes + (size_t)r * 128;
 #pragma unroll
@@ -226,13 +265,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
       float o[16];
       tmem_ld16(lane_addr + kOCol + (uint32_t)(h & 1) * 16u, o);
       if (qi < P.T) {
-        const float il = 1.0f / l;
+        const float il = inv_keep / l;
         float4* dst = reinterpret_cast<float4*>(P.out + (size_t)(row0 + qi) * kD + h * kDH);
 #pragma unroll
         for (int g = 0; g < 4; ++g) dst[g] = make_float4(o[4 * g] * il, o[4 * g + 1] * il, o[4 * g + 2] * il, o[4 * g + 3] * il);
       }
     } else if (qi < P.T) {
-      P.lse[((size_t)b * kNH + h) * P.T + qi] = mx + log2f(l);
+      P.lse[((size_t)b * kNH + h) * lse_stride(P.T) + qi] = mx + log2f(l);
     }
   }
   tc_fence_before();
@@ -255,7 +294,7 @@ int afl_har_attn_tc_supported(int T) {
 }
 
 int afl_har_attn_fwd_tc(const float* qkv, int B, int T, float drop_p, uint64_t seed, uint32_t client, uint32_t step,
-                        uint32_t site, float* out, float* lse, void* stream) {
+                        uint32_t site, float* out, float* lse, uint32_t* keep_mask, void* stream) {
   AFL_CHECK_ARG(B >= 1 && afl_har_attn_tc_supported(T), "afl_har_attn_fwd_tc: T too large for the shared-memory resident K/V");
   AFL_CHECK_ARG((uintptr_t)qkv % 16 == 0, "afl_har_attn_fwd_tc: qkv must be 16-byte aligned");
   const int n_kb = (T + kBlk - 1) / kBlk;
@@ -268,7 +307,7 @@ int afl_har_attn_fwd_tc(const float* qkv, int B, int T, float drop_p, uint64_t s
   if (!rc) rc = make_tmap_f32(&mvt, qkv, 3 * kD, rows, 3 * kD, tail, true);
   if (rc) return rc;
   AttnParams P{};
-  P.T = T; P.n_kb = n_kb; P.tail_rows = tail; P.out = out; P.lse = lse;
+  P.T = T; P.n_kb = n_kb; P.tail_rows = tail; P.out = out; P.lse = lse; P.mask = drop_p > 0.f ? keep_mask : nullptr;
   P.rng.s0 = (uint32_t)seed; P.rng.s1 = (uint32_t)(seed >> 32); P.rng.client = client; P.rng.step = step; P.rng.site = site;
   P.rng.p = drop_p;
   const size_t kv = (size_t)(n_kb - 1) * kBlkBytes + (size_t)tail * 128;

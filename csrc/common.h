@@ -44,12 +44,15 @@ AFL_HD uint32_t afl_mulhi(uint32_t a, uint32_t b) {
 #endif
 }
 
-AFL_HD AflU4 afl_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+// Philox4x32-R (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3"): R = 10 is the standard generator, R = 7 the
+// smallest round count that the paper reports as passing BigCrush (used only for the attention-weight dropout bits).
+template <int R>
+AFL_HD AflU4 afl_philox_r(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int r = 0; r < 10; ++r) {
+  for (int r = 0; r < R; ++r) {
     uint32_t hi0 = afl_mulhi(M0, c0), lo0 = M0 * c0;
     uint32_t hi1 = afl_mulhi(M1, c2), lo1 = M1 * c2;
     uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
@@ -58,6 +61,10 @@ AFL_HD AflU4 afl_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint
   }
   AflU4 o; o.x = c0; o.y = c1; o.z = c2; o.w = c3;
   return o;
+}
+
+AFL_HD AflU4 afl_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+  return afl_philox_r<10>(c0, c1, c2, c3, k0, k1);
 }
 
 // Uniform in [0,1) for element `elem` of stream (client, step, sample, rng_id).

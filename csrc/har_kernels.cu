@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(kQB) attn_fwd_kernel(const float* __restrict__
 #pragma unroll
     for (int d4 = 0; d4 < 4; ++d4)
       dst[d4] = make_float4(o[4 * d4] * il, o[4 * d4 + 1] * il, o[4 * d4 + 2] * il, o[4 * d4 + 3] * il);
-    lse[((int64_t)b * NH + h) * T + qi] = m + log2f(l);
+    lse[((int64_t)b * NH + h) * lse_stride(T) + qi] = m + log2f(l);
   }
 }
 
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(kQB) attn_bwd_dq_kernel(const float* __restric
       go[4 * d4] = gv.x; go[4 * d4 + 1] = gv.y; go[4 * d4 + 2] = gv.z; go[4 * d4 + 3] = gv.w;
       delta += ov.x * gv.x + ov.y * gv.y + ov.z * gv.z + ov.w * gv.w;
     }
-    L = lse[((int64_t)b * NH + h) * T + qi];
+    L = lse[((int64_t)b * NH + h) * lse_stride(T) + qi];
   }
   const float inv_keep = rng.p > 0.f ? 1.0f / (1.0f - rng.p) : 1.f;
   Rng hr = rng; hr.site = rng.site + (uint32_t)h;
@@ -370,7 +370,7 @@ __global__ void __launch_bounds__(kQB) attn_bwd_dkv_kernel(const float* __restri
           const float4 ov = osrc[d4], gv = gsrc[d4];
           de += ov.x * gv.x + ov.y * gv.y + ov.z * gv.z + ov.w * gv.w;
         }
-        Lv = lse[((int64_t)b * NH + h) * T + q0 + j];
+        Lv = lse[((int64_t)b * NH + h) * lse_stride(T) + q0 + j];
       }
       dsm[j] = de; lsm[j] = Lv;
     }
@@ -556,6 +556,8 @@ int afl_har_attn_bwd(const float* qkv, const float* out, const float* dout, cons
   afl_rt::count_launch(2);
   return afl_rt::check_last("afl_har_attn_bwd");
 }
+
+int afl_har_lse_stride(int T) { return lse_stride(T); }
 
 int afl_har_pool_fwd(const float* h, int B, int T, float* pooled, void* stream) {
   pool_fwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(h, T, pooled);

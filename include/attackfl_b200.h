@@ -124,7 +124,16 @@ int afl_har_attn_bwd(const float* qkv, const float* out, const float* dout, cons
  * fit in shared memory (T <= 568 with the 227 KB limit). */
 int afl_har_attn_tc_supported(int T);
 int afl_har_attn_fwd_tc(const float* qkv, int B, int T, float drop_p, uint64_t seed, uint32_t client, uint32_t step,
-                        uint32_t site, float* out, float* lse, void* stream);
+                        uint32_t site, float* out, float* lse, uint32_t* keep_mask, void* stream);
+/* lse (and the backward's delta) rows are lse_stride(T) = T rounded up to 64 floats long: [B][4][lse_stride(T)].
+ * keep_mask (NULL = not wanted): [B][4][afl_har_attn_mask_words(T)][lse_stride(T)] uint32, bit (key & 31) of word
+ * [key >> 5][query] = that attention weight survived the dropout; consumed by afl_har_attn_bwd_tc. */
+int afl_har_lse_stride(int T);
+int afl_har_attn_mask_words(int T);
+/* attention backward on the tensor cores (csrc/attn_bwd_tcgen05.cu): dqkv [B*T,192] from dout; needs lse and
+ * (drop_p > 0) keep_mask written by afl_har_attn_fwd_tc; delta: scratch [B][4][lse_stride(T)]. */
+int afl_har_attn_bwd_tc(const float* qkv, const float* out, const float* dout, const float* lse, const uint32_t* keep_mask,
+                        int B, int T, float drop_p, float* delta, float* dqkv, void* stream);
 int afl_har_pool_fwd(const float* h, int B, int T, float* pooled, void* stream);
 int afl_har_head(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                  const int64_t* labels, int B, int n_cls, float drop_p, uint64_t seed, uint32_t client, uint32_t step,

@@ -35,7 +35,7 @@ def test_attention_kernels_match_sdpa():
     B, T = 3, 561
     lib = cuda_lib()
     qkv = torch.randn(B * T, 192, device="cuda")
-    out = torch.empty(B * T, 64, device="cuda"); lse = torch.empty(B * 4 * T, device="cuda")
+    out = torch.empty(B * T, 64, device="cuda"); lse = torch.zeros(B * 4 * lib.afl_har_lse_stride(T), device="cuda")
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     check(lib, lib.afl_har_attn_fwd(ptr(qkv), B, T, ctypes.c_float(0.0), ctypes.c_uint64(0), 0, 0, 0, ptr(out), ptr(lse), st))
     q, k, v = (qkv[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2) for i in range(3))
@@ -63,8 +63,12 @@ def test_attention_tensor_core_forward(T, B):
     qkv = torch.randn(B * T, 192, device="cuda")
 
     def run(fn, p):
-        o = torch.full((B * T, 64), float("nan"), device="cuda"); l = torch.full((B * 4 * T,), float("nan"), device="cuda")
-        check(lib, fn(ptr(qkv), B, T, ctypes.c_float(p), ctypes.c_uint64(9), 2, 3, 4, ptr(o), ptr(l), st))
+        tp = lib.afl_har_lse_stride(T)
+        o = torch.full((B * T, 64), float("nan"), device="cuda"); l = torch.zeros(B * 4 * tp, device="cuda")
+        if fn is lib.afl_har_attn_fwd_tc:
+            check(lib, fn(ptr(qkv), B, T, ctypes.c_float(p), ctypes.c_uint64(9), 2, 3, 4, ptr(o), ptr(l), None, st))
+        else:
+            check(lib, fn(ptr(qkv), B, T, ctypes.c_float(p), ctypes.c_uint64(9), 2, 3, 4, ptr(o), ptr(l), st))
         return o, l
     o_tc, l_tc = run(lib.afl_har_attn_fwd_tc, 0.0)
     q, k, v = (qkv[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2) for i in range(3))
@@ -75,6 +79,37 @@ def test_attention_tensor_core_forward(T, B):
     o_tc, _ = run(lib.afl_har_attn_fwd_tc, 0.2)
     o_ff, _ = run(lib.afl_har_attn_fwd, 0.2)
     assert _rel(o_tc, o_ff) < 6e-3
+
+
+@pytest.mark.parametrize("T,B,p", [(561, 2, 0.0), (561, 2, 0.2), (200, 1, 0.1), (64, 2, 0.0), (37, 1, 0.3)])
+def test_attention_tensor_core_backward(T, B, p):
+    """tcgen05 attention backward (dq + dkv kernels, keep bits from the forward's mask words) against the FFMA backward
+    kernels, which regenerate the same dropout stream; p = 0 is also checked against SDPA autograd."""
+    from attackfl_b200.ops.native import cuda_lib, ptr, check
+    import ctypes
+    lib = cuda_lib()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    tp, mw = lib.afl_har_lse_stride(T), lib.afl_har_attn_mask_words(T)
+    qkv = torch.randn(B * T, 192, device="cuda")
+    dout = torch.randn(B * T, 64, device="cuda")
+    out = torch.empty(B * T, 64, device="cuda"); lse = torch.zeros(B * 4 * tp, device="cuda")
+    mask = torch.zeros(B * 4 * mw * tp, dtype=torch.int32, device="cuda")
+    delta = torch.zeros(B * 4 * tp, device="cuda")
+    cp = ctypes.c_float(p)
+    check(lib, lib.afl_har_attn_fwd_tc(ptr(qkv), B, T, cp, ctypes.c_uint64(9), 2, 3, 4, ptr(out), ptr(lse), ptr(mask), st))
+    got = torch.full((B * T, 192), float("nan"), device="cuda")
+    check(lib, lib.afl_har_attn_bwd_tc(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(mask), B, T, cp, ptr(delta), ptr(got), st))
+    want = torch.zeros(B * T, 192, device="cuda")
+    check(lib, lib.afl_har_attn_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), B, T, cp, ctypes.c_uint64(9), 2, 3, 4, ptr(want), st))
+    torch.cuda.synchronize()
+    for i, name in enumerate("qkv"):
+        assert _rel(got[:, i * 64:(i + 1) * 64], want[:, i * 64:(i + 1) * 64]) < 1.5e-2, name   # TF32 dS, P operands
+    if p == 0.0:
+        q, k, v = (qkv[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2).detach().clone().requires_grad_(True)
+                   for i in range(3))
+        torch.nn.functional.scaled_dot_product_attention(q, k, v).backward(dout.reshape(B, T, 4, 16).transpose(1, 2))
+        for i, t in enumerate((q, k, v)):
+            assert _rel(got[:, i * 64:(i + 1) * 64].reshape(B, T, 4, 16).transpose(1, 2), t.grad) < 1.5e-2, i
 
 
 def test_attention_dropout_is_consistent():
@@ -89,7 +124,7 @@ def test_attention_dropout_is_consistent():
     dout = torch.randn(B * T, 64, device="cuda")
 
     def fwd(t):
-        o = torch.empty(B * T, 64, device="cuda"); l = torch.empty(B * 4 * T, device="cuda")
+        o = torch.empty(B * T, 64, device="cuda"); l = torch.zeros(B * 4 * lib.afl_har_lse_stride(T), device="cuda")
         check(lib, lib.afl_har_attn_fwd(ptr(t), B, T, ctypes.c_float(p), ctypes.c_uint64(5), 1, 2, 3, ptr(o), ptr(l), st))
         return o, l
     out, lse = fwd(qkv)
