@@ -52,7 +52,8 @@ struct RowGemmParams {
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
-row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w, RowGemmParams P) {
+row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                const __grid_constant__ CUtensorMap tmap_o, RowGemmParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* aligned = smem_raw + (base - smem_u32(smem_raw));
@@ -60,12 +61,15 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const uint32_t w_bytes = w_box_bytes * (uint32_t)P.w_kblocks;
   const uint32_t w_base = base;
   const uint32_t a_base = base + w_bytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(aligned + w_bytes + (size_t)P.stages * kStageBytes);
+  const uint32_t o_base = a_base + (uint32_t)P.stages * kStageBytes;      // 2 output staging tiles [128 rows][32 cols]
+  uint8_t* o_ptr = aligned + (o_base - base);
+  uint64_t* full = reinterpret_cast<uint64_t*>(o_ptr + 2 * kStageBytes);
   uint64_t* empty = full + P.stages;
   uint64_t* w_full = empty + P.stages;
   uint64_t* acc_full = w_full + 1;             // [2]
   uint64_t* acc_empty = acc_full + 2;          // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* bias_s = reinterpret_cast<float*>(tmem_slot + 2);               // [n_out]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t n_tiles = (P.M + 127) / 128;
@@ -133,24 +137,35 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       }
     }
   } else {
-    // ===== epilogue warps 2..5: TMEM -> registers -> fused elementwise -> global =====
+    // ===== epilogue warps 2..5: TMEM -> registers -> fused elementwise -> swizzled staging tile -> TMA store =====
+    // The output leaves through 16 KB staging tiles ([128 rows][32 columns], SWIZZLE_128B) and cp.async.bulk.tensor
+    // stores (reduce-add when accumulating), so global writes are full 128-byte lines and rows >= M are clipped by TMA.
     const int q = warp & 3;
-    int t = 0;
+    const int et = threadIdx.x - 64;                       // 0..127
+    const int r = q * 32 + lane;                           // row of the tile = TMEM lane
+    if (P.mode == 0 && P.bias)
+      for (int i = et; i < P.n_out; i += 128) bias_s[i] = P.bias[i];
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    int t = 0, sc = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t) {
       const int buf = t & 1;
       mbar_wait(acc_full + buf, ((uint32_t)t >> 1) & 1u);
       tc_fence_after();
-      const int64_t row = tile * 128 + q * 32 + lane;
+      const int64_t row = tile * 128 + r;
       const bool live = row < P.M;
-      float* orow = P.out + row * P.n_out;
-      for (int c0 = 0; c0 < P.n_out; c0 += 16) {
-        float v[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols + (uint32_t)c0, v);
-        if (live) {
+      for (int c0 = 0; c0 < P.n_out; c0 += 32, ++sc) {
+        uint8_t* stage = o_ptr + (size_t)(sc & 1) * kStageBytes;
+        if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that used this tile is done reading
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+        for (int hc = 0; hc < 2; ++hc) {
+          const int cc = c0 + 16 * hc;
+          float v[16];
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols + (uint32_t)cc, v);
           if (P.mode == 0) {
             if (P.bias) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] += __ldg(P.bias + c0 + j);
+              for (int j = 0; j < 16; ++j) v[j] += bias_s[cc + j];
             }
             if (P.relu) {
 #pragma unroll
@@ -160,16 +175,16 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               const float inv = 1.0f / (1.0f - P.drop_p);
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
-                const AflU4 r = afl_philox((uint32_t)(c0 + 4 * g) >> 2, (P.rng_id & 0xFFFFu) | (P.rng_client << 16),
-                                           P.rng_step, (uint32_t)row, P.seed_lo, P.seed_hi);
-                const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+                const AflU4 rr = afl_philox((uint32_t)(cc + 4 * g) >> 2, (P.rng_id & 0xFFFFu) | (P.rng_client << 16),
+                                            P.rng_step, (uint32_t)row, P.seed_lo, P.seed_hi);
+                const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                   v[4 * g + j] = ((float)(w[j] >> 8) * (1.0f / 16777216.0f) >= P.drop_p) ? v[4 * g + j] * inv : 0.f;
               }
             }
-          } else if (P.mask_src) {
-            const float4* m4 = reinterpret_cast<const float4*>(P.mask_src + row * P.n_out + c0);
+          } else if (P.mask_src && live) {
+            const float4* m4 = reinterpret_cast<const float4*>(P.mask_src + row * P.n_out + cc);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               const float4 m = __ldg(m4 + g);
@@ -179,19 +194,29 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               v[4 * g + 3] = m.w > 0.f ? v[4 * g + 3] * P.mask_scale : 0.f;
             }
           }
-          float4* o4 = reinterpret_cast<float4*>(orow + c0);
+          uint8_t* rowp = stage + (size_t)r * 128;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float4 o = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
-            if (P.accumulate) { const float4 p = o4[g]; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
-            o4[g] = o;
-          }
+          for (int g = 0; g < 4; ++g)
+            *reinterpret_cast<float4*>(rowp + (((4 * hc + g) ^ (r & 7)) << 4)) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          const uint32_t src = o_base + (uint32_t)(sc & 1) * kStageBytes;
+          if (P.accumulate)
+            asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+                         ::"l"(reinterpret_cast<uint64_t>(&tmap_o)), "r"(c0), "r"((int)(tile * 128)), "r"(src) : "memory");
+          else
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                         ::"l"(reinterpret_cast<uint64_t>(&tmap_o)), "r"(c0), "r"((int)(tile * 128)), "r"(src) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty + buf);
     }
+    if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -207,7 +232,8 @@ struct DwParams {
   int N, K;              // dW is [N][K]
   int stages;
   int64_t n_chunks;
-  float* partials;       // [gridDim.x][N][K]
+  int want_db;           // also sum the columns of dY (bias gradient) from the staged tiles
+  float* partials;       // [gridDim.x][N*K + N]: dW partial, then db partial
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -233,7 +259,8 @@ dw_gemm_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constan
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_dy)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
-    for (int s = 0; s < P.stages; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    // a stage is free again when its MMAs have retired and (bias gradient wanted) the four epilogue warps have read it
+    for (int s = 0; s < P.stages; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, P.want_db ? 5 : 1); }
     mbar_init(acc_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -284,7 +311,31 @@ dw_gemm_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constan
     }
   } else {
     const int q = warp & 3;
-    float* out = P.partials + (size_t)blockIdx.x * (size_t)P.N * P.K;
+    float* out = P.partials + (size_t)blockIdx.x * ((size_t)P.N * P.K + P.N);
+    if (P.want_db) {
+      // bias gradient: column sums of the dY boxes while they sit in shared memory (MN-major 128B_ATOM_32B image:
+      // token row r at r*128 bytes, 32-byte chunk index XOR-ed with r & 3); thread e owns columns e and e + 128.
+      const int e = (warp - 2) * 32 + lane;
+      float acc0 = 0.f, acc1 = 0.f;
+      const uint32_t off0 = (uint32_t)(e >> 5) * kBoxBytes + (uint32_t)(e & 7) * 4u;
+      const uint32_t c32 = (uint32_t)(e & 31) >> 3;
+      for (int i = 0; i < nch; ++i) {
+        const int st = i % P.stages;
+        mbar_wait(full + st, (uint32_t)(i / P.stages) & 1u);
+        const uint8_t* sp = aligned + (size_t)st * stage_bytes;
+#pragma unroll 8
+        for (int r = 0; r < kChunkRows; ++r) {
+          const uint32_t o = off0 + (uint32_t)r * 128u + ((c32 ^ (uint32_t)(r & 3)) << 5);
+          if (e < P.N) acc0 += *reinterpret_cast<const float*>(sp + o);
+          if (e + 128 < P.N) acc1 += *reinterpret_cast<const float*>(sp + o + 4 * kBoxBytes);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + st);
+      }
+      float* ob = out + (size_t)P.N * P.K;
+      if (e < P.N) ob[e] = acc0;
+      if (e + 128 < P.N) ob[e + 128] = acc1;
+    }
     if (nch > 0) {
       mbar_wait(acc_full, 0);
       tc_fence_after();
@@ -312,32 +363,17 @@ dw_gemm_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
-// out[i] (+)= sum_p partials[p][i]   (fixed order: deterministic)
-__global__ void reduce_partials_kernel(const float* __restrict__ partials, int n_parts, int64_t n, float* __restrict__ out,
-                                       int accumulate) {
+// dW[i] (+)= sum_p partials[p][i] for i < n_w, db[i - n_w] (+)= ... for the n_b entries after them (fixed order:
+// deterministic)
+__global__ void reduce_partials_kernel(const float* __restrict__ partials, int n_parts, int64_t n_w, int n_b,
+                                       float* __restrict__ dw, float* __restrict__ db, int accumulate) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  const int64_t stride = n_w + n_b;
+  if (i >= stride || (i >= n_w && db == nullptr)) return;
   float acc = 0.f;
-  for (int p = 0; p < n_parts; ++p) acc += partials[(size_t)p * n + i];
-  out[i] = accumulate ? out[i] + acc : acc;
-}
-
-// db[n] (+)= sum_rows dY[row][n]: block (n-thread, row-slab) partial sums, then atomics on the N outputs
-__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ dy, int64_t M, int N, float* __restrict__ out) {
-  const int n = threadIdx.x % N, sub = threadIdx.x / N, nsub = 256 / N;
-  const int64_t rows_per = (M + gridDim.x - 1) / gridDim.x;
-  const int64_t r0 = (int64_t)blockIdx.x * rows_per, r1 = min(M, r0 + rows_per);
-  float acc = 0.f;
-  if (sub < nsub)
-    for (int64_t r = r0 + sub; r < r1; r += nsub) acc += dy[r * N + n];
-  __shared__ float part[256];
-  part[threadIdx.x] = acc;
-  __syncthreads();
-  if (threadIdx.x < N) {
-    float s = 0.f;
-    for (int j = 0; j < nsub; ++j) s += part[j * N + threadIdx.x];
-    atomicAdd(out + threadIdx.x, s);
-  }
+  for (int p = 0; p < n_parts; ++p) acc += partials[(size_t)p * stride + i];
+  float* dst = i < n_w ? dw + i : db + (i - n_w);
+  *dst = accumulate ? *dst + acc : acc;
 }
 
 int check_dims(int N, int K, const char* what) {
@@ -350,10 +386,13 @@ int check_dims(int N, int K, const char* what) {
 
 int launch_row_gemm(const float* A, int64_t M, int Kr, const float* W, int w_rows, int w_cols, int mode, RowGemmParams P,
                     cudaStream_t st) {
-  CUtensorMap ta, tw;
+  CUtensorMap ta, tw, to;
   int rc = make_tmap_f32(&ta, A, Kr, M, Kr, 128);
   if (rc) return rc;
   rc = make_tmap_f32(&tw, W, w_cols, w_rows, w_cols, w_rows, mode == 1);
+  if (rc) return rc;
+  const int n_out = mode == 0 ? w_rows : w_cols;
+  rc = make_tmap_f32(&to, P.out, n_out, M, n_out, 128);
   if (rc) return rc;
   P.M = M;
   P.n_kblocks = Kr / 32;
@@ -362,16 +401,17 @@ int launch_row_gemm(const float* A, int64_t M, int Kr, const float* W, int w_row
   P.w_kblocks = w_cols / 32;
   P.n_out = mode == 0 ? w_rows : w_cols;
   const size_t w_bytes = (size_t)w_rows * w_cols * 4;
-  const size_t budget = (size_t)afl_rt::max_smem_optin() - 1024 - 256 - w_bytes;
+  const size_t fixed = 1024 + 2 * (size_t)kStageBytes + 2048 + w_bytes;   // alignment, output staging, barriers + bias
+  const size_t budget = (size_t)afl_rt::max_smem_optin() - fixed;
   int stages = (int)(budget / kStageBytes);
   if (stages > 8) stages = 8;
   if (stages < 2) { afl_rt::set_error("row gemm: weight tile does not leave room for 2 pipeline stages"); return -2; }
   P.stages = stages;
-  const size_t smem = 1024 + w_bytes + (size_t)stages * kStageBytes + (2 * stages + 5) * 8 + 16;
+  const size_t smem = fixed + (size_t)stages * kStageBytes;
   AFL_CUDA(cudaFuncSetAttribute(row_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t n_tiles = (M + 127) / 128;
   const int grid = (int)(n_tiles < afl_rt::num_sms() ? n_tiles : afl_rt::num_sms());
-  row_gemm_kernel<<<grid, kThreads, smem, st>>>(ta, tw, P);
+  row_gemm_kernel<<<grid, kThreads, smem, st>>>(ta, tw, to, P);
   afl_rt::count_launch();
   return afl_rt::check_last("row_gemm_kernel");
 }
@@ -405,7 +445,7 @@ int afl_tc_linear_dx(const float* dY, int64_t M, int N, const float* W, int K, c
 
 int afl_tc_linear_dw_workspace(int N, int K, int64_t* partial_floats) {
   if (check_dims(N, K, "afl_tc_linear_dw_workspace")) return -1;
-  *partial_floats = (int64_t)afl_rt::num_sms() * N * K;
+  *partial_floats = (int64_t)afl_rt::num_sms() * ((int64_t)N * K + N);
   return 0;
 }
 
@@ -422,7 +462,7 @@ int afl_tc_linear_dw(const float* dY, const float* X, int64_t M, int N, int K, f
   rc = make_tmap_f32(&tx, X, K, M, K, kChunkRows, true);
   if (rc) return rc;
   DwParams P{};
-  P.M = M; P.N = N; P.K = K; P.partials = partials;
+  P.M = M; P.N = N; P.K = K; P.partials = partials; P.want_db = db != nullptr ? 1 : 0;
   P.n_chunks = (M + kChunkRows - 1) / kChunkRows;
   const size_t stage_bytes = (size_t)(N / 32 + K / 32) * kBoxBytes;
   const size_t budget = (size_t)afl_rt::max_smem_optin() - 1024 - 256 - 4 * kBoxBytes;
@@ -435,15 +475,8 @@ int afl_tc_linear_dw(const float* dY, const float* X, int64_t M, int N, int K, f
   dw_gemm_kernel<<<grid, kThreads, smem, st>>>(ty, tx, P);
   afl_rt::count_launch();
   const int64_t n = (int64_t)N * K;
-  reduce_partials_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(partials, grid, n, dW, accumulate);
+  reduce_partials_kernel<<<(int)((n + N + 255) / 256), 256, 0, st>>>(partials, grid, n, N, dW, db, accumulate);
   afl_rt::count_launch();
-  if (db) {
-    if (!accumulate) AFL_CUDA(cudaMemsetAsync(db, 0, sizeof(float) * N, st));
-    int g = (int)((M + 255) / 256);
-    if (g > 2 * afl_rt::num_sms()) g = 2 * afl_rt::num_sms();
-    colsum_kernel<<<g, 256, 0, st>>>(dY, M, N, db);
-    afl_rt::count_launch();
-  }
   return afl_rt::check_last("afl_tc_linear_dw");
 }
 
