@@ -194,27 +194,27 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
     const bool drop = P.drop_p > 0.f && P.mask != nullptr;
     const float inv_keep = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.f;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t keep_next = 0xFFFFFFFFu;
+    if (drop && live) keep_next = P.mask[(bh * P.mask_words + (size_t)half) * Tp + qi];
     for (int kb = 0; kb < n_blk; ++kb) {
       const int buf = kb & 1;
-      uint32_t keep = 0xFFFFFFFFu;
-      if (drop && live) keep = P.mask[(bh * P.mask_words + (size_t)(kb * 2 + half)) * Tp + qi];
+      const uint32_t keep = keep_next;                      // the next block's word is fetched one block ahead
+      if (drop && live && kb + 1 < n_blk) keep_next = P.mask[(bh * P.mask_words + (size_t)((kb + 1) * 2 + half)) * Tp + qi];
       mbar_wait(sd_full + buf, ((uint32_t)kb >> 1) & 1u);
       tc_fence_after();
       const int key0 = kb * kBlk + half * 32;
-      float ds[32];
+      float ds[32], dd[32];                                   // scores -> dS in place; dPd
+      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 32), ds);
+      tmem_ld32_async(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(half * 32), dd);
+      tmem_ld_wait();
+      const bool full = key0 + 32 <= P.T;
 #pragma unroll
-      for (int c0 = 0; c0 < 32; c0 += 16) {
-        float s[16], d[16];
-        tmem_ld16(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 32 + c0), s);
-        tmem_ld16(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(half * 32 + c0), d);
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          float p = ex2_approx(fmaf(s[j], kScaleLog2e, -L));
-          const float kp = ((keep >> (c0 + j)) & 1u) ? inv_keep : 0.f;
-          float v = p * fmaf(kp, d[j], -delta);
-          if (key0 + c0 + j >= P.T) v = 0.f;
-          ds[c0 + j] = v;
-        }
+      for (int j = 0; j < 32; ++j) {
+        const float p = ex2_approx(fmaf(ds[j], kScaleLog2e, -L));
+        const float kp = ((keep >> j) & 1u) ? inv_keep : 0.f;
+        float v = p * fmaf(kp, dd[j], -delta);
+        if (!full && key0 + j >= P.T) v = 0.f;
+        ds[j] = v;
       }
       tc_fence_before();
       __syncwarp();
@@ -377,20 +377,26 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       const float* del_s = reinterpret_cast<const float*>(aux + 256) + half * 32;
       const uint32_t* msk_s = reinterpret_cast<const uint32_t*>(aux + 512) + q * 64 + half * 32;
       const int i0 = ib * kBlk + half * 32;
-      float pd[32], ds[32];
+      float pd[32], ds[32];                                   // S^T -> Pd^T in place; dPd^T -> dS^T in place
+      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 32), pd);
+      tmem_ld32_async(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(half * 32), ds);
+      tmem_ld_wait();
+      const bool full = i0 + 32 <= P.T;
 #pragma unroll
-      for (int c0 = 0; c0 < 32; c0 += 16) {
-        float s[16], d[16];
-        tmem_ld16(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 32 + c0), s);
-        tmem_ld16(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(half * 32 + c0), d);
+      for (int i4 = 0; i4 < 32; i4 += 4) {
+        const float4 L4 = *reinterpret_cast<const float4*>(lse_s + i4);
+        const float4 D4 = *reinterpret_cast<const float4*>(del_s + i4);
+        uint4 M4 = make_uint4(~0u, ~0u, ~0u, ~0u);
+        if (drop) M4 = *reinterpret_cast<const uint4*>(msk_s + i4);
+        const float Lv[4] = {L4.x, L4.y, L4.z, L4.w}, Dv[4] = {D4.x, D4.y, D4.z, D4.w};
+        const uint32_t Mv[4] = {M4.x, M4.y, M4.z, M4.w};
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int i = c0 + j;
-          float p = ex2_approx(fmaf(s[j], kScaleLog2e, -lse_s[i]));
-          float kp = inv_keep;
-          if (drop) kp = ((msk_s[i] >> lane) & 1u) ? inv_keep : 0.f;
-          float a = p * kp, g = p * fmaf(kp, d[j], -del_s[i]);
-          if (i0 + i >= P.T) { a = 0.f; g = 0.f; }
+        for (int u = 0; u < 4; ++u) {
+          const int i = i4 + u;
+          const float p = ex2_approx(fmaf(pd[i], kScaleLog2e, -Lv[u]));
+          const float kp = ((Mv[u] >> lane) & 1u) ? inv_keep : 0.f;
+          float a = p * kp, g = p * fmaf(kp, ds[i], -Dv[u]);
+          if (!full && i0 + i >= P.T) { a = 0.f; g = 0.f; }
           pd[i] = a; ds[i] = g;
         }
       }

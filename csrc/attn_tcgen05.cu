@@ -191,17 +191,16 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
       mbar_wait(s_full + buf, ((uint32_t)n >> 1) & 1u);
       tc_fence_after();
       const int key0 = n * kBlk + half * 64;
+      float v[64];
+      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64), v);
+      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64 + 32), v + 32);
+      tmem_ld_wait();
+      if (key0 + 64 <= P.T) {                   // every key of this half is real: no masking
 #pragma unroll
-      for (int c0 = 0; c0 < 64; c0 += 16) {
-        float v[16];
-        tmem_ld16(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64 + c0), v);
-        if (key0 + 64 <= P.T) {                 // every key of this half is real: no masking
+        for (int j = 0; j < 64; ++j) mx = fmaxf(mx, v[j]);
+      } else {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) mx = fmaxf(mx, v[j]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) if (key0 + c0 + j < P.T) mx = fmaxf(mx, v[j]);
-        }
+        for (int j = 0; j < 64; ++j) if (key0 + j < P.T) mx = fmaxf(mx, v[j]);
       }
       tc_fence_before();
       __syncwarp();
@@ -220,10 +219,15 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
       const int key0 = kb * kBlk + half * 64;
       const bool full = key0 + 64 <= P.T;
       uint32_t keep_lo = 0;
+      float v64[64];
+      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64), v64);
+      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64 + 32), v64 + 32);
+      tmem_ld_wait();
+      // all 64 probabilities first (registers), so that this math overlaps the previous block's P V; only then wait for
+      // the P buffer and write the operand tile
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 16) {
-        float v[16];
-        tmem_ld16(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 64 + c0), v);
+        float* v = v64 + c0;
         const int kc = key0 + c0;
         uint32_t kb16;
         if (full) {
@@ -240,8 +244,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
         } else {
           keep_lo = kb16;
         }
+      }
+      mbar_wait(p_empty, ((uint32_t)kb & 1u) ^ 1u);       // previous block's P V has consumed the P buffer
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        const float* v = v64 + c0;
         // keys (half*64 + c0 .. +15) of this block: k-block (32 keys) index and 16-byte chunk inside the 128-byte row
-        if (c0 == 0) mbar_wait(p_empty, ((uint32_t)kb & 1u) ^ 1u);   // previous block's P V has consumed the P buffer
         const int kcol = half * 64 + c0;
         uint8_t* rowp = p_ptr + (size_t)(kcol >> 5) * kBlkBytes + (size_t)r * 128;
 #pragma unroll
