@@ -150,16 +150,21 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
     if (lane == 0) {
       const uint32_t idesc_s = idesc_tf32(128, kBlk, 0, 0);
       const uint32_t idesc_q = idesc_tf32(128, 32, 0, 1);
+      const uint64_t qd0 = desc_k_sw128(q_base + hoff), qd1 = desc_add(qd0, 32);
+      const uint64_t od0 = desc_k_sw128(do_base + hoff), od1 = desc_add(od0, 32);
+      const uint64_t kd0 = desc_k_sw128(st_base + hoff);                       // + stage offset (+ 2 boxes for V)
+      const uint64_t ad0 = desc_k_sw128(ds_base);                              // dS tile, + buffer / k-step offset
+      const uint64_t bd0 = desc_mn_sw128(st_base + kBlkBytes, kBlkBytes);      // K block MN-major, + stage / k-step offset
       auto issue_dq = [&](int kb) {          // dQ += dS(kb) . K(kb)
         const int dbuf = kb & 1, st = kb % kStages;
         mbar_wait(ds_full + dbuf, ((uint32_t)kb >> 1) & 1u);
         tc_fence_after();
-        const uint32_t a_addr = ds_base + (uint32_t)dbuf * 2 * kTileBytes;
-        const uint32_t k_at = st_base + (uint32_t)st * kStageBytes + kBlkBytes;
+        const uint64_t ad = desc_add(ad0, (uint32_t)dbuf * 2 * kTileBytes);
+        const uint64_t bd = desc_add(bd0, (uint32_t)st * kStageBytes);
 #pragma unroll
         for (int k8 = 0; k8 < kBlk / 8; ++k8)
-          umma_tf32(tmem_base + kDqCol, desc_k_sw128(a_addr + (uint32_t)(k8 >> 2) * kTileBytes + (uint32_t)(k8 & 3) * 32u),
-                    desc_mn_sw128(k_at + (uint32_t)k8 * 1024u, kBlkBytes), idesc_q, (kb > 0 || k8 > 0) ? 1u : 0u);
+          umma_tf32(tmem_base + kDqCol, desc_add(ad, (uint32_t)(k8 >> 2) * kTileBytes + (uint32_t)(k8 & 3) * 32u),
+                    desc_add(bd, (uint32_t)k8 * 1024u), idesc_q, (kb > 0 || k8 > 0) ? 1u : 0u);
         umma_commit(ds_empty + dbuf);
         umma_commit(kv_empty + st);
       };
@@ -169,14 +174,13 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
         mbar_wait(kv_full + st, ((uint32_t)(kb / kStages)) & 1u);
         mbar_wait(sd_empty + buf, (((uint32_t)kb >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t s_addr = st_base + (uint32_t)st * kStageBytes;
-#pragma unroll
-        for (int ks = 0; ks < 2; ++ks) {
-          umma_tf32(tmem_base + (uint32_t)buf * kBlk, desc_k_sw128(q_base + hoff + (uint32_t)ks * 32u),
-                    desc_k_sw128(s_addr + hoff + (uint32_t)ks * 32u), idesc_s, ks);
-          umma_tf32(tmem_base + 128u + (uint32_t)buf * kBlk, desc_k_sw128(do_base + hoff + (uint32_t)ks * 32u),
-                    desc_k_sw128(s_addr + 2 * kBlkBytes + hoff + (uint32_t)ks * 32u), idesc_s, ks);
-        }
+        const uint64_t kd = desc_add(kd0, (uint32_t)st * kStageBytes);
+        const uint64_t vd = desc_add(kd, 2 * kBlkBytes);
+        const uint32_t s_col = tmem_base + (uint32_t)buf * kBlk;
+        umma_tf32(s_col, qd0, kd, idesc_s, 0u);
+        umma_tf32(s_col, qd1, desc_add(kd, 32), idesc_s, 1u);
+        umma_tf32(s_col + 128u, od0, vd, idesc_s, 0u);
+        umma_tf32(s_col + 128u, od1, desc_add(vd, 32), idesc_s, 1u);
         umma_commit(sd_full + buf);
         if (kb > 0) issue_dq(kb - 1);
       }
@@ -325,18 +329,22 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
     if (lane == 0) {
       const uint32_t idesc_s = idesc_tf32(128, kBlk, 0, 0);
       const uint32_t idesc_g = idesc_tf32(128, 32, 0, 1);
+      const uint64_t kd0 = desc_k_sw128(k_base + hoff), kd1 = desc_add(kd0, 32);
+      const uint64_t vd0 = desc_k_sw128(v_base + hoff), vd1 = desc_add(vd0, 32);
+      const uint64_t qd0 = desc_k_sw128(st_base + hoff);                       // Q block K-major (+ stage; dO: + 1 box)
+      const uint64_t pa0 = desc_k_sw128(pd_base), sa0 = desc_k_sw128(dst_base);
+      const uint64_t qt0 = desc_mn_sw128(st_base + 2 * kBlkBytes, kBlkBytes);  // Q block MN-major (+ stage; dO: + 1 box)
       auto issue_grad = [&](int ib) {        // dV += Pd^T(ib) . dO(ib);  dK += dS^T(ib) . Q(ib)
         const int st = ib & 1;
         mbar_wait(pd_full, (uint32_t)ib & 1u);
         tc_fence_after();
-        const uint32_t s_addr = st_base + (uint32_t)st * kStageBytes;
+        const uint64_t qt = desc_add(qt0, (uint32_t)st * kStageBytes);
+        const uint64_t ot = desc_add(qt, kBlkBytes);
 #pragma unroll
         for (int k8 = 0; k8 < kBlk / 8; ++k8) {
           const uint32_t a_off = (uint32_t)(k8 >> 2) * kTileBytes + (uint32_t)(k8 & 3) * 32u;
-          umma_tf32(tmem_base + kDvCol, desc_k_sw128(pd_base + a_off),
-                    desc_mn_sw128(s_addr + 3 * kBlkBytes + (uint32_t)k8 * 1024u, kBlkBytes), idesc_g, (ib > 0 || k8 > 0) ? 1u : 0u);
-          umma_tf32(tmem_base + kDkCol, desc_k_sw128(dst_base + a_off),
-                    desc_mn_sw128(s_addr + 2 * kBlkBytes + (uint32_t)k8 * 1024u, kBlkBytes), idesc_g, (ib > 0 || k8 > 0) ? 1u : 0u);
+          umma_tf32(tmem_base + kDvCol, desc_add(pa0, a_off), desc_add(ot, (uint32_t)k8 * 1024u), idesc_g, (ib > 0 || k8 > 0) ? 1u : 0u);
+          umma_tf32(tmem_base + kDkCol, desc_add(sa0, a_off), desc_add(qt, (uint32_t)k8 * 1024u), idesc_g, (ib > 0 || k8 > 0) ? 1u : 0u);
         }
         umma_commit(pd_empty);
         umma_commit(q_empty + st);
@@ -347,14 +355,13 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
         mbar_wait(q_full + st, ((uint32_t)ib >> 1) & 1u);
         mbar_wait(sd_empty + buf, (((uint32_t)ib >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t s_addr = st_base + (uint32_t)st * kStageBytes;
-#pragma unroll
-        for (int ks = 0; ks < 2; ++ks) {
-          umma_tf32(tmem_base + (uint32_t)buf * kBlk, desc_k_sw128(k_base + hoff + (uint32_t)ks * 32u),
-                    desc_k_sw128(s_addr + hoff + (uint32_t)ks * 32u), idesc_s, ks);
-          umma_tf32(tmem_base + 128u + (uint32_t)buf * kBlk, desc_k_sw128(v_base + hoff + (uint32_t)ks * 32u),
-                    desc_k_sw128(s_addr + kBlkBytes + hoff + (uint32_t)ks * 32u), idesc_s, ks);
-        }
+        const uint64_t qd = desc_add(qd0, (uint32_t)st * kStageBytes);
+        const uint64_t od = desc_add(qd, kBlkBytes);
+        const uint32_t s_col = tmem_base + (uint32_t)buf * kBlk;
+        umma_tf32(s_col, kd0, qd, idesc_s, 0u);
+        umma_tf32(s_col, kd1, desc_add(qd, 32), idesc_s, 1u);
+        umma_tf32(s_col + 128u, vd0, od, idesc_s, 0u);
+        umma_tf32(s_col + 128u, vd1, desc_add(od, 32), idesc_s, 1u);
         umma_commit(sd_full + buf);
         if (ib > 0) issue_grad(ib - 1);
       }

@@ -139,20 +139,22 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
       const uint32_t idesc_s = idesc_tf32(128, kBlk, 0, 0);              // S: M = 128 queries, N = 128 keys
       const uint32_t idesc_o = idesc_tf32(128, 32, 0, 1);                // O: N = 32 (head pair), B MN-major
       const int n_s = 2 * n_kb;
+      const uint64_t qd0 = desc_k_sw128(q_base + hoff), qd1 = desc_add(qd0, 32);
+      const uint64_t kd0 = desc_k_sw128(k_base + hoff), kd1 = desc_add(kd0, 32);
+      const uint64_t pd0 = desc_k_sw128(p_base);
+      const uint64_t vd0 = desc_mn_sw128(v_base, kBlkBytes);
       auto issue_s = [&](int n) {
         const int buf = n & 1, kb = n % n_kb;
         mbar_wait(s_empty + buf, (((uint32_t)n >> 1) & 1u) ^ 1u);
         tc_fence_after();
-#pragma unroll
-        for (int ks = 0; ks < 2; ++ks)
-          umma_tf32(tmem_base + (uint32_t)buf * kBlk, desc_k_sw128(q_base + hoff + (uint32_t)ks * 32u),
-                    desc_k_sw128(k_base + (uint32_t)kb * kBlkBytes + hoff + (uint32_t)ks * 32u), idesc_s, ks);
+        const uint32_t koff = (uint32_t)kb * kBlkBytes;
+        umma_tf32(tmem_base + (uint32_t)buf * kBlk, qd0, desc_add(kd0, koff), idesc_s, 0u);
+        umma_tf32(tmem_base + (uint32_t)buf * kBlk, qd1, desc_add(kd1, koff), idesc_s, 1u);
         umma_commit(s_full + buf);
       };
       mbar_wait(qk_full, 0);
       tc_fence_after();
       issue_s(0);
-      bool first_pv = true;
       for (int n = 0; n < n_s; ++n) {
         if (n + 1 < n_s) issue_s(n + 1);
         if (n >= n_kb) {
@@ -160,13 +162,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_cons
           if (kb == 0) { mbar_wait(v_full, 0); tc_fence_after(); }
           mbar_wait(p_full, (uint32_t)kb & 1u);
           tc_fence_after();
-          const int keys = kb + 1 < n_kb ? kBlk : P.tail_rows;
-          for (int k8 = 0; k8 < keys / 8; ++k8) {
-            const uint64_t adesc = desc_k_sw128(p_base + (uint32_t)(k8 >> 2) * kBlkBytes + (uint32_t)(k8 & 3) * 32u);
-            const uint64_t bdesc = desc_mn_sw128(v_base + (uint32_t)kb * kBlkBytes + (uint32_t)k8 * 1024u, kBlkBytes);
-            umma_tf32(tmem_base + kOCol, adesc, bdesc, idesc_o, first_pv ? 0u : 1u);
-            first_pv = false;
-          }
+          const int nk8 = (kb + 1 < n_kb ? kBlk : P.tail_rows) / 8;
+          const uint64_t vd = desc_add(vd0, (uint32_t)kb * kBlkBytes);
+#pragma unroll
+          for (int k8 = 0; k8 < kBlk / 8; ++k8)
+            if (k8 < nk8)
+              umma_tf32(tmem_base + kOCol, desc_add(pd0, (uint32_t)(k8 >> 2) * kBlkBytes + (uint32_t)(k8 & 3) * 32u),
+                        desc_add(vd, (uint32_t)k8 * 1024u), idesc_o, (kb > 0 || k8 > 0) ? 1u : 0u);
           umma_commit(p_empty);
         }
       }

@@ -110,6 +110,7 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     if (lane == 0) {
       // ===== MMA issuer =====
       const uint32_t idesc = idesc_tf32(128, P.n_out, 0, P.mode);
+      const uint64_t ad0 = desc_k_sw128(a_base), bk0 = desc_k_sw128(w_base), bm0 = desc_mn_sw128(w_base, w_box_bytes);
       mbar_wait(w_full, 0);
       int it = 0, t = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t) {
@@ -122,15 +123,13 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const uint32_t ph = (uint32_t)(it / P.stages) & 1u;
           mbar_wait(full + st, ph);
           tc_fence_after();
-          const uint32_t a_addr = a_base + (uint32_t)st * kStageBytes;
+          const uint64_t ad = desc_add(ad0, (uint32_t)st * kStageBytes);
+          const uint64_t bd = P.mode == 0 ? desc_add(bk0, (uint32_t)kb * w_box_bytes) : desc_add(bm0, (uint32_t)kb * 4096u);
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks) {       // 8 tf32 (32 bytes) of the reduction per MMA
-            const uint64_t adesc = desc_k_sw128(a_addr + (uint32_t)ks * 32u);
-            const uint64_t bdesc = P.mode == 0
-                ? desc_k_sw128(w_base + (uint32_t)kb * w_box_bytes + (uint32_t)ks * 32u)
-                : desc_mn_sw128(w_base + (uint32_t)(kb * 4 + ks) * 1024u, w_box_bytes);
-            umma_tf32(d_tmem, adesc, bdesc, idesc, (kb > 0 || ks > 0) ? 1u : 0u);
-          }
+          for (int ks = 0; ks < 4; ++ks)         // 8 tf32 (32 bytes) of the reduction per MMA
+            umma_tf32(d_tmem, desc_add(ad, (uint32_t)ks * 32u),
+                      P.mode == 0 ? desc_add(bd, (uint32_t)ks * 32u) : desc_add(bd, (uint32_t)ks * 1024u), idesc,
+                      (kb > 0 || ks > 0) ? 1u : 0u);
           umma_commit(empty + st);
         }
         umma_commit(acc_full + buf);
@@ -291,20 +290,19 @@ dw_gemm_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constan
       // next boxes of the stage (X data, or the slack after the last stage) as extra A rows: finite or not, those
       // accumulator rows are never read back.
       const uint32_t idesc = idesc_tf32(128, P.K, 1, 1);
+      const uint64_t ad0 = desc_mn_sw128(base, kBoxBytes);
       for (int i = 0; i < nch; ++i) {
         const int st = i % P.stages;
         const uint32_t ph = (uint32_t)(i / P.stages) & 1u;
         mbar_wait(full + st, ph);
         tc_fence_after();
-        const uint32_t s_addr = base + (uint32_t)st * stage_bytes;
+        const uint64_t ad = desc_add(ad0, (uint32_t)st * stage_bytes);
+        const uint64_t bd = desc_add(ad, (uint32_t)a_boxes * kBoxBytes);
 #pragma unroll
-        for (int ks = 0; ks < kChunkRows / 8; ++ks) {
-          const uint64_t bdesc = desc_mn_sw128(s_addr + (uint32_t)a_boxes * kBoxBytes + (uint32_t)ks * 1024u, kBoxBytes);
-          for (int mt = 0; mt < m_tiles; ++mt) {
-            const uint64_t adesc = desc_mn_sw128(s_addr + (uint32_t)(mt * 4) * kBoxBytes + (uint32_t)ks * 1024u, kBoxBytes);
-            umma_tf32(tmem_base + (uint32_t)(mt * P.K), adesc, bdesc, idesc, (i > 0 || ks > 0) ? 1u : 0u);
-          }
-        }
+        for (int ks = 0; ks < kChunkRows / 8; ++ks)
+          for (int mt = 0; mt < m_tiles; ++mt)
+            umma_tf32(tmem_base + (uint32_t)(mt * P.K), desc_add(ad, (uint32_t)(mt * 4) * kBoxBytes + (uint32_t)ks * 1024u),
+                      desc_add(bd, (uint32_t)ks * 1024u), idesc, (i > 0 || ks > 0) ? 1u : 0u);
         umma_commit(empty + st);
       }
       umma_commit(acc_full);

@@ -70,6 +70,12 @@ __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t smem_addr, uint32_t l
   return d;
 }
 
+// Same descriptor `byte_off` bytes further (the start-address field counts 16-byte units and shared memory is < 256 KB,
+// so the add never carries out of the field).  The MMA-issuing thread is a serial resource: building each descriptor
+// from scratch costs ~10 dependent ALU ops per MMA, which made that one thread the bottleneck of the attention kernels;
+// hoisted base descriptors + constant offsets leave one add per operand.
+__device__ __forceinline__ uint64_t desc_add(uint64_t d, uint32_t byte_off) { return d + (uint64_t)(byte_off >> 4); }
+
 // kind::tf32 instruction descriptor: c_format [4,6) = 1 (F32), a_format [7,10) = b_format [10,13) = 2 (TF32),
 // a_major [15], b_major [16] (1 = MN-major), n_dim [17,23) = N >> 3, m_dim [24,29) = M >> 4.
 __device__ __forceinline__ uint32_t idesc_tf32(int M, int N, int a_mn, int b_mn) {
