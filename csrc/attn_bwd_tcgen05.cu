@@ -255,7 +255,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
                        const __grid_constant__ CUtensorMap tm_q64t, const __grid_constant__ CUtensorMap tm_o64,
                        const __grid_constant__ CUtensorMap tm_o64t, BwdParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  constexpr int kStages = 2;
+  constexpr int kStages = 3;
   constexpr uint32_t kAux = 2048;                                          // lse 256 + delta 256 + mask 1024 (+ pad)
   constexpr uint32_t kStageBytes = 4 * kBlkBytes + kAux;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -267,14 +267,14 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
   uint8_t* dst_ptr = aligned + (dst_base - base);
   uint64_t* bars = reinterpret_cast<uint64_t*>(dst_ptr + 2 * kTileBytes);
   uint64_t* kv_full = bars;
-  uint64_t* q_full = bars + 1;           // [2]
-  uint64_t* q_empty = bars + 3;          // [2]
-  uint64_t* sd_full = bars + 5;          // [2]
-  uint64_t* sd_empty = bars + 7;         // [2]
-  uint64_t* pd_full = bars + 9;
-  uint64_t* pd_empty = bars + 10;
-  uint64_t* acc_full = bars + 11;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* q_full = bars + 1;           // [3]
+  uint64_t* q_empty = bars + 4;          // [3]
+  uint64_t* sd_full = bars + 7;          // [2]
+  uint64_t* sd_empty = bars + 9;         // [2]
+  uint64_t* pd_full = bars + 11;
+  uint64_t* pd_empty = bars + 12;
+  uint64_t* acc_full = bars + 13;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, h = blockIdx.y, k0 = blockIdx.x * kTile;
@@ -290,7 +290,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
 
   if (warp == 0 && lane == 0) {
     mbar_init(kv_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(q_full + i, 1); mbar_init(q_empty + i, 1); mbar_init(sd_full + i, 1); mbar_init(sd_empty + i, 8); }
+    for (int i = 0; i < kStages; ++i) { mbar_init(q_full + i, 1); mbar_init(q_empty + i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(sd_full + i, 1); mbar_init(sd_empty + i, 8); }
     mbar_init(pd_full, 8); mbar_init(pd_empty, 1); mbar_init(acc_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -306,8 +307,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       tma_load_2d(k_base, &tm_k128, kD + hp * 32, row0 + k0, kv_full);
       tma_load_2d(v_base, &tm_k128, 2 * kD + hp * 32, row0 + k0, kv_full);
       for (int ib = 0; ib < n_blk; ++ib) {
-        const int st = ib & 1;
-        mbar_wait(q_empty + st, (((uint32_t)ib >> 1) & 1u) ^ 1u);
+        const int st = ib % kStages;
+        mbar_wait(q_empty + st, (((uint32_t)(ib / kStages)) & 1u) ^ 1u);
         const uint32_t aux_bytes = 512u + (drop ? 1024u : 0u);
         mbar_expect_tx(q_full + st, 4 * kBlkBytes + aux_bytes);
         const uint32_t s_addr = st_base + (uint32_t)st * kStageBytes;
@@ -335,7 +336,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       const uint64_t pa0 = desc_k_sw128(pd_base), sa0 = desc_k_sw128(dst_base);
       const uint64_t qt0 = desc_mn_sw128(st_base + 2 * kBlkBytes, kBlkBytes);  // Q block MN-major (+ stage; dO: + 1 box)
       auto issue_grad = [&](int ib) {        // dV += Pd^T(ib) . dO(ib);  dK += dS^T(ib) . Q(ib)
-        const int st = ib & 1;
+        const int st = ib % kStages;
         mbar_wait(pd_full, (uint32_t)ib & 1u);
         tc_fence_after();
         const uint64_t qt = desc_add(qt0, (uint32_t)st * kStageBytes);
@@ -351,8 +352,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       };
       mbar_wait(kv_full, 0);
       for (int ib = 0; ib < n_blk; ++ib) {
-        const int st = ib & 1, buf = ib & 1;
-        mbar_wait(q_full + st, ((uint32_t)ib >> 1) & 1u);
+        const int st = ib % kStages, buf = ib & 1;
+        mbar_wait(q_full + st, ((uint32_t)(ib / kStages)) & 1u);
         mbar_wait(sd_empty + buf, (((uint32_t)ib >> 1) & 1u) ^ 1u);
         tc_fence_after();
         const uint64_t qd = desc_add(qd0, (uint32_t)st * kStageBytes);
@@ -375,8 +376,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
     const float inv_keep = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.f;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int ib = 0; ib < n_blk; ++ib) {
-      const int buf = ib & 1, st = ib & 1;
-      mbar_wait(q_full + st, ((uint32_t)ib >> 1) & 1u);        // lse / delta / mask rows of this block are in smem
+      const int buf = ib & 1, st = ib % kStages;
+      mbar_wait(q_full + st, ((uint32_t)(ib / kStages)) & 1u); // lse / delta / mask rows of this block are in smem
       mbar_wait(sd_full + buf, ((uint32_t)ib >> 1) & 1u);
       tc_fence_after();
       const uint8_t* aux = aligned + (st_base - base) + (size_t)st * kStageBytes + 4 * kBlkBytes;
@@ -470,7 +471,7 @@ int afl_har_attn_bwd_tc(const float* qkv, const float* out, const float* dout, c
   const size_t smem_dq = 1024 + 2 * kTileBytes + 3 * 3 * kBlkBytes + 4 * kTileBytes + 17 * 8 + 64;
   AFL_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
   attn_bwd_dq_tc_kernel<<<grid, kThreads, smem_dq, st>>>(q128, o128, k64, k64t, P);
-  const size_t smem_kv = 1024 + 2 * kTileBytes + 2 * (4 * kBlkBytes + 2048) + 4 * kTileBytes + 13 * 8 + 64;
+  const size_t smem_kv = 1024 + 2 * kTileBytes + 3 * (4 * kBlkBytes + 2048) + 4 * kTileBytes + 15 * 8 + 64;
   AFL_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_kv));
   attn_bwd_dkv_tc_kernel<<<grid, kThreads, smem_kv, st>>>(q128, k64, k64t, o64, o64t, P);
   afl_rt::count_launch(3);
