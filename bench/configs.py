@@ -8,6 +8,8 @@
   2: CNNModel, mode hyper, 8 clients, genuine-rate 0.5
   3: TransformerModel, fedavg, 8 clients per GPU, LIE z=0.74          (same as bench.py)
   4: RNNModel, fedavg, 128 clients, Min-Max / Min-Sum / Opt-Fang       (Gram-GEMM path)
+  6: HAR TransformerClassifier (T = 561), fedavg, 8 clients, 1 local epoch of 1,024 samples, batch 128 — not a
+     BASELINE.json config (the reference's HAR client path raises); `--backend torch` is the PyTorch-module arm
 One JSON line: FL rounds/sec, device-timed (CUDA events per round, max over ranks), shipped learning config.
 """
 import argparse
@@ -32,12 +34,18 @@ def make(config: int, clients: int, attack: str):
     elif config == 4:
         cfg["server"].update(mode="fedavg", model="RNNModel")
         attackers = {c: (attack, 2, None) for c in range(clients) if c % 8 == 7}
+    elif config == 6:
+        cfg["server"].update(mode="fedavg", model="TransformerClassifier")
+        cfg["server"]["data-name"] = "HAR"
+        cfg["server"]["data-distribution"] = {"num-data-range": [1024, 1024]}
+        cfg["learning"].update(epoch=1)
+        attackers = {c: ("LIE", 2, [0.74]) for c in range(clients) if c % 8 == 7}
     else:
-        raise SystemExit("--config must be 2, 3 or 4")
+        raise SystemExit("--config must be 2, 3, 4 or 6")
     return cfg, attackers
 
 
-def run_ours(cfg_d, attackers, rounds, warmup):
+def run_ours(cfg_d, attackers, rounds, warmup, backend="auto"):
     import torch
 
     from attackfl_b200 import from_dict
@@ -49,10 +57,16 @@ def run_ours(cfg_d, attackers, rounds, warmup):
     set_quiet(True)
     ctx = pctx.init_from_env("cuda")
     cfg = from_dict(cfg_d)
+    cfg.runtime.backend = backend
     C = cfg.server.clients
     specs = [ClientSpec(i, True, *attackers[i]) if i in attackers else ClientSpec(i) for i in range(C)]
-    fed = Federation(cfg, specs, ctx=ctx, train_set=synthetic_icu(headline.TRAIN_ROWS, 1),
-                     test_set=synthetic_icu(headline.TEST_ROWS, 102), workdir=tempfile.mkdtemp(), save=False, verbose=False)
+    if cfg.server.data_name == "HAR":
+        from attackfl_b200.data import synthetic_har
+        train, test = synthetic_har(4096, 1), synthetic_har(1024, 102)
+    else:
+        train, test = synthetic_icu(headline.TRAIN_ROWS, 1), synthetic_icu(headline.TEST_ROWS, 102)
+    fed = Federation(cfg, specs, ctx=ctx, train_set=train, test_set=test, workdir=tempfile.mkdtemp(), save=False,
+                     verbose=False)
     if ctx.distributed and cfg.runtime.collectives == "fused":
         from attackfl_b200.parallel import symm
         symm.attach(fed)
@@ -79,7 +93,8 @@ def run_ours(cfg_d, attackers, rounds, warmup):
            "n_gpus": ctx.world, "clients": C, "rounds": rounds, "warmup": warmup, "model": cfg.server.model,
            "mode": cfg.server.mode, "attackers": {str(k): list(v) for k, v in attackers.items()},
            "phases_ms": {k: round(v, 3) for k, v in phases.items()}, "gpu_launches": native.launch_count(),
-           "metric_last": metric, "plan": {"G": fed.plan.G, "M": fed.plan.M, "S": fed.plan.S, "chunk": fed.plan.chunk}}
+           "metric_last": metric, "plan": ({"G": fed.plan.G, "M": fed.plan.M, "S": fed.plan.S, "chunk": fed.plan.chunk} if getattr(fed, "plan", None)
+                                             else {"trainer": "har-native" if fed.har_trainer is not None else "torch"})}
     return out if ctx.rank == 0 else {}
 
 
@@ -91,9 +106,10 @@ def main():
     ap.add_argument("--rounds", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
+    ap.add_argument("--backend", default="auto", help="runtime.backend of our arm: auto | native | torch")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    clients = a.clients or {2: 8, 3: 8 * world, 4: 128}[a.config]
+    clients = a.clients or {2: 8, 3: 8 * world, 4: 128, 6: 8 * world}[a.config]
     cfg, attackers = make(a.config, clients, a.attack)
     if a.impl == "reference":
         from baseline import harness_ref
@@ -102,7 +118,9 @@ def main():
         if out:
             out["rounds_per_sec"] = out.get("rounds_per_sec")
     else:
-        out = run_ours(cfg, attackers, a.rounds, a.warmup)
+        out = run_ours(cfg, attackers, a.rounds, a.warmup, a.backend)
+        if out:
+            out["backend"] = a.backend
     if out:
         out["bench_config"] = a.config
         print(json.dumps(out), flush=True)
