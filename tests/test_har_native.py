@@ -226,3 +226,41 @@ def test_engine_har_round_native_vs_torch(tmp_path):
         rows.append(fed.global_row.clone()); metrics.append(res[0].metric)
         fed.close()
     assert _rel(rows[0], rows[1]) < 2e-2
+
+
+@pytest.mark.parametrize("mode", ["ffma", "tc-fwd"])
+def test_grad_step_attention_fallback_modes(mode, monkeypatch):
+    """ATTACKFL_HAR_ATTN selects the FFMA attention kernels (the path sequences longer than 568 tokens take) or the
+    tensor-core forward with the FFMA backward; both must give the same gradients as autograd."""
+    monkeypatch.setenv("ATTACKFL_HAR_ATTN", mode)
+    mod, lay, row, tr, x, y = _setup(B=3, seed=5)
+    assert tr.attn_tc == (mode != "ffma") and not (tr.attn_tc and tr.attn_bwd_tc)
+    loss = torch.nn.functional.cross_entropy(mod(x[:, None, :]), y)
+    loss.backward()
+    grad = torch.zeros_like(row)
+    tr.out3.zero_()
+    tr.grad_step(row, grad, x, y, dropout=False)
+    got = lay.views(grad)
+    bad = {k: round(_rel(got[k], v.grad), 4) for k, v in mod.named_parameters() if _rel(got[k], v.grad) > 2e-2}
+    assert not bad, bad
+
+
+def test_partial_batch_and_dropout_masks_reach_backward():
+    """A ragged last batch (B = 5 of max 8) with dropout: finite-difference check of the full step's loss against the
+    analytic gradient along a random direction (same seed => same masks on every evaluation)."""
+    mod, lay, row, tr, x, y = _setup(B=5, seed=6)
+    grad = torch.zeros_like(row)
+
+    def loss_at(r):
+        tr.out3.zero_()
+        tr.grad_step(r, grad, x, y, seed=11, client=2, step=4, dropout=True)
+        return tr.out3[0].item() / 5
+    base = loss_at(row)
+    g0 = grad.clone()
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    d = torch.randn(row.shape, device="cuda", generator=gen) * lay.valid_mask("cuda").float()
+    d[lay.views(torch.arange(row.numel(), device="cuda").float())["pe.pe"].long().flatten()] = 0   # buffer, not trained
+    eps = 2e-3
+    fd = (loss_at(row + eps * d) - loss_at(row - eps * d)) / (2 * eps)
+    an = float((g0 * d).sum())
+    assert abs(fd - an) < 5e-2 * max(1.0, abs(an)), (fd, an, base)
