@@ -1,6 +1,6 @@
 #!/usr/bin/env bash
 set -u
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/ -m gpu -q 2>&1 | tail -8
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
-python bench.py --steps 5 --warmup 3 2>&1 | tail -1 | tee gpurun_out/bench_n1_latest.json | cut -c1-400
+timeout 1500 python -m pytest tests/ -m gpu -q 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3
+python bench.py --steps 5 --warmup 3 2>&1 | tail -1 | tee gpurun_out/bench_n1_latest.json | cut -c1-200
