@@ -19,7 +19,7 @@ def main():
     device = os.environ.get("AFL_TEST_DEVICE", "cpu")
     ctx = pctx.init_from_env(device)
     n = 6
-    cfg = from_dict({"server": {"num-round": 2, "clients": n, "mode": mode, "model": "TransformerModel", "data-name": "ICU",
+    cfg = from_dict({"server": {"num-round": int(os.environ.get("AFL_TEST_ROUNDS", "2")), "clients": n, "mode": mode, "model": "TransformerModel", "data-name": "ICU",
                                 "data-distribution": {"num-data-range": [200, 260]}, "random-seed": 1},
                      "learning": {"epoch": 1, "batch-size": 64, "learning-rate": 0.004, "hyper-lr": 0.001,
                                   "clip-grad-norm": 1.0},
@@ -32,6 +32,19 @@ def main():
     if ctx.distributed and cfg.runtime.collectives == "fused":
         from attackfl_b200.parallel import symm
         symm.attach(fed)
+        if os.environ.get("AFL_TEST_JITTER"):
+            # randomised per-rank delays (up to ~2 ms of device time) in front of every fused collective: the in-kernel
+            # flag barriers must not depend on the ranks arriving together
+            import random
+            rng = random.Random(1234 + 17 * ctx.rank)
+            comm = fed.fused_comm
+            for name in ("fedavg", "gram_attack"):
+                inner = getattr(comm, name)
+
+                def delayed(*a, _inner=inner, **k):
+                    torch.cuda._sleep(rng.randrange(0, 4_000_000))
+                    return _inner(*a, **k)
+                setattr(comm, name, delayed)
     res = fed.run()
     glob = fed.global_row if mode != "hyper" else fed.hyper.head_b
     rec = {"rank": ctx.rank, "world": ctx.world, "ok": [r.ok for r in res], "metric": [r.metric for r in res],

@@ -55,3 +55,23 @@ def test_two_gpus_fused_matches_nccl_path(tmp_path, attack):
     # same seeds, same algorithm: the two data paths agree up to fp summation order / tf32 Gram rounding
     assert out["fused"]["checksum"] == pytest.approx(out["nccl"]["checksum"], rel=2e-3, abs=2e-2)
     assert out["fused"]["metric"][-1] == pytest.approx(out["nccl"]["metric"][-1], abs=0.02)
+
+
+@pytest.mark.gpu
+def test_two_gpus_fused_with_random_rank_delays(tmp_path):
+    """Cross-GPU flag protocol under skew: every fused collective is preceded by a random per-rank device delay; the
+    result must equal the undelayed run bit for bit (same kernels, same order of operations)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = {}
+    for tag, env in (("plain", {}), ("jitter", {"AFL_TEST_JITTER": "1"})):
+        d = tmp_path / tag
+        d.mkdir()
+        recs = _launch(d, 2, "fedavg", "Min-Max", {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": "fused",
+                                                    "AFL_TEST_ROUNDS": "4", **env})
+        a, b = recs
+        assert a["ok"] == b["ok"] == [True] * 4 and a["fused"]
+        assert a["checksum"] == pytest.approx(b["checksum"], rel=1e-6)
+        out[tag] = a
+    assert out["jitter"]["checksum"] == pytest.approx(out["plain"]["checksum"], rel=1e-6)
+    assert out["jitter"]["metric"] == pytest.approx(out["plain"]["metric"], abs=1e-6)
