@@ -10,9 +10,8 @@ from __future__ import annotations
 
 import json
 import socket
-import threading
 import time
-from typing import Callable, Dict, List, Optional, Tuple
+from typing import Callable, List, Optional, Tuple
 
 
 def _send(sock: socket.socket, obj: dict) -> None:

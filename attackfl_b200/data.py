@@ -17,9 +17,8 @@ import io
 import os
 import pickle
 import random
-from typing import Optional, Tuple
+from typing import Optional
 
-import numpy as np
 import torch
 from torch.utils.data import Dataset
 

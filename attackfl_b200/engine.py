@@ -14,8 +14,6 @@ Only per-client ``size`` / ``result`` scalars and the round metric ever reach th
 """
 from __future__ import annotations
 
-import copy
-import math
 import os
 import random
 import time
@@ -29,15 +27,15 @@ from . import aggregators as agg
 from . import attacks as atk
 from . import models
 from .config import Config
-from .data import HARData, ICUData, as_har, load_test, load_train, make_round_indices
+from .data import as_har, load_test, load_train, make_round_indices
 from .detection import EmbeddingMonitor
 from .layout import FlatLayout
-from .log import Logger, MetricsWriter, NullLogger, print_with_color
+from .log import MetricsWriter, NullLogger, print_with_color
 from .models.hyper import FusedHyperNet, HyperNetwork
 from .models.programs import SUPPORTED as NATIVE_MODELS, build_program
 from .parallel.ctx import ParallelContext, single
 from .utils.timers import PhaseTimer, Watchdog
-from .validation import Validator, roc_auc
+from .validation import Validator
 
 GRAM_MODES = ("Min-Max", "Min-Sum", "Opt-Fang")
 

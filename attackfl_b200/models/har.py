@@ -8,7 +8,6 @@ broken (``src/RpcClient.py:157-164`` falls into ``raise``); here it 
 """
 from __future__ import annotations
 
-import math
 
 import torch
 import torch.nn as nn

@@ -4,11 +4,11 @@ library, CPU tensors to the CPU twin built from the same sources."""
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional, Sequence, Tuple
+from typing import List, Optional, Sequence
 
 import torch
 
-from . import native
+
 from .native import check, lib_for, ptr, stream_ptr
 
 c_i, c_f, c_i64, c_u64, c_u32 = ctypes.c_int, ctypes.c_float, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint32

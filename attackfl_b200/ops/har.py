@@ -21,7 +21,7 @@ import torch
 
 from ..layout import FlatLayout
 from . import tc_linear as tc
-from .native import check, cuda_lib, ptr, stream_ptr
+from .native import check, cuda_lib, ptr
 
 c_i, c_f, c_i64, c_u64, c_u32 = ctypes.c_int, ctypes.c_float, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint32
 

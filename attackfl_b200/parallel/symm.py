@@ -12,7 +12,7 @@ handles), builds the pointer tables and installs ``fed.fused_comm``.
 from __future__ import annotations
 
 import ctypes
-from typing import Dict, List, Optional
+from typing import List, Optional
 
 import torch
 import torch.distributed as dist

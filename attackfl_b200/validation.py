@@ -11,7 +11,7 @@ up to fp rounding) so the scores never travel to the host; only the scalar does.
 """
 from __future__ import annotations
 
-from typing import Callable, Optional, Tuple
+from typing import Optional
 
 import torch
 
