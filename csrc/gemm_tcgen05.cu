@@ -361,17 +361,38 @@ dw_gemm_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
-// dW[i] (+)= sum_p partials[p][i] for i < n_w, db[i - n_w] (+)= ... for the n_b entries after them (fixed order:
-// deterministic)
-__global__ void reduce_partials_kernel(const float* __restrict__ partials, int n_parts, int64_t n_w, int n_b,
-                                       float* __restrict__ dw, float* __restrict__ db, int accumulate) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// dW[i] (+)= sum_p partials[p][i] for i < n_w, db[i - n_w] (+)= ... for the n_b entries after them.  A block owns 64
+// consecutive outputs; its four 64-thread groups each sum every fourth partial (8 independent loads in flight per thread)
+// and the groups are combined in a fixed order through shared memory: deterministic, and ~4x the memory parallelism of
+// one thread per output walking all partials.
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partials, int n_parts, int64_t n_w,
+                                                              int n_b, float* __restrict__ dw, float* __restrict__ db,
+                                                              int accumulate) {
+  __shared__ float part[4][64];
+  const int o = threadIdx.x & 63, g = threadIdx.x >> 6;
+  const int64_t i = (int64_t)blockIdx.x * 64 + o;
   const int64_t stride = n_w + n_b;
-  if (i >= stride || (i >= n_w && db == nullptr)) return;
   float acc = 0.f;
-  for (int p = 0; p < n_parts; ++p) acc += partials[(size_t)p * stride + i];
-  float* dst = i < n_w ? dw + i : db + (i - n_w);
-  *dst = accumulate ? *dst + acc : acc;
+  if (i < stride) {
+    const float* src = partials + i;
+    int p = g;
+#pragma unroll 1
+    for (; p + 28 < n_parts; p += 32) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = src[(size_t)(p + 4 * u) * stride];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += v[u];
+    }
+    for (; p < n_parts; p += 4) acc += src[(size_t)p * stride];
+  }
+  part[g][o] = acc;
+  __syncthreads();
+  if (g == 0 && i < stride && (i < n_w || db != nullptr)) {
+    const float sum = (part[0][o] + part[1][o]) + (part[2][o] + part[3][o]);
+    float* dst = i < n_w ? dw + i : db + (i - n_w);
+    *dst = accumulate ? *dst + sum : sum;
+  }
 }
 
 int check_dims(int N, int K, const char* what) {
@@ -473,7 +494,7 @@ int afl_tc_linear_dw(const float* dY, const float* X, int64_t M, int N, int K, f
   dw_gemm_kernel<<<grid, kThreads, smem, st>>>(ty, tx, P);
   afl_rt::count_launch();
   const int64_t n = (int64_t)N * K;
-  reduce_partials_kernel<<<(int)((n + N + 255) / 256), 256, 0, st>>>(partials, grid, n, N, dW, db, accumulate);
+  reduce_partials_kernel<<<(int)((n + N + 63) / 64), 256, 0, st>>>(partials, grid, n, N, dW, db, accumulate);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_tc_linear_dw");
 }

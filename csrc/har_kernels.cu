@@ -513,7 +513,7 @@ int afl_har_embed_fwd(const float* x, const float* conv_w, const float* conv_b, 
 }
 
 int afl_har_embed_bwd(const float* dh, const float* x, int B, int T, float* dconv_w, float* dconv_b, void* stream) {
-  embed_bwd_kernel<<<grid_rows((int64_t)B * T, 512, 2), 256, 0, (cudaStream_t)stream>>>(dh, x, B, T, dconv_w, dconv_b);
+  embed_bwd_kernel<<<grid_rows((int64_t)B * T, 64, 8), 256, 0, (cudaStream_t)stream>>>(dh, x, B, T, dconv_w, dconv_b);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_har_embed_bwd");
 }
