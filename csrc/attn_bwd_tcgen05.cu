@@ -12,7 +12,8 @@
 //               S^T = K Q^T, dPd^T = V dO^T (TMEM) -> Pd^T, dS^T -> smem -> dV += Pd^T dO, dK += dS^T Q (B MN-major)
 // P is recomputed from the forward's base-2 log-sum-exp; the dropout keep bits come from the mask words the forward
 // kernel stored (bit (key & 31) of word [key >> 5][query]), so no random numbers are regenerated here.
-// 320 threads per CTA: warp 0 TMA, warp 1 MMA issue, warps 2-9 element-wise (two warps per TMEM lane quarter).
+// 64 + 128 * kParts threads per CTA: warp 0 TMA, warp 1 MMA issue, the rest element-wise (kParts warps per TMEM lane
+// quarter, 64 / kParts columns of a streamed block each).
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <math.h>
@@ -28,7 +29,16 @@ namespace {
 using namespace afl_tc;
 using namespace afl_har;
 
-constexpr int kThreads = 320;
+// Element-wise warps per TMEM lane quarter: each owns 64 / kParts columns of a streamed block.  Measured (B200, batch 128,
+// dropout 0.1): 2 (8 warps, 320 threads) 468 us per layer, 4 (16 warps, 576 threads) 499 us — the per-block fixed costs of
+// a warp (TMEM load latency, proxy fence, barrier round trips) do not shrink with its column count, so more warps only
+// add arrivals; 2 is the default.
+#ifndef AFL_ATTN_PARTS
+#define AFL_ATTN_PARTS 2
+#endif
+constexpr int kParts = AFL_ATTN_PARTS;
+constexpr int kCW = 64 / kParts;                // columns per element-wise warp
+constexpr int kThreads = 64 + 128 * kParts;
 constexpr int kD = 64, kNH = 4, kDH = 16;
 constexpr int kTile = 128;                      // rows per CTA (queries or keys)
 constexpr int kBlk = 64;                        // streamed block (keys or queries)
@@ -121,7 +131,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
   if (warp == 0 && lane == 0) {
     mbar_init(qd_full, 1);
     for (int i = 0; i < kStages; ++i) { mbar_init(kv_full + i, 1); mbar_init(kv_empty + i, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(sd_full + i, 1); mbar_init(sd_empty + i, 8); mbar_init(ds_full + i, 8); mbar_init(ds_empty + i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(sd_full + i, 1); mbar_init(sd_empty + i, 4 * kParts); mbar_init(ds_full + i, 4 * kParts); mbar_init(ds_empty + i, 1); }
     mbar_init(dq_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -188,7 +198,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
       umma_commit(dq_full);
     }
   } else {
-    const int q = warp & 3, half = (warp - 2) >> 2;
+    const int q = warp & 3, part = (warp - 2) >> 2;
+    const int col0 = part * kCW;                            // this warp's columns of a 64-key block
     const int r = q * 32 + lane, qi = q0 + r;
     const bool live = qi < P.T;
     const int Tp = lse_stride(P.T);
@@ -198,22 +209,26 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
     const bool drop = P.drop_p > 0.f && P.mask != nullptr;
     const float inv_keep = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.f;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int wsel = col0 >> 5, wshift = col0 & 31;         // keep-mask word of the block's 2 and bit offset inside it
     uint32_t keep_next = 0xFFFFFFFFu;
-    if (drop && live) keep_next = P.mask[(bh * P.mask_words + (size_t)half) * Tp + qi];
+    if (drop && live) keep_next = P.mask[(bh * P.mask_words + (size_t)wsel) * Tp + qi];
     for (int kb = 0; kb < n_blk; ++kb) {
       const int buf = kb & 1;
-      const uint32_t keep = keep_next;                      // the next block's word is fetched one block ahead
-      if (drop && live && kb + 1 < n_blk) keep_next = P.mask[(bh * P.mask_words + (size_t)((kb + 1) * 2 + half)) * Tp + qi];
+      const uint32_t keep = keep_next >> wshift;            // the next block's word is fetched one block ahead
+      if (drop && live && kb + 1 < n_blk) keep_next = P.mask[(bh * P.mask_words + (size_t)((kb + 1) * 2 + wsel)) * Tp + qi];
       mbar_wait(sd_full + buf, ((uint32_t)kb >> 1) & 1u);
       tc_fence_after();
-      const int key0 = kb * kBlk + half * 32;
-      float ds[32], dd[32];                                   // scores -> dS in place; dPd
-      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 32), ds);
-      tmem_ld32_async(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(half * 32), dd);
-      tmem_ld_wait();
-      const bool full = key0 + 32 <= P.T;
+      const int key0 = kb * kBlk + col0;
+      float ds[kCW], dd[kCW];                                 // scores -> dS in place; dPd
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
+      for (int c = 0; c < kCW; c += 16) {
+        tmem_ld16_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(col0 + c), ds + c);
+        tmem_ld16_async(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(col0 + c), dd + c);
+      }
+      tmem_ld_wait();
+      const bool full = key0 + kCW <= P.T;
+#pragma unroll
+      for (int j = 0; j < kCW; ++j) {
         const float p = ex2_approx(fmaf(ds[j], kScaleLog2e, -L));
         const float kp = ((keep >> j) & 1u) ? inv_keep : 0.f;
         float v = p * fmaf(kp, dd[j], -delta);
@@ -225,15 +240,15 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tm_q128, const __grid_
       if (lane == 0) mbar_arrive(sd_empty + buf);
       mbar_wait(ds_empty + buf, (((uint32_t)kb >> 1) & 1u) ^ 1u);
       uint8_t* tile = ds_ptr + (size_t)buf * 2 * kTileBytes;
-      store16_sw128(tile, half, kTileBytes, r, 0, ds);
-      store16_sw128(tile, half, kTileBytes, r, 1, ds + 16);
+#pragma unroll
+      for (int c = 0; c < kCW; c += 16) store16_sw128(tile, (col0 + c) >> 5, kTileBytes, r, ((col0 + c) & 31) >> 4, ds + c);
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(ds_full + buf);
     }
     mbar_wait(dq_full, 0);
     tc_fence_after();
-    if (half == 0) {
+    if (part == 0) {
       float o[16];
       tmem_ld16(lane_addr + kDqCol + (uint32_t)(h & 1) * 16u, o);
       if (live) {
@@ -291,8 +306,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
   if (warp == 0 && lane == 0) {
     mbar_init(kv_full, 1);
     for (int i = 0; i < kStages; ++i) { mbar_init(q_full + i, 1); mbar_init(q_empty + i, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(sd_full + i, 1); mbar_init(sd_empty + i, 8); }
-    mbar_init(pd_full, 8); mbar_init(pd_empty, 1); mbar_init(acc_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(sd_full + i, 1); mbar_init(sd_empty + i, 4 * kParts); }
+    mbar_init(pd_full, 4 * kParts); mbar_init(pd_empty, 1); mbar_init(acc_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
@@ -370,7 +385,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       umma_commit(acc_full);
     }
   } else {
-    const int q = warp & 3, half = (warp - 2) >> 2;
+    const int q = warp & 3, part = (warp - 2) >> 2;
+    const int col0 = part * kCW;                            // this warp's columns (queries) of a 64-query block
     const int r = q * 32 + lane, kj = k0 + r;
     const bool live = kj < P.T;
     const float inv_keep = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.f;
@@ -381,17 +397,20 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       mbar_wait(sd_full + buf, ((uint32_t)ib >> 1) & 1u);
       tc_fence_after();
       const uint8_t* aux = aligned + (st_base - base) + (size_t)st * kStageBytes + 4 * kBlkBytes;
-      const float* lse_s = reinterpret_cast<const float*>(aux) + half * 32;
-      const float* del_s = reinterpret_cast<const float*>(aux + 256) + half * 32;
-      const uint32_t* msk_s = reinterpret_cast<const uint32_t*>(aux + 512) + q * 64 + half * 32;
-      const int i0 = ib * kBlk + half * 32;
-      float pd[32], ds[32];                                   // S^T -> Pd^T in place; dPd^T -> dS^T in place
-      tmem_ld32_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(half * 32), pd);
-      tmem_ld32_async(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(half * 32), ds);
-      tmem_ld_wait();
-      const bool full = i0 + 32 <= P.T;
+      const float* lse_s = reinterpret_cast<const float*>(aux) + col0;
+      const float* del_s = reinterpret_cast<const float*>(aux + 256) + col0;
+      const uint32_t* msk_s = reinterpret_cast<const uint32_t*>(aux + 512) + q * 64 + col0;
+      const int i0 = ib * kBlk + col0;
+      float pd[kCW], ds[kCW];                                 // S^T -> Pd^T in place; dPd^T -> dS^T in place
 #pragma unroll
-      for (int i4 = 0; i4 < 32; i4 += 4) {
+      for (int c = 0; c < kCW; c += 16) {
+        tmem_ld16_async(lane_addr + (uint32_t)buf * kBlk + (uint32_t)(col0 + c), pd + c);
+        tmem_ld16_async(lane_addr + 128u + (uint32_t)buf * kBlk + (uint32_t)(col0 + c), ds + c);
+      }
+      tmem_ld_wait();
+      const bool full = i0 + kCW <= P.T;
+#pragma unroll
+      for (int i4 = 0; i4 < kCW; i4 += 4) {
         const float4 L4 = *reinterpret_cast<const float4*>(lse_s + i4);
         const float4 D4 = *reinterpret_cast<const float4*>(del_s + i4);
         uint4 M4 = make_uint4(~0u, ~0u, ~0u, ~0u);
@@ -412,23 +431,26 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tm_k128, const __grid
       __syncwarp();
       if (lane == 0) mbar_arrive(sd_empty + buf);
       mbar_wait(pd_empty, ((uint32_t)ib & 1u) ^ 1u);
-      store16_sw128(pd_ptr, half, kTileBytes, r, 0, pd);
-      store16_sw128(pd_ptr, half, kTileBytes, r, 1, pd + 16);
-      store16_sw128(dst_ptr, half, kTileBytes, r, 0, ds);
-      store16_sw128(dst_ptr, half, kTileBytes, r, 1, ds + 16);
+#pragma unroll
+      for (int c = 0; c < kCW; c += 16) {
+        store16_sw128(pd_ptr, (col0 + c) >> 5, kTileBytes, r, ((col0 + c) & 31) >> 4, pd + c);
+        store16_sw128(dst_ptr, (col0 + c) >> 5, kTileBytes, r, ((col0 + c) & 31) >> 4, ds + c);
+      }
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(pd_full);
     }
     mbar_wait(acc_full, 0);
     tc_fence_after();
-    float o[16];
-    tmem_ld16(lane_addr + (half == 0 ? kDkCol : kDvCol) + (uint32_t)(h & 1) * 16u, o);
-    if (live) {
-      const float sc = half == 0 ? 0.25f : 1.0f;
-      float4* dst = reinterpret_cast<float4*>(P.dqkv + (size_t)(row0 + kj) * (3 * kD) + (half == 0 ? kD : 2 * kD) + h * kDH);
+    if (part < 2) {                                         // part 0 writes dK, part 1 writes dV
+      float o[16];
+      tmem_ld16(lane_addr + (part == 0 ? kDkCol : kDvCol) + (uint32_t)(h & 1) * 16u, o);
+      if (live) {
+        const float sc = part == 0 ? 0.25f : 1.0f;
+        float4* dst = reinterpret_cast<float4*>(P.dqkv + (size_t)(row0 + kj) * (3 * kD) + (part == 0 ? kD : 2 * kD) + h * kDH);
 #pragma unroll
-      for (int g = 0; g < 4; ++g) dst[g] = make_float4(o[4 * g] * sc, o[4 * g + 1] * sc, o[4 * g + 2] * sc, o[4 * g + 3] * sc);
+        for (int g = 0; g < 4; ++g) dst[g] = make_float4(o[4 * g] * sc, o[4 * g + 1] * sc, o[4 * g + 2] * sc, o[4 * g + 3] * sc);
+      }
     }
   }
   tc_fence_before();
