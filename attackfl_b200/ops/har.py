@@ -45,6 +45,7 @@ class HarNativeTrainer:
         mode = os.environ.get("ATTACKFL_HAR_ATTN", "tc")            # tc | tc-fwd (FFMA backward) | ffma
         self.attn_tc = bool(self.lib.afl_har_attn_tc_supported(c_i(seq_len))) and mode != "ffma"
         self.attn_bwd_tc = mode == "tc"
+        self.fuse_ln = os.environ.get("ATTACKFL_HAR_FUSE_LN", "1") != "0"      # LayerNorm in the GEMM epilogue
         m = max_batch * seq_len
         z = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.device)          # noqa: E731
         self.h0 = z(m, D_MODEL)
@@ -93,17 +94,29 @@ class HarNativeTrainer:
             else:
                 self._ck(lib.afl_har_attn_fwd(ptr(a["qkv"]), c_i(B), c_i(T), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
                                               c_u32(16 * l + SITE_ATTN), ptr(a["att"]), ptr(a["lse"]), st), "afl_har_attn_fwd")
-            tc.linear_fwd(a["att"][:M], w[pre + "self_attn.out_proj.weight"], w[pre + "self_attn.out_proj.bias"],
-                          out=a["sa"][:M])
-            self._ck(lib.afl_har_add_ln_fwd(ptr(h), ptr(a["sa"]), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
-                                            c_u32(16 * l + SITE_SA), ptr(w[pre + "norm1.weight"]), ptr(w[pre + "norm1.bias"]),
-                                            c_i64(M), ptr(a["h1"]), ptr(a["xhat1"]), ptr(a["rstd1"]), st), "afl_har_add_ln_fwd")
+            if self.fuse_ln:        # out_proj with residual + dropout + LayerNorm in its epilogue
+                tc.linear_ln_fwd(a["att"][:M], w[pre + "self_attn.out_proj.weight"], w[pre + "self_attn.out_proj.bias"],
+                                 h[:M], w[pre + "norm1.weight"], w[pre + "norm1.bias"], a["h1"][:M], a["xhat1"][:M],
+                                 a["rstd1"][:M], drop_p=p, seed=seed, rng=(client, step, 16 * l + SITE_SA))
+            else:
+                tc.linear_fwd(a["att"][:M], w[pre + "self_attn.out_proj.weight"], w[pre + "self_attn.out_proj.bias"],
+                              out=a["sa"][:M])
+                self._ck(lib.afl_har_add_ln_fwd(ptr(h), ptr(a["sa"]), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
+                                                c_u32(16 * l + SITE_SA), ptr(w[pre + "norm1.weight"]),
+                                                ptr(w[pre + "norm1.bias"]), c_i64(M), ptr(a["h1"]), ptr(a["xhat1"]),
+                                                ptr(a["rstd1"]), st), "afl_har_add_ln_fwd")
             tc.linear_fwd(a["h1"][:M], w[pre + "linear1.weight"], w[pre + "linear1.bias"], relu=True, drop_p=p, seed=seed,
                           rng=(rng[0], rng[1], 16 * l + SITE_FF), out=a["f1"][:M])
-            tc.linear_fwd(a["f1"][:M], w[pre + "linear2.weight"], w[pre + "linear2.bias"], out=a["f2"][:M])
-            self._ck(lib.afl_har_add_ln_fwd(ptr(a["h1"]), ptr(a["f2"]), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
-                                            c_u32(16 * l + SITE_OUT), ptr(w[pre + "norm2.weight"]), ptr(w[pre + "norm2.bias"]),
-                                            c_i64(M), ptr(a["h2"]), ptr(a["xhat2"]), ptr(a["rstd2"]), st), "afl_har_add_ln_fwd")
+            if self.fuse_ln:
+                tc.linear_ln_fwd(a["f1"][:M], w[pre + "linear2.weight"], w[pre + "linear2.bias"], a["h1"][:M],
+                                 w[pre + "norm2.weight"], w[pre + "norm2.bias"], a["h2"][:M], a["xhat2"][:M], a["rstd2"][:M],
+                                 drop_p=p, seed=seed, rng=(client, step, 16 * l + SITE_OUT))
+            else:
+                tc.linear_fwd(a["f1"][:M], w[pre + "linear2.weight"], w[pre + "linear2.bias"], out=a["f2"][:M])
+                self._ck(lib.afl_har_add_ln_fwd(ptr(a["h1"]), ptr(a["f2"]), c_f(p), c_u64(seed), c_u32(client), c_u32(step),
+                                                c_u32(16 * l + SITE_OUT), ptr(w[pre + "norm2.weight"]),
+                                                ptr(w[pre + "norm2.bias"]), c_i64(M), ptr(a["h2"]), ptr(a["xhat2"]),
+                                                ptr(a["rstd2"]), st), "afl_har_add_ln_fwd")
             h = a["h2"]
         self._ck(lib.afl_har_pool_fwd(ptr(h), c_i(B), c_i(T), ptr(self.pooled), st), "afl_har_pool_fwd")
 

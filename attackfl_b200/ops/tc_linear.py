@@ -35,6 +35,20 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = 
     return out
 
 
+def linear_ln_fwd(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, resid: torch.Tensor, gamma: torch.Tensor,
+                  beta: torch.Tensor, y: torch.Tensor, xhat: torch.Tensor, rstd: torch.Tensor, drop_p: float = 0.0,
+                  seed: int = 0, rng: Tuple[int, int, int] = (0, 0, 0)) -> torch.Tensor:
+    """``y = LayerNorm(resid + dropout(x @ w.T + bias)) * gamma + beta`` for ``w [64, K]`` in one kernel (the normalisation
+    runs in the GEMM epilogue); ``xhat``, ``rstd`` are saved for the backward pass."""
+    m, k = x.shape
+    lib = cuda_lib()
+    rc = lib.afl_tc_linear_ln_fwd(ptr(x), c_i64(m), c_i(k), ptr(w), ptr(bias), ptr(resid), c_f(drop_p), c_u64(seed),
+                                  c_u32(rng[0]), c_u32(rng[1]), c_u32(rng[2]), ptr(gamma), ptr(beta), ptr(y), ptr(xhat),
+                                  ptr(rstd), stream_ptr(x))
+    check(lib, rc, "afl_tc_linear_ln_fwd")
+    return y
+
+
 def linear_dx(dy: torch.Tensor, w: torch.Tensor, mask_src: Optional[torch.Tensor] = None, mask_scale: float = 1.0,
               out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
     """``(dy @ w) * (mask_src > 0 ? mask_scale : 0)`` for ``dy [M, N]``, ``w [N, K]``."""

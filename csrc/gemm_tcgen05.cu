@@ -49,11 +49,17 @@ struct RowGemmParams {
   const float* mask_src; // mode 1: out *= (mask_src[row][col] > 0 ? mask_scale : 0)
   float mask_scale;
   int accumulate;        // out += result
+  // mode 0, n_out == 64: fused residual + dropout + LayerNorm epilogue (out = LN(resid + dropout(acc + bias)))
+  int ln;
+  const float* resid;    // [M][64]
+  const float* gamma;    // [64]
+  const float* beta;     // [64]
+  float* rstd;           // [M]; xhat goes out through tmap_x
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
 row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                const __grid_constant__ CUtensorMap tmap_o, RowGemmParams P) {
+                const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_x, RowGemmParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* aligned = smem_raw + (base - smem_u32(smem_raw));
@@ -61,9 +67,9 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const uint32_t w_bytes = w_box_bytes * (uint32_t)P.w_kblocks;
   const uint32_t w_base = base;
   const uint32_t a_base = base + w_bytes;
-  const uint32_t o_base = a_base + (uint32_t)P.stages * kStageBytes;      // 2 output staging tiles [128 rows][32 cols]
+  const uint32_t o_base = a_base + (uint32_t)P.stages * kStageBytes;      // 2 (4 with LN) output staging tiles [128 rows][32 cols]
   uint8_t* o_ptr = aligned + (o_base - base);
-  uint64_t* full = reinterpret_cast<uint64_t*>(o_ptr + 2 * kStageBytes);
+  uint64_t* full = reinterpret_cast<uint64_t*>(o_ptr + (P.ln ? 4 : 2) * kStageBytes);
   uint64_t* empty = full + P.stages;
   uint64_t* w_full = empty + P.stages;
   uint64_t* acc_full = w_full + 1;             // [2]
@@ -144,6 +150,7 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int r = q * 32 + lane;                           // row of the tile = TMEM lane
     if (P.mode == 0 && P.bias)
       for (int i = et; i < P.n_out; i += 128) bias_s[i] = P.bias[i];
+    if (P.ln && et < 64) { bias_s[64 + et] = P.gamma[et]; bias_s[128 + et] = P.beta[et]; }
     asm volatile("bar.sync 1, 128;" ::: "memory");
     int t = 0, sc = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t) {
@@ -152,6 +159,68 @@ row_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       tc_fence_after();
       const int64_t row = tile * 128 + r;
       const bool live = row < P.M;
+      if (P.ln) {
+        // ---- fused epilogue: y = LayerNorm(resid + dropout(acc + bias)) * gamma + beta; the thread owns the whole row, so
+        // the statistics need no shuffles.  y and xhat leave through four staging tiles and TMA stores, rstd directly.
+        float v[64];
+        tmem_ld32_async(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols, v);
+        tmem_ld32_async(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols + 32u, v + 32);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty + buf);           // accumulator is in registers: the next tile's MMAs may start
+        const float inv = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.f;
+        float sum = 0.f;
+#pragma unroll
+        for (int g = 0; g < 16; ++g) {
+          float a[4] = {v[4 * g] + bias_s[4 * g], v[4 * g + 1] + bias_s[4 * g + 1], v[4 * g + 2] + bias_s[4 * g + 2],
+                        v[4 * g + 3] + bias_s[4 * g + 3]};
+          if (P.drop_p > 0.f) {
+            const AflU4 rr = afl_philox((uint32_t)g, (P.rng_id & 0xFFFFu) | (P.rng_client << 16), P.rng_step, (uint32_t)row,
+                                        P.seed_lo, P.seed_hi);
+            const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a[j] = ((float)(w[j] >> 8) * (1.0f / 16777216.0f) >= P.drop_p) ? a[j] * inv : 0.f;
+          }
+          float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (live) x4 = __ldg(reinterpret_cast<const float4*>(P.resid + row * 64) + g);
+          v[4 * g] = a[0] + x4.x; v[4 * g + 1] = a[1] + x4.y; v[4 * g + 2] = a[2] + x4.z; v[4 * g + 3] = a[3] + x4.w;
+          sum += (v[4 * g] + v[4 * g + 1]) + (v[4 * g + 2] + v[4 * g + 3]);
+        }
+        const float mean = sum * (1.0f / 64.0f);
+        float sq = 0.f;
+#pragma unroll
+        for (int j = 0; j < 64; ++j) { v[j] -= mean; sq = fmaf(v[j], v[j], sq); }
+        const float rs = rsqrtf(sq * (1.0f / 64.0f) + 1e-5f);
+        if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous tile's stores have read the tiles
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint8_t* yrow = o_ptr + (size_t)half * kStageBytes + (size_t)r * 128;
+          uint8_t* xrow = o_ptr + (size_t)(2 + half) * kStageBytes + (size_t)r * 128;
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const int c = 32 * half + 4 * g;
+            const float4 xh = make_float4(v[c] * rs, v[c + 1] * rs, v[c + 2] * rs, v[c + 3] * rs);
+            const float4 y = make_float4(fmaf(xh.x, bias_s[64 + c], bias_s[128 + c]), fmaf(xh.y, bias_s[65 + c], bias_s[129 + c]),
+                                         fmaf(xh.z, bias_s[66 + c], bias_s[130 + c]), fmaf(xh.w, bias_s[67 + c], bias_s[131 + c]));
+            *reinterpret_cast<float4*>(xrow + ((g ^ (r & 7)) << 4)) = xh;
+            *reinterpret_cast<float4*>(yrow + ((g ^ (r & 7)) << 4)) = y;
+          }
+        }
+        if (live) P.rstd[row] = rs;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                         ::"l"(reinterpret_cast<uint64_t>(k < 2 ? &tmap_o : &tmap_x)), "r"((k & 1) * 32), "r"((int)(tile * 128)),
+                           "r"(o_base + (uint32_t)k * kStageBytes) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        continue;
+      }
       for (int c0 = 0; c0 < P.n_out; c0 += 32, ++sc) {
         uint8_t* stage = o_ptr + (size_t)(sc & 1) * kStageBytes;
         if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that used this tile is done reading
@@ -404,7 +473,7 @@ int check_dims(int N, int K, const char* what) {
 }
 
 int launch_row_gemm(const float* A, int64_t M, int Kr, const float* W, int w_rows, int w_cols, int mode, RowGemmParams P,
-                    cudaStream_t st) {
+                    cudaStream_t st, float* xhat = nullptr) {
   CUtensorMap ta, tw, to;
   int rc = make_tmap_f32(&ta, A, Kr, M, Kr, 128);
   if (rc) return rc;
@@ -413,6 +482,11 @@ int launch_row_gemm(const float* A, int64_t M, int Kr, const float* W, int w_row
   const int n_out = mode == 0 ? w_rows : w_cols;
   rc = make_tmap_f32(&to, P.out, n_out, M, n_out, 128);
   if (rc) return rc;
+  CUtensorMap tx = to;
+  if (P.ln) {
+    rc = make_tmap_f32(&tx, xhat, 64, M, 64, 128);
+    if (rc) return rc;
+  }
   P.M = M;
   P.n_kblocks = Kr / 32;
   P.mode = mode;
@@ -420,7 +494,7 @@ int launch_row_gemm(const float* A, int64_t M, int Kr, const float* W, int w_row
   P.w_kblocks = w_cols / 32;
   P.n_out = mode == 0 ? w_rows : w_cols;
   const size_t w_bytes = (size_t)w_rows * w_cols * 4;
-  const size_t fixed = 1024 + 2 * (size_t)kStageBytes + 2048 + w_bytes;   // alignment, output staging, barriers + bias
+  const size_t fixed = 1024 + (P.ln ? 4 : 2) * (size_t)kStageBytes + 2048 + w_bytes;   // alignment, output staging, barriers + bias
   const size_t budget = (size_t)afl_rt::max_smem_optin() - fixed;
   int stages = (int)(budget / kStageBytes);
   if (stages > 8) stages = 8;
@@ -430,7 +504,7 @@ int launch_row_gemm(const float* A, int64_t M, int Kr, const float* W, int w_row
   AFL_CUDA(cudaFuncSetAttribute(row_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t n_tiles = (M + 127) / 128;
   const int grid = (int)(n_tiles < afl_rt::num_sms() ? n_tiles : afl_rt::num_sms());
-  row_gemm_kernel<<<grid, kThreads, smem, st>>>(ta, tw, to, P);
+  row_gemm_kernel<<<grid, kThreads, smem, st>>>(ta, tw, to, tx, P);
   afl_rt::count_launch();
   return afl_rt::check_last("row_gemm_kernel");
 }
@@ -449,6 +523,22 @@ int afl_tc_linear_fwd(const float* X, int64_t M, int K, const float* W, int N, c
   P.seed_lo = (uint32_t)seed; P.seed_hi = (uint32_t)(seed >> 32);
   P.rng_client = rng_client; P.rng_step = rng_step; P.rng_id = rng_id;
   return launch_row_gemm(X, M, K, W, N, K, 0, P, (cudaStream_t)stream);
+}
+
+int afl_tc_linear_ln_fwd(const float* X, int64_t M, int K, const float* W, const float* bias, const float* resid, float drop_p,
+                         uint64_t seed, uint32_t rng_client, uint32_t rng_step, uint32_t rng_id, const float* gamma,
+                         const float* beta, float* Y, float* xhat, float* rstd, void* stream) {
+  if (check_dims(64, K, "afl_tc_linear_ln_fwd")) return -1;
+  AFL_CHECK_ARG(M >= 1 && drop_p >= 0.f && drop_p < 1.f && bias && resid && gamma && beta,
+                "afl_tc_linear_ln_fwd: M >= 1, 0 <= p < 1, bias / resid / gamma / beta required");
+  AFL_CHECK_ARG(((uintptr_t)X | (uintptr_t)W | (uintptr_t)Y | (uintptr_t)xhat | (uintptr_t)resid) % 16 == 0,
+                "afl_tc_linear_ln_fwd: pointers must be 16-byte aligned");
+  RowGemmParams P{};
+  P.out = Y; P.bias = bias; P.drop_p = drop_p;
+  P.seed_lo = (uint32_t)seed; P.seed_hi = (uint32_t)(seed >> 32);
+  P.rng_client = rng_client; P.rng_step = rng_step; P.rng_id = rng_id;
+  P.ln = 1; P.resid = resid; P.gamma = gamma; P.beta = beta; P.rstd = rstd;
+  return launch_row_gemm(X, M, K, W, 64, K, 0, P, (cudaStream_t)stream, xhat);
 }
 
 int afl_tc_linear_dx(const float* dY, int64_t M, int N, const float* W, int K, const float* mask_src, float mask_scale,

@@ -88,6 +88,11 @@ int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mo
  *         afl_tc_linear_dw_workspace floats. */
 int afl_tc_linear_fwd(const float* X, int64_t M, int K, const float* W, int N, const float* bias, int relu, float drop_p,
                       uint64_t seed, uint32_t rng_client, uint32_t rng_step, uint32_t rng_id, float* Y, void* stream);
+/* fwd with the residual + dropout + LayerNorm fused into the epilogue (N = 64): Y = LN(resid + dropout(X W^T + bias)) * gamma
+ * + beta, xhat [M,64] and rstd [M] saved for afl_har_ln_bwd; same dropout stream as afl_har_add_ln_fwd. */
+int afl_tc_linear_ln_fwd(const float* X, int64_t M, int K, const float* W, const float* bias, const float* resid, float drop_p,
+                         uint64_t seed, uint32_t rng_client, uint32_t rng_step, uint32_t rng_id, const float* gamma,
+                         const float* beta, float* Y, float* xhat, float* rstd, void* stream);
 int afl_tc_linear_dx(const float* dY, int64_t M, int N, const float* W, int K, const float* mask_src, float mask_scale,
                      int accumulate, float* dX, void* stream);
 int afl_tc_linear_dw_workspace(int N, int K, int64_t* partial_floats);

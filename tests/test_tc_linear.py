@@ -75,3 +75,29 @@ def test_autograd_function_matches_linear():
     _close(xs[0].grad, g @ w)
     _close(xs[1].grad, g.t() @ x)
     _close(xs[2].grad, g.sum(0), tol=1e-4)
+
+
+@pytest.mark.parametrize("k,p", [(64, 0.0), (64, 0.2), (256, 0.1)])
+@pytest.mark.parametrize("m", [128, 777])
+def test_linear_layernorm_fused_epilogue(m, k, p):
+    """GEMM + bias + dropout + residual + LayerNorm in one kernel against the unfused kernels (same Philox stream) and,
+    without dropout, against torch."""
+    import ctypes
+    from attackfl_b200.ops import tc_linear as tc
+    from attackfl_b200.ops.native import check, cuda_lib, ptr
+    x, w, b, _ = _mk(m, 64, k, seed=7)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    resid, gamma, beta = (torch.randn(s, device="cuda", generator=g) for s in ((m, 64), (64,), (64,)))
+    y, xh, rs = torch.empty(m, 64, device="cuda"), torch.empty(m, 64, device="cuda"), torch.empty(m, device="cuda")
+    tc.linear_ln_fwd(x, w, b, resid, gamma, beta, y, xh, rs, drop_p=p, seed=5, rng=(2, 9, 18))
+    lib = cuda_lib()
+    lin = tc.linear_fwd(x, w, b)
+    y2, xh2, rs2 = torch.empty_like(y), torch.empty_like(xh), torch.empty_like(rs)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    check(lib, lib.afl_har_add_ln_fwd(ptr(resid), ptr(lin), ctypes.c_float(p), ctypes.c_uint64(5), 2, 9, 18, ptr(gamma), ptr(beta),
+                                      ctypes.c_int64(m), ptr(y2), ptr(xh2), ptr(rs2), st))
+    assert torch.allclose(y, y2, atol=2e-5, rtol=1e-5) and torch.allclose(xh, xh2, atol=2e-5, rtol=1e-5)
+    assert torch.allclose(rs, rs2, rtol=1e-5)
+    if p == 0.0:
+        want = torch.nn.functional.layer_norm(resid + x @ w.t() + b, (64,), gamma, beta)
+        _close(y, want)
