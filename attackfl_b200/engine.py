@@ -107,9 +107,8 @@ class Federation:
         if (self.data_name == "HAR" and self.model_name == "TransformerClassifier" and self.device.type == "cuda"
                 and cfg.runtime.backend in ("auto", "native")):
             from .ops.har import HarNativeTrainer
-            self.har_trainer = HarNativeTrainer(self.layout, self.device, max_batch=min(max(cfg.learning.batch_size, 1), 128))
-            if cfg.learning.batch_size > 128:
-                self.har_trainer = None                           # buffers are sized for the reference's batch (<= 128)
+            if cfg.learning.batch_size <= 512:                   # activation buffers: ~4 MB per sample of the batch
+                self.har_trainer = HarNativeTrainer(self.layout, self.device, max_batch=max(cfg.learning.batch_size, 1))
         if backend == "native":
             from .ops import train as T
             self.T = T

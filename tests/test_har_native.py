@@ -264,3 +264,21 @@ def test_partial_batch_and_dropout_masks_reach_backward():
     fd = (loss_at(row + eps * d) - loss_at(row - eps * d)) / (2 * eps)
     an = float((g0 * d).sum())
     assert abs(fd - an) < 5e-2 * max(1.0, abs(an)), (fd, an, base)
+
+
+def test_grad_step_batch_above_128():
+    """Batches larger than the reference's 128 (the engine allows up to 512 on the native path).  With many samples a few
+    head pre-activations land within TF32 noise of 0 and their ReLU derivative flips against the fp32 oracle (measured:
+    4 of 8,192 at B = 128, which alone moves dpooled by 9 % in max-norm), so the check is on the loss and on the
+    direction / size of the whole gradient; the per-tensor 2 % bound is tested at small batches above."""
+    mod, lay, row, tr, x, y = _setup(B=130, seed=9)
+    loss = torch.nn.functional.cross_entropy(mod(x[:, None, :]), y)
+    loss.backward()
+    grad = torch.zeros_like(row)
+    tr.out3.zero_()
+    tr.grad_step(row, grad, x, y, dropout=False)
+    assert abs(tr.out3[0].item() / 130 - loss.item()) < 2e-3 * max(1.0, abs(loss.item()))
+    want = lay.flatten({k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in
+                        list(mod.named_parameters()) + [("pe.pe", mod.pe.pe)]}, device="cuda")
+    cos = torch.nn.functional.cosine_similarity(grad, want, dim=0).item()
+    assert cos > 0.995 and abs(grad.norm().item() / want.norm().item() - 1) < 0.05, cos

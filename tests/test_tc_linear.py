@@ -23,7 +23,7 @@ def _mk(m, n, k, seed=0):
 
 
 @pytest.mark.parametrize("n,k", SHAPES)
-@pytest.mark.parametrize("m", [128, 1000, 5 * 561])
+@pytest.mark.parametrize("m", [128, 1000, 5 * 561, 300 * 128 + 37])   # last: more tiles than SMs (multi-tile CTAs)
 def test_linear_fwd(m, n, k):
     from attackfl_b200.ops import tc_linear as tc
     x, w, b, _ = _mk(m, n, k)
@@ -32,7 +32,7 @@ def test_linear_fwd(m, n, k):
 
 
 @pytest.mark.parametrize("n,k", SHAPES)
-@pytest.mark.parametrize("m", [128, 1000, 5 * 561])
+@pytest.mark.parametrize("m", [128, 1000, 5 * 561, 300 * 128 + 37])   # last: more tiles than SMs (multi-tile CTAs)
 def test_linear_dx_dw(m, n, k):
     from attackfl_b200.ops import tc_linear as tc
     x, w, b, dy = _mk(m, n, k, seed=1)
@@ -78,7 +78,7 @@ def test_autograd_function_matches_linear():
 
 
 @pytest.mark.parametrize("k,p", [(64, 0.0), (64, 0.2), (256, 0.1)])
-@pytest.mark.parametrize("m", [128, 777])
+@pytest.mark.parametrize("m", [128, 777, 300 * 128 + 37])
 def test_linear_layernorm_fused_epilogue(m, k, p):
     """GEMM + bias + dropout + residual + LayerNorm in one kernel against the unfused kernels (same Philox stream) and,
     without dropout, against torch."""
