@@ -33,11 +33,29 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 GXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-fno-fast-math"]
 
 
-def _newer(target: str, sources: List[str]) -> bool:
-    if not os.path.exists(target):
+def _digest(sources: List[str], flags: List[str]) -> str:
+    """Content hash of the sources and flags: the staleness test does not depend on file times (a snapshot copied to
+    another machine keeps contents, not necessarily mtimes)."""
+    import hashlib
+    h = hashlib.sha1(" ".join(flags).encode())
+    for s in sorted(sources):
+        h.update(os.path.basename(s).encode())
+        with open(s, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
+def _stamp_ok(target: str, digest: str) -> bool:
+    try:
+        with open(target + ".sha1") as fh:
+            return os.path.exists(target) and fh.read().strip() == digest
+    except OSError:
         return False
-    t = os.path.getmtime(target)
-    return all(os.path.getmtime(s) <= t for s in sources)
+
+
+def _write_stamp(target: str, digest: str) -> None:
+    with open(target + ".sha1", "w") as fh:
+        fh.write(digest)
 
 
 def _sources():
@@ -57,27 +75,35 @@ def nvcc_path() -> Optional[str]:
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
     """Compiles every ``csrc/*.cu`` for sm_100a into one shared object (cross-compiles without a GPU)."""
     cu, hdr = _sources()
-    if not force and _newer(CUDA_LIB, cu + hdr):
+    digest = _digest(cu + hdr, NVCC_FLAGS)
+    if not force and _stamp_ok(CUDA_LIB, digest):
         return CUDA_LIB
     nvcc = nvcc_path()
     if nvcc is None:
         raise RuntimeError("nvcc not found; cannot build the sm_100a library")
     os.makedirs(LIBDIR, exist_ok=True)
-    objs = []
+    objs = [os.path.join(LIBDIR, os.path.basename(src) + ".o") for src in cu]
     logs = []
-    for src in cu:
-        obj = os.path.join(LIBDIR, os.path.basename(src) + ".o")
-        if force or not _newer(obj, [src] + hdr):
-            cmd = [nvcc] + NVCC_FLAGS + ["-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
-            r = subprocess.run(cmd, capture_output=True, text=True)
-            logs.append(f"$ {' '.join(cmd)}\n{r.stdout}{r.stderr}")
-            if r.returncode != 0:
-                raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
-        objs.append(obj)
+
+    def compile_one(src: str, obj: str) -> str:
+        obj_digest = _digest([src] + hdr, NVCC_FLAGS)
+        if not force and _stamp_ok(obj, obj_digest):
+            return ""
+        cmd = [nvcc] + NVCC_FLAGS + ["-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+        _write_stamp(obj, obj_digest)
+        return f"$ {' '.join(cmd)}\n{r.stdout}{r.stderr}"
+
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as pool:      # one nvcc process per translation unit
+        logs = [l for l in pool.map(compile_one, cu, objs) if l]
     cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC", "-o", CUDA_LIB] + objs
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    _write_stamp(CUDA_LIB, digest)
     with open(os.path.join(LIBDIR, "build_cuda.log"), "w") as fh:
         fh.write("\n".join(logs))
     if verbose:
@@ -88,13 +114,15 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
 def build_cpu(force: bool = False) -> str:
     src = os.path.join(CSRC, "cpu_backend.cpp")
     _, hdr = _sources()
-    if not force and _newer(CPU_LIB, [src] + hdr):
+    digest = _digest([src] + hdr, GXX_FLAGS)
+    if not force and _stamp_ok(CPU_LIB, digest):
         return CPU_LIB
     os.makedirs(LIBDIR, exist_ok=True)
     cmd = ["g++"] + GXX_FLAGS + ["-I", os.path.join(ROOT, "include"), src, "-o", CPU_LIB]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"g++ failed:\n{r.stdout}\n{r.stderr}")
+    _write_stamp(CPU_LIB, digest)
     return CPU_LIB
 
 
@@ -118,8 +146,8 @@ def cpu_lib() -> ctypes.CDLL:
 def cuda_lib() -> ctypes.CDLL:
     global _cuda
     if _cuda is None:
-        if not os.path.exists(CUDA_LIB) or os.environ.get("ATTACKFL_REBUILD"):
-            build_cuda()
+        # always ask the builder: it is a no-op when the content stamp matches, and a stale binary can never be loaded
+        build_cuda(force=bool(os.environ.get("ATTACKFL_REBUILD")))
         _cuda = _declare(ctypes.CDLL(CUDA_LIB))
     return _cuda
 
