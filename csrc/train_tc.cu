@@ -38,9 +38,12 @@ constexpr int kSlotB = 16384;             // one [128 x 32] fp32 block
 constexpr int kSlotF = 4096;
 constexpr int kNSlot = 48;                // stash slots per client
 
-// ---- stash slots (per client); per-branch base = 19 * s
-enum { SL_X = 0, SL_GP1 = 1, SL_H1 = 3, SL_VD = 5, SL_XH1 = 7, SL_N1 = 9, SL_GPF = 11, SL_GF = 12, SL_XH2 = 13, SL_XH3 = 15,
-       SL_RES = 17, SL_BR = 19, SL_CAT = 38, SL_GPA = 42, SL_HD = 44, SL_H2 = 46 };
+// ---- stash slots (per client); per-branch base = 8 * s
+// Row-major [128 x 32] blocks that TMA reads back as MN-major MMA operands of the dW GEMMs:
+enum { SL_X = 0, SL_H1 = 1, SL_VD = 3, SL_N1 = 5, SL_GF = 7, SL_BR = 8, SL_CAT = 16, SL_HD = 20, SL_H2 = 22 };
+// Tensors that only the thread that wrote them reads back (activation derivatives, normalised rows, residual gradients):
+// stored lane-interleaved, [warp][128-bit chunk][lane], so every warp access is 512 contiguous bytes.
+enum { EL_GP1 = 24, EL_XH1 = 28, EL_XH2 = 32, EL_XH3 = 36, EL_RES = 40, EL_GPA = 44, EL_GPF = 46 };
 
 // ---- small parameters / their gradients mirrored in shared memory; per-branch base = 656 * s
 enum { SP_BD = 0, SP_BV = 64, SP_BO = 128, SP_G1 = 192, SP_BE1 = 256, SP_BF0 = 320, SP_BF3 = 336, SP_G2 = 400, SP_BE2 = 464,
@@ -77,6 +80,7 @@ struct TcParams {
   uint32_t seed_lo, seed_hi; int dropout; float p1, p3;
   int n_ranges; int range_lo[16], range_hi[16];
   float* loss_out; int32_t* steps_out;
+  long long* dbg;        // optional [64] clock64 stamps of thread 0 of client 0 at step 5 (profiling aid), or null
 };
 
 struct TcMaps { CUtensorMap m[TM_N]; };
@@ -152,28 +156,55 @@ __device__ __forceinline__ void mbar_wait_to(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void bar_named(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-// ---- MMA job shapes (issued by one thread) --------------------------------------------------------------------------
-// forward / dX: D[128 x N] = A(tmem, K columns) . B
-__device__ __forceinline__ void job_ksw(uint32_t d, uint32_t a, uint32_t b_addr, int N, int K, uint32_t box_bytes) {
-  const uint32_t idesc = idesc_tf32(128, N, 0, 0);
-  for (int ks = 0; ks < K / 8; ++ks)
-    umma_tf32_ts(d, a + ks * 8, desc_add(desc_k_sw128(b_addr + (uint32_t)(ks >> 2) * box_bytes), (uint32_t)(ks & 3) * 32u), idesc, ks > 0);
+// One lane of a converged warp.  ptxas recognises elect.sync, so a tcgen05 / TMA instruction guarded by it is issued once
+// with uniform-register operands; guarded by `lane == 0` instead, every such instruction is wrapped in a
+// vote-and-branch loop (ELECT ... BRA.U.ANY in SASS) with per-operand R2UR moves.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t p;
+  asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(p));
+  return p != 0;
 }
-__device__ __forceinline__ void job_knosw(uint32_t d, uint32_t a, uint32_t b_addr, int N, int K) {
+
+// ---- MMA job shapes (issued by one elected lane of the converged producer warp) --------------------------------------------------------------------------
+// forward / dX: D[128 x N] = A(tmem, K columns) . B.  Shapes are template parameters so that the issue loops unroll to one
+// add per operand: the issuing thread is a serial resource on the critical path of every phase.
+template <int N, int K>
+__device__ __forceinline__ void job_ksw(uint32_t d, uint32_t a, uint32_t b_addr, uint32_t box_bytes) {
+  const uint32_t idesc = idesc_tf32(128, N, 0, 0);
+  const uint64_t bd = desc_k_sw128(b_addr);
+  if (elect_one()) {
+#pragma unroll
+    for (int ks = 0; ks < K / 8; ++ks)
+      umma_tf32_ts(d, a + ks * 8, desc_add(bd, (uint32_t)(ks >> 2) * box_bytes + (uint32_t)(ks & 3) * 32u), idesc, ks > 0);
+  }
+}
+template <int N, int K>
+__device__ __forceinline__ void job_knosw(uint32_t d, uint32_t a, uint32_t b_addr) {
   const uint32_t idesc = idesc_tf32(128, N, 0, 0);
   const uint64_t bd = desc_nosw(b_addr, 128, (uint32_t)(K / 4) * 128u);
-  for (int ks = 0; ks < K / 8; ++ks) umma_tf32_ts(d, a + ks * 8, desc_add(bd, (uint32_t)ks * 256u), idesc, ks > 0);
+  if (elect_one()) {
+#pragma unroll
+    for (int ks = 0; ks < K / 8; ++ks) umma_tf32_ts(d, a + ks * 8, desc_add(bd, (uint32_t)ks * 256u), idesc, ks > 0);
+  }
 }
-__device__ __forceinline__ void job_mn(uint32_t d, uint32_t a, uint32_t b_addr, int N, int K, uint32_t lbo) {
+template <int N, int K>
+__device__ __forceinline__ void job_mn(uint32_t d, uint32_t a, uint32_t b_addr, uint32_t lbo) {
   const uint32_t idesc = idesc_tf32(128, N, 0, 1);
   const uint64_t bd = desc_mn_sw128(b_addr, lbo);
-  for (int ks = 0; ks < K / 8; ++ks) umma_tf32_ts(d, a + ks * 8, desc_add(bd, (uint32_t)ks * 1024u), idesc, ks > 0);
+  if (elect_one()) {
+#pragma unroll
+    for (int ks = 0; ks < K / 8; ++ks) umma_tf32_ts(d, a + ks * 8, desc_add(bd, (uint32_t)ks * 1024u), idesc, ks > 0);
+  }
 }
 // dW: D[64 x N] = dY^T (smem MN-major, two 32-wide blocks 16 KB apart) . X (smem MN-major), K = 128 samples
-__device__ __forceinline__ void job_dw(uint32_t d, uint32_t a_addr, uint32_t b_addr, int N, uint32_t b_lbo) {
+template <int N>
+__device__ __forceinline__ void job_dw(uint32_t d, uint32_t a_addr, uint32_t b_addr, uint32_t b_lbo) {
   const uint32_t idesc = idesc_tf32(64, N, 1, 1);
   const uint64_t ad = desc_mn_sw128(a_addr, kSlotB), bd = desc_mn_sw128(b_addr, b_lbo);
-  for (int ks = 0; ks < 16; ++ks) umma_tf32(d, desc_add(ad, (uint32_t)ks * 1024u), desc_add(bd, (uint32_t)ks * 1024u), idesc, ks > 0);
+  if (elect_one()) {
+#pragma unroll
+    for (int ks = 0; ks < 16; ++ks) umma_tf32(d, desc_add(ad, (uint32_t)ks * 1024u), desc_add(bd, (uint32_t)ks * 1024u), idesc, ks > 0);
+  }
 }
 
 // Column sums over the 32 rows of a warp for 16 columns per lane: 16 shuffles, then one shared atomic per column pair.
@@ -196,6 +227,19 @@ __device__ __forceinline__ float warp_sum(float x) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
   return x;
+}
+
+// gelu(z) and gelu'(z) from one exponential: erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7), whose exp(-x^2) with
+// x = |z| / sqrt(2) is the Gaussian factor of the derivative as well.
+__device__ __forceinline__ void gelu_both(float z, float& g, float& gp) {
+  const float az = fabsf(z);
+  const float e = __expf(-0.5f * z * z);
+  const float t = __frcp_rn(1.0f + 0.3275911f * 0.70710678118654752440f * az);
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float erf_abs = 1.0f - poly * e;
+  const float cdf = 0.5f * (1.0f + copysignf(erf_abs, z));
+  g = z * cdf;
+  gp = cdf + z * e * 0.39894228040143267794f;
 }
 
 struct Rng { uint32_t seed_lo, seed_hi, client, step; int on; };
@@ -243,6 +287,84 @@ __device__ __forceinline__ void st_dymn(uint8_t* buf, int row, int col0, const f
   }
 }
 
+// ---- coalesced stash access ------------------------------------------------------------------------------------------
+// A thread owns one sample row, i.e. 128 contiguous bytes of a [128 x 32] stash block, so a plain 128-bit access by the 32
+// lanes of a warp touches 32 different lines (32 L1 transactions for 512 bytes).  An 8 x 8 transpose of float4 chunks
+// inside each group of 8 lanes (3 butterfly stages) turns "lane = row" into "lane = chunk": every 128-bit instruction then
+// covers 4 whole lines.  The transpose is its own inverse, so loads use it after the access and stores before it.
+__device__ __forceinline__ void transpose8(float4* v, int lane) {
+#pragma unroll
+  for (int b = 4; b >= 1; b >>= 1) {
+    const bool up = lane & b;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c & b) continue;
+      float4 send = up ? v[c] : v[c ^ b];
+      float4 recv;
+      recv.x = __shfl_xor_sync(0xffffffffu, send.x, b);
+      recv.y = __shfl_xor_sync(0xffffffffu, send.y, b);
+      recv.z = __shfl_xor_sync(0xffffffffu, send.z, b);
+      recv.w = __shfl_xor_sync(0xffffffffu, send.w, b);
+      if (up) v[c] = recv; else v[c ^ b] = recv;
+    }
+  }
+}
+// 32 floats of this thread's row <-> one [128 x 32] stash block (blk: first float of the block, row0: first row of the warp)
+__device__ __forceinline__ void st32t(float* blk, int row0, int lane, const float* x) {
+  float4 v[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) v[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+  transpose8(v, lane);
+  float4* dst = reinterpret_cast<float4*>(blk + (row0 + (lane & ~7)) * 32) + (lane & 7);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) __stcg(dst + k * 8, v[k]);
+}
+__device__ __forceinline__ void ld32t(const float* blk, int row0, int lane, float* x) {
+  float4 v[8];
+  const float4* src = reinterpret_cast<const float4*>(blk + (row0 + (lane & ~7)) * 32) + (lane & 7);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = __ldcg(src + k * 8);
+  transpose8(v, lane);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) { x[4 * c] = v[c].x; x[4 * c + 1] = v[c].y; x[4 * c + 2] = v[c].z; x[4 * c + 3] = v[c].w; }
+}
+// 16-float variant (head phases: 16 columns per thread): 4 x 4 transpose inside groups of 4 lanes, 64-byte runs
+__device__ __forceinline__ void transpose4(float4* v, int lane) {
+#pragma unroll
+  for (int b = 2; b >= 1; b >>= 1) {
+    const bool up = lane & b;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      if (c & b) continue;
+      float4 send = up ? v[c] : v[c ^ b];
+      float4 recv;
+      recv.x = __shfl_xor_sync(0xffffffffu, send.x, b);
+      recv.y = __shfl_xor_sync(0xffffffffu, send.y, b);
+      recv.z = __shfl_xor_sync(0xffffffffu, send.z, b);
+      recv.w = __shfl_xor_sync(0xffffffffu, send.w, b);
+      if (up) v[c] = recv; else v[c ^ b] = recv;
+    }
+  }
+}
+__device__ __forceinline__ void st16t(float* blk, int row0, int lane, int colf, const float* x) {
+  float4 v[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) v[c] = make_float4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+  transpose4(v, lane);
+  float4* dst = reinterpret_cast<float4*>(blk + (row0 + (lane & ~3)) * 32 + colf) + (lane & 3);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) __stcg(dst + k * 8, v[k]);
+}
+__device__ __forceinline__ void ld16t(const float* blk, int row0, int lane, int colf, float* x) {
+  float4 v[4];
+  const float4* src = reinterpret_cast<const float4*>(blk + (row0 + (lane & ~3)) * 32 + colf) + (lane & 3);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v[k] = __ldcg(src + k * 8);
+  transpose4(v, lane);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) { x[4 * c] = v[c].x; x[4 * c + 1] = v[c].y; x[4 * c + 2] = v[c].z; x[4 * c + 3] = v[c].w; }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -272,8 +394,8 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
   __syncthreads();
   if (tid == 0) {
     for (int b = 0; b < B_N; ++b) {
-      const bool many = b == B_STEP || (b >= B_A && b < B_A + 3);
-      mbar_init(&bars[b], many ? 16u : 1u);
+      const uint32_t cnt = (b == B_STEP || b == B_A + 2) ? 16u : (b == B_A || b == B_A + 1) ? 8u : 1u;
+      mbar_init(&bars[b], cnt);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -286,21 +408,25 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
   const int n = P.n_data[c];
   const int steps_per_epoch = (n + P.batch - 1) / P.batch;
 
-  if (warp == kEpi / 32) {
+  if (warp == 0) {
     // =================================================================================== producer warp
-    if (lane == 0) {
+    // (warp 0: the oldest warp of its scheduler, so the serial TMA / MMA issue stream is not starved by the math warps)
+    {
       uint32_t ph = 0;                          // parity toggles of the barriers this thread waits on every phase
       uint32_t n_acc[3] = {0, 0, 0}, n_dw[3] = {0, 0, 0};
       auto wait = [&](int b) { mbar_wait_to(&bars[b], (ph >> b) & 1u); ph ^= 1u << b; };
       auto wait_a = [&](int s) { wait(B_A + s); tc_fence_after(); };
-      auto commit_acc = [&](int s) { umma_commit(&bars[B_ACC + s]); ++n_acc[s]; };
-      auto commit_dw = [&](int s) { umma_commit(&bars[B_DW + s]); ++n_dw[s]; };
+      auto commit_acc = [&](int s) { if (elect_one()) umma_commit(&bars[B_ACC + s]); ++n_acc[s]; };
+      auto commit_dw = [&](int s) { if (elect_one()) umma_commit(&bars[B_DW + s]); ++n_dw[s]; };
       auto wait_acc_last = [&](int s) { mbar_wait_to(&bars[B_ACC + s], (n_acc[s] - 1) & 1u); };
       auto wait_dw_last = [&](int s) { mbar_wait_to(&bars[B_DW + s], (n_dw[s] - 1) & 1u); };
-      auto tma = [&](int map, uint32_t dst, int c0, int c1, int bar) { tma_load_3d(dst, &maps.m[map], c0, c1, c, &bars[bar]); };
+      auto tma = [&](int map, uint32_t dst, int c0, int c1, int bar) { if (elect_one()) tma_load_3d(dst, &maps.m[map], c0, c1, c, &bars[bar]); };
+      auto expect = [&](int bar, uint32_t bytes) { if (elect_one()) mbar_expect_tx(&bars[bar], bytes); };
       auto stash_ld = [&](int slot, int nslots, uint32_t dst, int bar) {
-        mbar_expect_tx(&bars[bar], (uint32_t)nslots * kSlotB);
-        for (int j = 0; j < nslots; ++j) tma_load_3d(dst + j * kSlotB, &maps.m[TM_STASH], 0, 0, c * kNSlot + slot + j, &bars[bar]);
+        if (elect_one()) {
+          mbar_expect_tx(&bars[bar], (uint32_t)nslots * kSlotB);
+          for (int j = 0; j < nslots; ++j) tma_load_3d(dst + j * kSlotB, &maps.m[TM_STASH], 0, 0, c * kNSlot + slot + j, &bars[bar]);
+        }
       };
       const uint32_t wb[2][2] = {{sbase + kOffW, sbase + kOffW + kSlotB}, {sbase + kOffW + 2 * kSlotB, sbase + kOffW + 3 * kSlotB}};
       const uint32_t xb[2] = {sbase + kOffX, sbase + kOffX + 2 * kSlotB};
@@ -319,130 +445,135 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
           // ---- forward weights (all buffers are free: the step barrier follows the last drain + optimiser step)
           wait(B_STEP);
           for (int s = 0; s < 2; ++s) {
-            mbar_expect_tx(&bars[B_WF_V + s], 16384);
+            expect(B_WF_V + s, 16384);
             tma(TM_WV_K + s, wb[s][0], 0, 0, B_WF_V + s);
             tma(TM_WV_K + s, wb[s][0] + 8192, 32, 0, B_WF_V + s);
-            mbar_expect_tx(&bars[B_WF_O + s], 16384);
+            expect(B_WF_O + s, 16384);
             tma(TM_WO_K + s, wb[s][1], 0, 0, B_WF_O + s);
             tma(TM_WO_K + s, wb[s][1] + 8192, 32, 0, B_WF_O + s);
           }
-          mbar_expect_tx(&bars[B_WF_W2], 2 * 4096 + 4 * 2048);
+          expect(B_WF_W2, 2 * 4096 + 4 * 2048);
           for (int kb = 0; kb < 2; ++kb) tma(TM_W2_K, w2f + kb * 4096, kb * 32, 0, B_WF_W2);
           for (int s = 0; s < 2; ++s)
             for (int kb = 0; kb < 2; ++kb) tma(TM_WF0_K + s, wf0f[s] + kb * 2048, kb * 32, 0, B_WF_W2);
-          mbar_expect_tx(&bars[B_WF_W1], 32768);
+          expect(B_WF_W1, 32768);
           for (int kb = 0; kb < 4; ++kb) tma(TM_W1_K, xb[0] + kb * 8192, kb * 32, 0, B_WF_W1);
 
           // ---- forward
           for (int s = 0; s < 2; ++s) {   // P1: dense
             wait_a(s);
-            job_knosw(accc[s], acol[s], smw + (s ? kSmWd1 : kSmWd0), 64, s ? 16 : 8);
+            if (s) job_knosw<64, 16>(accc[s], acol[s], smw + kSmWd1); else job_knosw<64, 8>(accc[s], acol[s], smw + kSmWd0);
             commit_acc(s);
           }
           for (int s = 0; s < 2; ++s) {   // P2: V projection
             wait_a(s);
             wait(B_WF_V + s);
-            job_ksw(accc[s], acol[s], wb[s][0], 64, 64, 8192);
+            job_ksw<64, 64>(accc[s], acol[s], wb[s][0], 8192);
             commit_acc(s);
           }
           for (int s = 0; s < 2; ++s) {   // P3: out_proj
+            const bool dbgp = P.dbg && c == 0 && e == 0 && st == 5 && s == 0;
+            if (dbgp && lane == 0) P.dbg[48] = clock64();
             wait_a(s);
+            if (dbgp && lane == 0) P.dbg[49] = clock64();
             wait(B_WF_O + s);
-            job_ksw(accc[s], acol[s], wb[s][1], 64, 64, 8192);
+            if (dbgp && lane == 0) P.dbg[50] = clock64();
+            job_ksw<64, 64>(accc[s], acol[s], wb[s][1], 8192);
             commit_acc(s);
+            if (dbgp && lane == 0) P.dbg[51] = clock64();
           }
           wait(B_WF_W2);
           for (int s = 0; s < 2; ++s) {   // P4: ffn.0 (N padded to 16)
             wait_a(s);
-            job_ksw(accc[s], acol[s], wf0f[s], 16, 64, 2048);
+            job_ksw<16, 64>(accc[s], acol[s], wf0f[s], 2048);
             commit_acc(s);
           }
           for (int s = 0; s < 2; ++s) {   // P5: ffn.3 (K padded to 8)
             wait_a(s);
-            job_knosw(accc[s], acol[s], smw + (s ? kSmWf31 : kSmWf30), 64, 8);
+            job_knosw<64, 8>(accc[s], acol[s], smw + (s ? kSmWf31 : kSmWf30));
             commit_acc(s);
           }
           wait_a(0); wait_a(1);           // P6: fc1 on cat
           wait(B_WF_W1);
-          job_ksw(accc[2], acol[2], xb[0], 64, 128, 8192);
+          job_ksw<64, 128>(accc[2], acol[2], xb[0], 8192);
           commit_acc(2);
           wait_a(2);                      // P7: fc2
-          job_ksw(accc[2], acol[2], w2f, 32, 64, 4096);
+          job_ksw<32, 64>(accc[2], acol[2], w2f, 4096);
           commit_acc(2);
           wait_a(2);                      // P8: output (N padded to 16)
-          job_knosw(accc[2], acol[2], smw + kSmW3, 16, 32);
+          job_knosw<16, 32>(accc[2], acol[2], smw + kSmW3);
           commit_acc(2);
 
           // ---- backward, head
           wait_acc_last(2);               // every forward MMA has finished: weight / x buffers are free
-          mbar_expect_tx(&bars[B_WB + 0], 8192);
+          expect(B_WB + 0, 8192);
           for (int nb = 0; nb < 2; ++nb) tma(TM_W2_M, wb[0][0] + nb * 4096, nb * 32, 0, B_WB + 0);
           stash_ld(SL_HD, 2, xb[0], B_X + 0);
-          mbar_expect_tx(&bars[B_WB + 1], 32768);
+          expect(B_WB + 1, 32768);
           for (int nb = 0; nb < 4; ++nb) tma(TM_W1_M, wb[0][1] + nb * 8192, nb * 32, 0, B_WB + 1);
           wait_a(2);                      // B7: da2 in A[0..31] and dymn[V]
           wait(B_WB + 0);
-          job_mn(accc[2], acol[2], wb[0][0], 64, 32, 4096);
+          job_mn<64, 32>(accc[2], acol[2], wb[0][0], 4096);
           commit_acc(2);
           wait(B_X + 0);
-          job_dw(tmem + kColDw, dy[0], xb[0], 64, kSlotB);                    // dW2 -> V slot 0
+          job_dw<64>(tmem + kColDw, dy[0], xb[0], kSlotB);                    // dW2 -> V slot 0
           commit_dw(2);
           wait_dw_last(2);
           stash_ld(SL_CAT, 4, xb[0], B_X + 1);
           wait_a(2);                      // B6: da in A[0..63] and dymn[L]
           wait(B_WB + 1);
-          job_mn(accc[2], acol[2], wb[0][1], 128, 64, 8192);                  // dcat -> acc 128..255
+          job_mn<128, 64>(accc[2], acol[2], wb[0][1], 8192);                  // dcat -> acc 128..255
           commit_acc(2);
           wait(B_X + 1);
-          job_dw(tmem + kColDw + 128, dy[1], xb[0], 128, kSlotB);             // dW1 -> L slots (128 columns)
+          job_dw<128>(tmem + kColDw + 128, dy[1], xb[0], kSlotB);             // dW1 -> L slots (128 columns)
           commit_dw(2);
           // ---- backward, branches.  Weight double buffer: wb[s][0] / wb[s][1]; X single buffer xb[s]
           wait_acc_last(2);               // dX6 done: W1mn (wb[0][1], wb[1][0]) is free
           wait_dw_last(2);                // dW1 done: xbuf is free
           for (int s = 0; s < 2; ++s) {
-            mbar_expect_tx(&bars[B_WB + 2 * s], 2048);
+            expect(B_WB + 2 * s, 2048);
             for (int nb = 0; nb < 2; ++nb) tma(TM_WF0_M + s, wb[s][0] + nb * 1024, nb * 32, 0, B_WB + 2 * s);
             stash_ld(SL_BR * s + SL_GF, 1, xb[s], B_X + s);
           }
           dwk[0] = 1; dwk[1] = 0;         // dW2 sits in V slot 0 until its drain; dW1 is drained before b_a[L]
           for (int s = 0; s < 2; ++s) {   // B5: ffn.3 (Wf3 MN-major written by the element-wise warps into wb[s][1])
             wait_a(s);
-            job_mn(accc[s], acol[s], wb[s][1], 16, 64, 0);
+            job_mn<16, 64>(accc[s], acol[s], wb[s][1], 0);
             commit_acc(s);
             wait(B_X + s);
-            job_dw(dwcol(s), dy[s], xb[s], 16, 0);
+            job_dw<16>(dwcol(s), dy[s], xb[s], 0);
             commit_dw(s);
             dwk[s] ^= 1;
           }
           for (int s = 0; s < 2; ++s) {
             wait_dw_last(s);
             stash_ld(SL_BR * s + SL_N1, 2, xb[s], B_X + s);
-            mbar_expect_tx(&bars[B_WB + 2 * s + 1], 16384);
+            expect(B_WB + 2 * s + 1, 16384);
             for (int nb = 0; nb < 2; ++nb) tma(TM_WO_M + s, wb[s][1] + nb * 8192, nb * 32, 0, B_WB + 2 * s + 1);
           }
           for (int s = 0; s < 2; ++s) {   // B4: ffn.0
             wait_a(s);
             wait(B_WB + 2 * s);
-            job_mn(accc[s], acol[s], wb[s][0], 64, 8, 1024);
+            job_mn<64, 8>(accc[s], acol[s], wb[s][0], 1024);
             commit_acc(s);
             wait(B_X + s);
-            job_dw(dwcol(s), dy[s], xb[s], 64, kSlotB);
+            job_dw<64>(dwcol(s), dy[s], xb[s], kSlotB);
             commit_dw(s);
             dwk[s] ^= 1;
           }
           for (int s = 0; s < 2; ++s) {
             wait_dw_last(s);
             stash_ld(SL_BR * s + SL_VD, 2, xb[s], B_X + s);
-            mbar_expect_tx(&bars[B_WB + 2 * s], 16384);
+            expect(B_WB + 2 * s, 16384);
             for (int nb = 0; nb < 2; ++nb) tma(TM_WV_M + s, wb[s][0] + nb * 8192, nb * 32, 0, B_WB + 2 * s);
           }
           for (int s = 0; s < 2; ++s) {   // B3: out_proj
             wait_a(s);
             wait(B_WB + 2 * s + 1);
-            job_mn(accc[s], acol[s], wb[s][1], 64, 64, 8192);
+            job_mn<64, 64>(accc[s], acol[s], wb[s][1], 8192);
             commit_acc(s);
             wait(B_X + s);
-            job_dw(dwcol(s), dy[s], xb[s], 64, kSlotB);
+            job_dw<64>(dwcol(s), dy[s], xb[s], kSlotB);
             commit_dw(s);
             dwk[s] ^= 1;
           }
@@ -450,10 +581,10 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
           for (int s = 0; s < 2; ++s) {   // B2: V projection
             wait_a(s);
             wait(B_WB + 2 * s);
-            job_mn(accc[s], acol[s], wb[s][0], 64, 64, 8192);
+            job_mn<64, 64>(accc[s], acol[s], wb[s][0], 8192);
             commit_acc(s);
             wait(B_X + s);
-            job_dw(dwcol(s), dy[s], xb[s], 64, kSlotB);
+            job_dw<64>(dwcol(s), dy[s], xb[s], kSlotB);
             commit_dw(s);
             dwk[s] ^= 1;
           }
@@ -461,7 +592,7 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
           for (int s = 0; s < 2; ++s) {   // B1: dense (dW only)
             wait_a(s);
             wait(B_X + s);
-            job_dw(dwcol(s), dy[s], xb[s], 16, 0);
+            job_dw<16>(dwcol(s), dy[s], xb[s], 0);
             commit_dw(s);
             dwk[s] ^= 1;
           }
@@ -470,92 +601,193 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
     }
   } else {
     // =================================================================================== element-wise warps
-    const int q = warp & 3, chunk = warp >> 2, row = 32 * q + lane, col0 = 16 * chunk;
+    // Branch phases: warps 0-7 own the vitals stream and warps 8-15 the labs stream, so the two branches run concurrently
+    // and each hides the other's latencies; a thread owns one sample (TMEM lane) and 32 of the 64 features, processed as
+    // two 16-column halves.  Head phases: all 16 warps, 16 columns per thread.
+    // warps 1..16; the TMEM lane quarter of a warp is fixed by the hardware (warp id % 4), its other role bits are free
+    const int etid = tid - 32, ew = warp - 1;
+    const int q = warp & 3, row = 32 * q + lane;
+    const int s = ew >> 3, ch2 = (ew >> 2) & 1;               // branch phases: stream and 32-column half
+    const int chunk = ew >> 2, col0 = 16 * chunk;             // head phases
+    const int SB = SP_BR * s, S0 = SL_BR * s;
     const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
     uint8_t* dymn[2] = {smem + kOffDy, smem + kOffDy + 2 * kSlotB};
     uint32_t ph = 0;
     auto wait_b = [&](int b) { mbar_wait_to(&bars[b], (ph >> b) & 1u); ph ^= 1u << b; };
-    auto wait_acc = [&](int s) { wait_b(B_ACC + s); tc_fence_after(); };
-    auto wait_dw = [&](int s) { wait_b(B_DW + s); tc_fence_after(); };
-    auto signal_a = [&](int s) {
+    auto wait_acc = [&](int st) { wait_b(B_ACC + st); tc_fence_after(); };
+    auto wait_dw = [&](int st) { wait_b(B_DW + st); tc_fence_after(); };
+    // forward: the next MMA reads its A operand from TMEM only, no proxy fence needed
+    auto signal_fwd = [&](int st) { tmem_st_wait(); tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(&bars[B_A + st]); };
+    // backward: dY was also written to shared memory for the dW MMA (generic -> async proxy)
+    auto signal_bwd = [&](int st) {
       tmem_st_wait();
-      fence_async();
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bars[B_A + s]);
+      if (lane == 0) mbar_arrive(&bars[B_A + st]);
     };
     auto slot = [&](int sl) { return stash + (int64_t)sl * kSlotF + row * 32; };
-    auto sl64 = [&](int sl) { return slot(sl + (col0 >> 5)) + (col0 & 31); };     // (row, col0..col0+15) of a 64-wide activation
+    auto blk = [&](int sl) { return stash + (int64_t)sl * kSlotF; };
+    // thread-private stash tensors, lane-interleaved (this thread's 128-bit chunk j of tensor `sl`)
+    auto el32 = [&](int sl, int j) { return reinterpret_cast<float4*>(stash + (int64_t)sl * kSlotF) + (ew * 8 + j) * 32 + lane; };
+    auto el16 = [&](int sl, int j) { return reinterpret_cast<float4*>(stash + (int64_t)sl * kSlotF) + (ew * 4 + j) * 32 + lane; };
+    auto el_st32 = [&](int sl, const float* x) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) __stcg(el32(sl, j), make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]));
+    };
+    auto el_ld32 = [&](int sl, float* x) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float4 t = __ldcg(el32(sl, j)); x[4 * j] = t.x; x[4 * j + 1] = t.y; x[4 * j + 2] = t.z; x[4 * j + 3] = t.w; }
+    };
+    auto el_st16 = [&](int sl, const float* x) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) __stcg(el16(sl, j), make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]));
+    };
+    auto el_ld16 = [&](int sl, float* x) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { const float4 t = __ldcg(el16(sl, j)); x[4 * j] = t.x; x[4 * j + 1] = t.y; x[4 * j + 2] = t.z; x[4 * j + 3] = t.w; }
+    };
+    // forward-only TMEM scratch in the (then idle) dW accumulator columns: the residual inputs h1 and n1 of this branch
+    const uint32_t tH1 = tq + kColDw + 64 * s + 32 * ch2, tN1 = tq + kColDw + 128 + 64 * s + 32 * ch2;
+    const int row0 = 32 * q;
     auto ld_acc16 = [&](uint32_t col, float* v) { tmem_ld16_async(tq + col, v); tmem_ld_wait(); };
-    // drain a 64 x (16 per chunk) dW tile (M = 64: row r lives in lane (r / 16) * 32 + r % 16) into the gradient row
-    auto drain = [&](uint32_t col, int w_off, int rows, int ld, int ncols) {
+    int lnk = 0;
+    // LayerNorm partial sums of this thread's row: exchanged between the two warps that share the row
+    auto ln_stats2 = [&](float a, float b, float& sa, float& sb) {
+      float2* x = lnx + ((s * 2 + lnk) * 128 + row) * 2;
+      lnk ^= 1;
+      x[ch2] = make_float2(a, b);
+      bar_named(1 + q + 4 * s, 64);
+      sa = x[0].x + x[1].x;
+      sb = x[0].y + x[1].y;
+    };
+    // drain one 16-column piece of a dW tile (M = 64: row r lives in lane (r / 16) * 32 + r % 16) into the gradient row
+    auto drain16 = [&](uint32_t col, float* dst_row0, int rows, int ld, int c0, int ncols) {
       float g[16];
-      ld_acc16(col + col0, g);
+      ld_acc16(col + c0, g);
       const int r = 16 * q + lane;
-      if (lane < 16 && r < rows && col0 < ncols) {
-        float* dst = gw + w_off + (int64_t)r * ld + col0;
-        if ((ld & 3) == 0 && col0 + 16 <= ncols) st16g(dst, g);
-        else for (int j = 0; j < 16; ++j) if (col0 + j < ncols) __stcg(dst + j, g[j]);
+      if (lane < 16 && r < rows && c0 < ncols) {
+        float* dst = dst_row0 + (int64_t)r * ld + c0;
+        if ((ld & 3) == 0 && c0 + 16 <= ncols) st16g(dst, g);
+        else for (int j = 0; j < 16; ++j) if (c0 + j < ncols) __stcg(dst + j, g[j]);
       }
     };
-    // LayerNorm statistics of this thread's row across the 4 column chunks
-    auto ln_stats = [&](int buf, float a, float b, float& sa, float& sb) {
-      float2* x = lnx + (buf * 128 + row) * 4;
-      x[chunk] = make_float2(a, b);
-      bar_named(1 + q, 128);
-      sa = (x[0].x + x[1].x) + (x[2].x + x[3].x);
-      sb = (x[0].y + x[1].y) + (x[2].y + x[3].y);
-    };
 
+    int tsi = 0;
+#define TS2(k) do { if (P.dbg && c == 0 && etid == 0 && gstep == 5) P.dbg[32 + (k)] = clock64(); } while (0)
+#define TSTAMP() do { if (P.dbg && c == 0 && etid == 0 && gstep == 5 && tsi < 64) P.dbg[tsi++] = clock64(); } while (0)
     Rng rng; rng.seed_lo = P.seed_lo; rng.seed_hi = P.seed_hi; rng.client = (uint32_t)P.client_ids[c]; rng.on = P.dropout;
+    const float inv1 = 1.f / (1.f - P.p1), inv3 = 1.f / (1.f - P.p3);
     double b1t = 1.0, b2t = 1.0;
     int opt_steps = 0, gstep = 0;
-    int dwk[2] = {0, 0};
-    float rstd_r[2][3];                     // LayerNorm 1/std of this thread's row, kept for the backward
-    auto dwcol = [&](int s) { return kColDw + (uint32_t)s * 128u + (uint32_t)dwk[s] * 64u; };
+    int dwk = 0;
+    float rstd_r[3];                          // LayerNorm 1/std of this thread's row (own branch), kept for the backward
+    uint32_t mk1 = 0, mk2 = 0, mk3 = 0, mkh = 0, mkf = 0;   // dropout keep bits drawn in the forward, reused by the backward
+    auto dwcol = [&]() { return kColDw + (uint32_t)s * 128u + (uint32_t)dwk * 64u; };
+    // keep bits of 32 consecutive elements of a site (bit j = element e0 + j)
+    auto keep32 = [&](int site, uint32_t e0, float p) -> uint32_t {
+      if (!(rng.on && p > 0.f)) return 0xffffffffu;
+      uint32_t bits = 0;
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const AflU4 u = afl_philox((e0 + j) >> 2, ((uint32_t)site & 0xFFFFu) | (rng.client << 16), rng.step, (uint32_t)row, rng.seed_lo, rng.seed_hi);
+        const float sc = 1.0f / 16777216.0f;
+        bits |= (((float)(u.x >> 8) * sc >= p) ? 1u : 0u) << j;
+        bits |= (((float)(u.y >> 8) * sc >= p) ? 1u : 0u) << (j + 1);
+        bits |= (((float)(u.z >> 8) * sc >= p) ? 1u : 0u) << (j + 2);
+        bits |= (((float)(u.w >> 8) * sc >= p) ? 1u : 0u) << (j + 3);
+      }
+      return bits;
+    };
+    auto keep16 = [&](int site, uint32_t e0, float p) -> uint32_t {
+      if (!(rng.on && p > 0.f)) return 0xffffu;
+      uint32_t bits = 0;
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) {
+        const AflU4 u = afl_philox((e0 + j) >> 2, ((uint32_t)site & 0xFFFFu) | (rng.client << 16), rng.step, (uint32_t)row, rng.seed_lo, rng.seed_hi);
+        const float sc = 1.0f / 16777216.0f;
+        bits |= (((float)(u.x >> 8) * sc >= p) ? 1u : 0u) << j;
+        bits |= (((float)(u.y >> 8) * sc >= p) ? 1u : 0u) << (j + 1);
+        bits |= (((float)(u.z >> 8) * sc >= p) ? 1u : 0u) << (j + 2);
+        bits |= (((float)(u.w >> 8) * sc >= p) ? 1u : 0u) << (j + 3);
+      }
+      return bits;
+    };
 
-    // small weights + parameters -> shared memory (start of every step: after the optimiser changed them)
+    // small weights + parameters -> shared memory (start of every step: after the optimiser changed them).  All global
+    // loads are issued before the first store so that one L2 round trip covers them.
+    auto sp_src = [&](int i) -> int {          // parameter-row offset of small-parameter slot i (-1: padding)
+      if (i < 2 * SP_BR) {
+        const int b = i >= SP_BR, r = i - b * SP_BR;
+        if (r < SP_BF0) {
+          const int seg = r >> 6, j = r & 63;
+          const int o = seg == 0 ? L.bd[b] : seg == 1 ? L.bv[b] : seg == 2 ? L.bo[b] : seg == 3 ? L.g1[b] : L.be1[b];
+          return o + j;
+        }
+        if (r < SP_BF3) return (r - SP_BF0) < L.ff ? L.bf0[b] + (r - SP_BF0) : -1;
+        const int r2 = r - SP_BF3, seg = r2 >> 6, j = r2 & 63;
+        const int o = seg == 0 ? L.bf3[b] : seg == 1 ? L.g2[b] : seg == 2 ? L.be2[b] : seg == 3 ? L.g3[b] : L.be3[b];
+        return o + j;
+      }
+      const int r = i - 2 * SP_BR;
+      if (r < 64) return L.b1 + r;
+      if (r < 96) return L.b2 + (r - 64);
+      if (r < 128) return L.w3 + (r - 96);
+      return r == 128 ? L.b3 : -1;
+    };
     auto load_small = [&]() {
-      for (int s = 0; s < 2; ++s) {
-        const int kin = L.kin[s], kp = s ? 16 : 8;
-        uint8_t* wd = smem + kOffSm + (s ? kSmWd1 : kSmWd0);
-        for (int i = tid; i < 64 * kp; i += kEpi) {
-          const int nn = i / kp, k = i - nn * kp;
-          const float val = k < kin ? __ldcg(w + L.wd[s] + nn * kin + k) : 0.f;
-          *reinterpret_cast<float*>(wd + (nn >> 3) * (kp / 4 * 128) + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = val;
-        }
-        uint8_t* wf = smem + kOffSm + (s ? kSmWf31 : kSmWf30);
-        for (int i = tid; i < 64 * 8; i += kEpi) {
-          const int nn = i >> 3, k = i & 7;
-          const float val = k < L.ff ? __ldcg(w + L.wf3[s] + nn * L.ff + k) : 0.f;
-          *reinterpret_cast<float*>(wf + (nn >> 3) * 256 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = val;
-        }
-        const int B = SP_BR * s;
-        for (int i = tid; i < 64; i += kEpi) {
-          sp[B + SP_BD + i] = __ldcg(w + L.bd[s] + i); sp[B + SP_BV + i] = __ldcg(w + L.bv[s] + i);
-          sp[B + SP_BO + i] = __ldcg(w + L.bo[s] + i); sp[B + SP_G1 + i] = __ldcg(w + L.g1[s] + i);
-          sp[B + SP_BE1 + i] = __ldcg(w + L.be1[s] + i); sp[B + SP_BF3 + i] = __ldcg(w + L.bf3[s] + i);
-          sp[B + SP_G2 + i] = __ldcg(w + L.g2[s] + i); sp[B + SP_BE2 + i] = __ldcg(w + L.be2[s] + i);
-          sp[B + SP_G3 + i] = __ldcg(w + L.g3[s] + i); sp[B + SP_BE3 + i] = __ldcg(w + L.be3[s] + i);
-          if (i < 16) sp[B + SP_BF0 + i] = i < L.ff ? __ldcg(w + L.bf0[s] + i) : 0.f;
-        }
+      float vsp[3], vwd0, vwd1[2], vf3[2], vw3;
+      int isp[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int i = etid + k * kEpi;
+        isp[k] = i < SP_N ? sp_src(i) : -2;
+        vsp[k] = isp[k] >= 0 ? __ldcg(w + isp[k]) : 0.f;
       }
-      uint8_t* w3 = smem + kOffSm + kSmW3;
-      for (int i = tid; i < 16 * 32; i += kEpi) {
-        const int nn = i >> 5, k = i & 31;
-        *reinterpret_cast<float*>(w3 + (nn >> 3) * 1024 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = nn == 0 ? __ldcg(w + L.w3 + k) : 0.f;
+      {  // dense V: [64 x 8]
+        const int nn = etid >> 3, k = etid & 7;
+        vwd0 = k < L.kin[0] ? __ldcg(w + L.wd[0] + nn * L.kin[0] + k) : 0.f;
       }
-      for (int i = tid; i < 64; i += kEpi) {
-        sp[SP_B1 + i] = __ldcg(w + L.b1 + i);
-        if (i < 32) { sp[SP_B2 + i] = __ldcg(w + L.b2 + i); sp[SP_W3 + i] = __ldcg(w + L.w3 + i); }
-        if (i < 16) sp[SP_B3 + i] = i == 0 ? __ldcg(w + L.b3) : 0.f;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {  // dense L: [64 x 16]
+        const int i = etid + t * kEpi, nn = i >> 4, k = i & 15;
+        vwd1[t] = k < L.kin[1] ? __ldcg(w + L.wd[1] + nn * L.kin[1] + k) : 0.f;
       }
-      for (int i = tid; i < SP_N; i += kEpi) sg[i] = 0.f;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {  // ffn.3: [64 x 8]
+        const int nn = etid >> 3, k = etid & 7;
+        vf3[b] = k < L.ff ? __ldcg(w + L.wf3[b] + nn * L.ff + k) : 0.f;
+      }
+      {  // output: [16 x 32], row 0 only
+        const int nn = etid >> 5, k = etid & 31;
+        vw3 = nn == 0 ? __ldcg(w + L.w3 + k) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int i = etid + k * kEpi;
+        if (i < SP_N) { sp[i] = vsp[k]; sg[i] = 0.f; }
+      }
+      uint8_t* sm = smem + kOffSm;
+      {
+        const int nn = etid >> 3, k = etid & 7;
+        *reinterpret_cast<float*>(sm + kSmWd0 + (nn >> 3) * 256 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = vwd0;
+        *reinterpret_cast<float*>(sm + kSmWf30 + (nn >> 3) * 256 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = vf3[0];
+        *reinterpret_cast<float*>(sm + kSmWf31 + (nn >> 3) * 256 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = vf3[1];
+      }
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        const int i = etid + t * kEpi, nn = i >> 4, k = i & 15;
+        *reinterpret_cast<float*>(sm + kSmWd1 + (nn >> 3) * 512 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = vwd1[t];
+      }
+      {
+        const int nn = etid >> 5, k = etid & 31;
+        *reinterpret_cast<float*>(sm + kSmW3 + (nn >> 3) * 1024 + (k >> 2) * 128 + (nn & 7) * 16 + (k & 3) * 4) = vw3;
+      }
     };
 
     load_small();
     fence_async();
-    bar_named(5, kEpi);
+    bar_named(13, kEpi);
     if (lane == 0) mbar_arrive(&bars[B_STEP]);
 
     for (int e = 0; e < P.epochs; ++e) {
@@ -566,167 +798,223 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
         rng.step = (uint32_t)gstep;
         const float inv_b = 1.0f / (float)b;
         const bool valid = row < b;
-
+        const uint32_t accS = kColAcc + 64 * s, aS = kColA + 64 * s;     // this branch's accumulator / A-operand columns
+        TSTAMP();
         // ---------------------------------------------------------------- E0: gather the batch
-        if (chunk == 0) {
-          float xv[8], xl[16], y = 0.f;
+        if (ch2 == 0) {
+          float x[16];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) xv[j] = 0.f;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) xl[j] = 0.f;
+          for (int j = 0; j < 16; ++j) x[j] = 0.f;
+          float y = 0.f;
           if (valid) {
             const float* rec = P.data + (int64_t)idx_e[(int64_t)st * P.batch + row] * P.rec;
-            for (int j = 0; j < L.kin[0]; ++j) xv[j] = rec[j];
-            for (int j = 0; j < L.kin[1]; ++j) xl[j] = rec[L.kin[0] + j];
-            y = rec[L.kin[0] + L.kin[1]];
+            if (s == 0) { for (int j = 0; j < L.kin[0]; ++j) x[j] = rec[j]; y = rec[L.kin[0] + L.kin[1]]; }
+            else for (int j = 0; j < L.kin[1]; ++j) x[j] = rec[L.kin[0] + j];
           }
-          ylab[row] = y;
-          tmem_st8(tq + kColA, xv);
-          tmem_st16(tq + kColA + 64, xl);
-          float pad[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) pad[j] = j < 8 ? xv[j] : 0.f;
-          st16g(slot(SL_X), pad);
-          st16g(slot(SL_BR + SL_X), xl);
+          if (s == 0) { ylab[row] = y; tmem_st8(tq + aS, x); } else tmem_st16(tq + aS, x);
+          st16t(blk(S0 + SL_X), row0, lane, 0, x);
         }
-        signal_a(0);
-        signal_a(1);
-
-        // ---------------------------------------------------------------- forward, branches
-        for (int s = 0; s < 2; ++s) {   // E1: h1 = gelu(x Wd^T + bd)
-          const int B = SP_BR * s, S0 = SL_BR * s;
+        signal_fwd(s);
+        TSTAMP();
+        // ---------------------------------------------------------------- forward, this warp group's branch
+        {                               // E1: h1 = gelu(x Wd^T + bd)
           wait_acc(s);
-          float a[16], g[16];
-          ld_acc16(kColAcc + 64 * s + col0, a);
+          float a[32], g[32];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { const float z = a[j] + sp[B + SP_BD + col0 + j]; g[j] = afl_gelu_grad(z); a[j] = afl_gelu(z); }
-          st16g(sl64(S0 + SL_GP1), g);
-          st16g(sl64(S0 + SL_H1), a);
-          tmem_st16(tq + kColA + 64 * s + col0, a);
-          signal_a(s);
-        }
-        for (int s = 0; s < 2; ++s) {   // E2: vd = headdrop(h1 Wv^T + bv)
-          const int B = SP_BR * s, S0 = SL_BR * s;
-          wait_acc(s);
-          float a[16];
-          ld_acc16(kColAcc + 64 * s + col0, a);
-          const float ds = drop1(rng, L.rng_head[s], row, chunk, P.p1);
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            ld_acc16(accS + c0, a + 16 * hf);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) a[j] = (a[j] + sp[B + SP_BV + col0 + j]) * ds;
-          st16g(sl64(S0 + SL_VD), a);
-          tmem_st16(tq + kColA + 64 * s + col0, a);
-          signal_a(s);
+            for (int j = 0; j < 16; ++j) gelu_both(a[16 * hf + j] + sp[SB + SP_BD + c0 + j], a[16 * hf + j], g[16 * hf + j]);
+            tmem_st16(tq + aS + c0, a + 16 * hf);
+          }
+          signal_fwd(s);
+          tmem_st16(tH1, a);
+          tmem_st16(tH1 + 16, a + 16);
+          el_st32(EL_GP1, g);
+          st32t(blk(S0 + SL_H1 + ch2), row0, lane, a);
         }
-        for (int s = 0; s < 2; ++s) {   // E3: n1 = LN1(h1 + drop(vd Wo^T + bo))
-          const int B = SP_BR * s, S0 = SL_BR * s;
-          float h[16], ds[16];
-          ld16g(sl64(S0 + SL_H1), h);
-          drop16(rng, L.rng_ln1[s], row, col0, P.p1, ds);
+        TSTAMP();
+        {                               // E2: vd = headdrop(h1 Wv^T + bv)
+          mkh = 0;
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf)
+            mkh |= (drop1(rng, L.rng_head[s], row, 2 * ch2 + hf, P.p1) != 0.f ? 1u : 0u) << hf;
           wait_acc(s);
-          float a[16];
-          ld_acc16(kColAcc + 64 * s + col0, a);
+          float a[32];
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            const float ds = !rng.on ? 1.f : ((mkh >> hf) & 1u) ? inv1 : 0.f;
+            ld_acc16(accS + c0, a + 16 * hf);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a[16 * hf + j] = (a[16 * hf + j] + sp[SB + SP_BV + c0 + j]) * ds;
+            tmem_st16(tq + aS + c0, a + 16 * hf);
+          }
+          signal_fwd(s);
+          st32t(blk(S0 + SL_VD + ch2), row0, lane, a);
+        }
+        TSTAMP();
+        {                               // E3: n1 = LN1(h1 + drop(vd Wo^T + bo))
+          TS2(0);
+          float r[32];
+          tmem_ld16_async(tH1, r);
+          tmem_ld16_async(tH1 + 16, r + 16);
+          tmem_ld_wait();
+          mk1 = keep32(L.rng_ln1[s], 32 * ch2, P.p1);
+          TS2(1);
+          wait_acc(s);
+          TS2(2);
           float sum = 0.f, sq = 0.f;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { a[j] = h[j] + (a[j] + sp[B + SP_BO + col0 + j]) * ds[j]; sum += a[j]; sq += a[j] * a[j]; }
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            float a[16];
+            ld_acc16(accS + c0, a);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float ds = !rng.on ? 1.f : ((mk1 >> (16 * hf + j)) & 1u) ? inv1 : 0.f;
+              const float x = r[16 * hf + j] + (a[j] + sp[SB + SP_BO + c0 + j]) * ds;
+              r[16 * hf + j] = x; sum += x; sq += x * x;
+            }
+          }
+          TS2(3);
           float ts, tq2;
-          ln_stats(s, sum, sq, ts, tq2);
+          ln_stats2(sum, sq, ts, tq2);
+          TS2(4);
           const float mean = ts * (1.f / 64.f);
           float var = tq2 * (1.f / 64.f) - mean * mean;
           var = var > 0.f ? var : 0.f;
           const float rstd = 1.0f / sqrtf(var + AFL_LN_EPS);
+          rstd_r[0] = rstd;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { h[j] = (a[j] - mean) * rstd; a[j] = h[j] * sp[B + SP_G1 + col0 + j] + sp[B + SP_BE1 + col0 + j]; }
-          rstd_r[s][0] = rstd;
-          st16g(sl64(S0 + SL_XH1), h);
-          st16g(sl64(S0 + SL_N1), a);
-          tmem_st16(tq + kColA + 64 * s + col0, a);
-          signal_a(s);
+          for (int j = 0; j < 32; ++j) r[j] = (r[j] - mean) * rstd;                        // xhat
+          {
+            float n1[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) n1[j] = r[j] * sp[SB + SP_G1 + 32 * ch2 + j] + sp[SB + SP_BE1 + 32 * ch2 + j];
+            tmem_st16(tq + aS + 32 * ch2, n1);
+            tmem_st16(tq + aS + 32 * ch2 + 16, n1 + 16);
+            TS2(5);
+            signal_fwd(s);
+            TS2(6);
+            tmem_st16(tN1, n1);
+            tmem_st16(tN1 + 16, n1 + 16);
+            st32t(blk(S0 + SL_N1 + ch2), row0, lane, n1);
+          }
+          el_st32(EL_XH1, r);
         }
-        for (int s = 0; s < 2; ++s) {   // E4: gf = drop(gelu(n1 Wf0^T + bf0))   (ff <= 8 columns)
-          const int B = SP_BR * s, S0 = SL_BR * s;
+        TSTAMP();
+        {                               // E4: gf = drop(gelu(n1 Wf0^T + bf0))   (ff <= 8 columns)
           wait_acc(s);
-          if (chunk == 0) {
-            float a[16], g[16], ds[8];
-            ld_acc16(kColAcc + 64 * s, a);
-            drop4(rng, L.rng_f1[s], row, 0, P.p1, ds);
-            drop4(rng, L.rng_f1[s], row, 4, P.p1, ds + 4);
+          if (ch2 == 0) {
+            float a[16], g[16];
+            ld_acc16(accS, a);
+            mkf = keep16(L.rng_f1[s], 0, P.p1) & 0xffu;
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               if (j < 8 && j < L.ff) {
-                const float z = a[j] + sp[B + SP_BF0 + j];
-                g[j] = afl_gelu_grad(z) * ds[j]; a[j] = afl_gelu(z) * ds[j];
+                const float ds = !rng.on ? 1.f : ((mkf >> j) & 1u) ? inv1 : 0.f;
+                float gl, gp;
+                gelu_both(a[j] + sp[SB + SP_BF0 + j], gl, gp);
+                g[j] = gp * ds; a[j] = gl * ds;
               } else { g[j] = 0.f; a[j] = 0.f; }
             }
-            st16g(slot(S0 + SL_GPF), g);
-            st16g(slot(S0 + SL_GF), a);
-            tmem_st8(tq + kColA + 64 * s, a);
+            tmem_st8(tq + aS, a);
+            el_st16(EL_GPF, g);
+            st16t(blk(S0 + SL_GF), row0, lane, 0, a);
           }
-          signal_a(s);
+          signal_fwd(s);
         }
-        for (int s = 0; s < 2; ++s) {   // E5: n3 = LN3(LN2(n1 + drop(gf Wf3^T + bf3)))
-          const int B = SP_BR * s, S0 = SL_BR * s;
-          float h[16], ds[16];
-          ld16g(sl64(S0 + SL_N1), h);
-          drop16(rng, L.rng_ln2[s], row, col0, P.p1, ds);
+        TSTAMP();
+        {                               // E5: n3 = LN3(LN2(n1 + drop(gf Wf3^T + bf3)))
+          float r[32];
+          tmem_ld16_async(tN1, r);
+          tmem_ld16_async(tN1 + 16, r + 16);
+          tmem_ld_wait();
+          mk2 = keep32(L.rng_ln2[s], 32 * ch2, P.p1);
           wait_acc(s);
-          float a[16];
-          ld_acc16(kColAcc + 64 * s + col0, a);
           float sum = 0.f, sq = 0.f;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { a[j] = h[j] + (a[j] + sp[B + SP_BF3 + col0 + j]) * ds[j]; sum += a[j]; sq += a[j] * a[j]; }
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            float a[16];
+            ld_acc16(accS + c0, a);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float ds = !rng.on ? 1.f : ((mk2 >> (16 * hf + j)) & 1u) ? inv1 : 0.f;
+              const float x = r[16 * hf + j] + (a[j] + sp[SB + SP_BF3 + c0 + j]) * ds;
+              r[16 * hf + j] = x; sum += x; sq += x * x;
+            }
+          }
           float ts, tq2;
-          ln_stats(0, sum, sq, ts, tq2);
+          ln_stats2(sum, sq, ts, tq2);
           float mean = ts * (1.f / 64.f);
           float var = tq2 * (1.f / 64.f) - mean * mean;
           var = var > 0.f ? var : 0.f;
           float rstd = 1.0f / sqrtf(var + AFL_LN_EPS);
+          rstd_r[1] = rstd;
           sum = 0.f; sq = 0.f;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            h[j] = (a[j] - mean) * rstd; a[j] = h[j] * sp[B + SP_G2 + col0 + j] + sp[B + SP_BE2 + col0 + j];
-            sum += a[j]; sq += a[j] * a[j];
+          for (int j = 0; j < 32; ++j) r[j] = (r[j] - mean) * rstd;                        // xhat2
+          el_st32(EL_XH2, r);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float x = r[j] * sp[SB + SP_G2 + 32 * ch2 + j] + sp[SB + SP_BE2 + 32 * ch2 + j];
+            r[j] = x; sum += x; sq += x * x;
           }
-          rstd_r[s][1] = rstd;
-          st16g(sl64(S0 + SL_XH2), h);
-          ln_stats(1, sum, sq, ts, tq2);
+          ln_stats2(sum, sq, ts, tq2);
           mean = ts * (1.f / 64.f);
           var = tq2 * (1.f / 64.f) - mean * mean;
           var = var > 0.f ? var : 0.f;
           rstd = 1.0f / sqrtf(var + AFL_LN_EPS);
+          rstd_r[2] = rstd;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { h[j] = (a[j] - mean) * rstd; a[j] = h[j] * sp[B + SP_G3 + col0 + j] + sp[B + SP_BE3 + col0 + j]; }
-          rstd_r[s][2] = rstd;
-          st16g(sl64(S0 + SL_XH3), h);
-          st16g(sl64(SL_CAT + 2 * s), a);
-          tmem_st16(tq + kColA + 64 * s + col0, a);
-          signal_a(s);
+          for (int j = 0; j < 32; ++j) r[j] = (r[j] - mean) * rstd;                        // xhat3
+          {
+            float n3[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) n3[j] = r[j] * sp[SB + SP_G3 + 32 * ch2 + j] + sp[SB + SP_BE3 + 32 * ch2 + j];
+            tmem_st16(tq + aS + 32 * ch2, n3);
+            tmem_st16(tq + aS + 32 * ch2 + 16, n3 + 16);
+            signal_fwd(s);
+            st32t(blk(SL_CAT + 2 * s + ch2), row0, lane, n3);
+          }
+          el_st32(EL_XH3, r);
         }
-        // ---------------------------------------------------------------- forward, head
+        TSTAMP();
+        // ---------------------------------------------------------------- forward, head (all 16 warps, 16 columns each)
         {                               // E6: hd = drop(gelu(cat W1^T + b1))
-          float ds[16];
-          drop16(rng, L.rng_fc1, row, col0, P.p3, ds);
+          mk3 = keep16(L.rng_fc1, col0, P.p3);
           wait_acc(2);
           float a[16], g[16];
           ld_acc16(kColAcc + col0, a);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { const float z = a[j] + sp[SP_B1 + col0 + j]; g[j] = afl_gelu_grad(z) * ds[j]; a[j] = afl_gelu(z) * ds[j]; }
-          st16g(sl64(SL_GPA), g);
-          st16g(sl64(SL_HD), a);
+          for (int j = 0; j < 16; ++j) {
+            const float ds = !rng.on ? 1.f : ((mk3 >> j) & 1u) ? inv3 : 0.f;
+            float gl, gp;
+            gelu_both(a[j] + sp[SP_B1 + col0 + j], gl, gp);
+            g[j] = gp * ds; a[j] = gl * ds;
+          }
           tmem_st16(tq + kColA + col0, a);
-          signal_a(2);
+          signal_fwd(2);
+          el_st16(EL_GPA, g);
+          st16t(blk(SL_HD + (col0 >> 5)), row0, lane, col0 & 31, a);
         }
+        TSTAMP();
         float h2[16], gp2[16];
         {                               // E7: h2 = gelu(hd W2^T + b2)   (32 columns: chunks 0, 1)
           wait_acc(2);
           if (chunk < 2) {
             ld_acc16(kColAcc + col0, h2);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) { const float z = h2[j] + sp[SP_B2 + col0 + j]; gp2[j] = afl_gelu_grad(z); h2[j] = afl_gelu(z); }
-            st16g(slot(SL_H2) + col0, h2);
+            for (int j = 0; j < 16; ++j) gelu_both(h2[j] + sp[SP_B2 + col0 + j], h2[j], gp2[j]);
             tmem_st16(tq + kColA + col0, h2);
+            st16t(blk(SL_H2), row0, lane, col0, h2);
           }
-          signal_a(2);
+          signal_fwd(2);
         }
+        TSTAMP();
         {                               // E8 + B8: p = sigmoid(h2 w3 + b3), BCE, da2 = (dz w3) gelu'(a2)
           wait_acc(2);
           if (chunk == 0) {
@@ -748,7 +1036,7 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
             const float dzs = warp_sum(dz);
             if (lane == 0) { atomicAdd(loss_acc, loss); atomicAdd(loss_acc + 1, bad); atomicAdd(sg + SP_B3, dzs); }
           }
-          bar_named(1 + q, 128);
+          bar_named(9 + q, 128);
           if (chunk < 2) {
             const float dz = dzrow[row];
             float t[16];
@@ -761,12 +1049,18 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
             tmem_st16(tq + kColA + col0, t);
             st_dymn(dymn[0], row, col0, t);
           }
-          signal_a(2);
+          // every stash store of the forward is fenced here, once, for the TMA reads of the backward
+          tmem_st_wait();
+          fence_async();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars[B_A + 2]);
         }
+        TSTAMP();
         // ---------------------------------------------------------------- backward, head
         {                               // B7: da = (da2 W2) gelu'(a) mask
           float g[16];
-          ld16g(sl64(SL_GPA), g);
+          el_ld16(EL_GPA, g);
           wait_acc(2);
           float a[16];
           ld_acc16(kColAcc + col0, a);
@@ -776,191 +1070,213 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
           tmem_st16(tq + kColA + col0, a);
           st_dymn(dymn[1], row, col0, a);
           wait_dw(2);                                         // dW2 (reads dymn[V]) finished before it may be lapped
-          signal_a(2);
-          drain(kColDw, L.w2, 32, 64, 64);
+          signal_bwd(2);
+          drain16(kColDw, gw + L.w2, 32, 64, col0, 64);
         }
-        {                               // B6: dcat -> LN3, LN2 backward per branch -> do2
+        TSTAMP();
+        {                               // B6: dcat -> LN3, LN2 backward (own branch) -> do2
+          float g[32], xh[32];
+          el_ld32(EL_XH3, xh);
           wait_acc(2);
-          for (int s = 0; s < 2; ++s) {
-            const int B = SP_BR * s, S0 = SL_BR * s;
-            float xh[16], g[16], t[16], ds[16];
-            ld16g(sl64(S0 + SL_XH3), xh);
-            drop16(rng, L.rng_ln2[s], row, col0, P.p1, ds);
-            ld_acc16(kColAcc + 64 * s + col0, g);
-            float sa = 0.f, sb = 0.f;
+          ld_acc16(accS + 32 * ch2, g);
+          ld_acc16(accS + 32 * ch2 + 16, g + 16);
+          float sa = 0.f, sb = 0.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) { t[j] = g[j] * xh[j]; }
-            colsum16(t, sg + B + SP_G3 + col0, lane);
-            colsum16(g, sg + B + SP_BE3 + col0, lane);
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            float t[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) { g[j] *= sp[B + SP_G3 + col0 + j]; sa += g[j]; sb += g[j] * xh[j]; }
-            float ta, tb;
-            ln_stats(0, sa, sb, ta, tb);
-            float rs = rstd_r[s][2];
-            float m1 = ta * (1.f / 64.f), m2 = tb * (1.f / 64.f);
+            for (int j = 0; j < 16; ++j) t[j] = g[16 * hf + j] * xh[16 * hf + j];
+            colsum16(t, sg + SB + SP_G3 + c0, lane);
+            colsum16(g + 16 * hf, sg + SB + SP_BE3 + c0, lane);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) g[j] = rs * (g[j] - m1 - xh[j] * m2);          // dL/dn2
-            ld16g(sl64(S0 + SL_XH2), xh);
+            for (int j = 0; j < 16; ++j) { g[16 * hf + j] *= sp[SB + SP_G3 + c0 + j]; sa += g[16 * hf + j]; sb += g[16 * hf + j] * xh[16 * hf + j]; }
+          }
+          float ta, tb;
+          ln_stats2(sa, sb, ta, tb);
+          float rs = rstd_r[2], m1 = ta * (1.f / 64.f), m2 = tb * (1.f / 64.f);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) t[j] = g[j] * xh[j];
-            colsum16(t, sg + B + SP_G2 + col0, lane);
-            colsum16(g, sg + B + SP_BE2 + col0, lane);
-            sa = 0.f; sb = 0.f;
+          for (int j = 0; j < 32; ++j) g[j] = rs * (g[j] - m1 - xh[j] * m2);             // dL/dn2
+          el_ld32(EL_XH2, xh);
+          sa = 0.f; sb = 0.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) { g[j] *= sp[B + SP_G2 + col0 + j]; sa += g[j]; sb += g[j] * xh[j]; }
-            ln_stats(1, sa, sb, ta, tb);
-            rs = rstd_r[s][1];
-            m1 = ta * (1.f / 64.f); m2 = tb * (1.f / 64.f);
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            float t[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) g[j] = rs * (g[j] - m1 - xh[j] * m2);          // dL/dr2
-            st16g(sl64(S0 + SL_RES), g);
+            for (int j = 0; j < 16; ++j) t[j] = g[16 * hf + j] * xh[16 * hf + j];
+            colsum16(t, sg + SB + SP_G2 + c0, lane);
+            colsum16(g + 16 * hf, sg + SB + SP_BE2 + c0, lane);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) g[j] *= ds[j];                                  // dL/do2
-            colsum16(g, sg + B + SP_BF3 + col0, lane);
-            // ffn.3 weights, MN-major, for dgf = do2 . Wf3 (N = in padded to 16, K = 64 outputs)
+            for (int j = 0; j < 16; ++j) { g[16 * hf + j] *= sp[SB + SP_G2 + c0 + j]; sa += g[16 * hf + j]; sb += g[16 * hf + j] * xh[16 * hf + j]; }
+          }
+          ln_stats2(sa, sb, ta, tb);
+          rs = rstd_r[1]; m1 = ta * (1.f / 64.f); m2 = tb * (1.f / 64.f);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) g[j] = rs * (g[j] - m1 - xh[j] * m2);             // dL/dr2
+          el_st32(EL_RES, g);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) g[j] *= !rng.on ? 1.f : ((mk2 >> j) & 1u) ? inv1 : 0.f;   // dL/do2
+          colsum16(g, sg + SB + SP_BF3 + 32 * ch2, lane);
+          colsum16(g + 16, sg + SB + SP_BF3 + 32 * ch2 + 16, lane);
+          {   // ffn.3 weights, MN-major, for dgf = do2 . Wf3 (N = in padded to 16, K = 64 outputs)
             uint8_t* wmn = smem + kOffW + (2 * s + 1) * kSlotB;
-            for (int i = tid; i < 64 * 16; i += kEpi) {
+            for (int i = etid - 256 * s; i < 64 * 16; i += 256) {
               const int o = i >> 4, ii = i & 15;
               *reinterpret_cast<float*>(wmn + o * 128 + (((ii >> 3) ^ (o & 3)) << 5) + (ii & 7) * 4) =
                   ii < L.ff ? __ldcg(w + L.wf3[s] + o * L.ff + ii) : 0.f;
             }
-            if (s == 1) wait_dw(2);                           // dW1 (reads dymn[L]) finished
-            tmem_st16(tq + kColA + 64 * s + col0, g);
-            st_dymn(dymn[s], row, col0, g);
-            if (s == 1) {                                     // dW1: 64 x 128, 32 columns per chunk
-              const int r = 16 * q + lane;
-#pragma unroll
-              for (int hf = 0; hf < 2; ++hf) {
-                float g2[16];
-                ld_acc16(kColDw + 128 + 32 * chunk + 16 * hf, g2);
-                if (lane < 16) st16g(gw + L.w1 + (int64_t)r * 128 + 32 * chunk + 16 * hf, g2);
-              }
-            }
-            signal_a(s);
           }
-          dwk[0] = 1; dwk[1] = 0;
+          if (s == 1) wait_dw(2);                             // dW1 (reads dymn[L]) finished
+          tmem_st16(tq + aS + 32 * ch2, g);
+          tmem_st16(tq + aS + 32 * ch2 + 16, g + 16);
+          st_dymn(dymn[s], row, 32 * ch2, g);
+          st_dymn(dymn[s], row, 32 * ch2 + 16, g + 16);
+          if (s == 1) {                                       // dW1: 64 x 128 tile, 64 columns per warp
+#pragma unroll
+            for (int k = 0; k < 4; ++k) drain16(kColDw + 128, gw + L.w1, 64, 128, 64 * ch2 + 16 * k, 128);
+          }
+          signal_bwd(s);
+          if (s == 0) wait_dw(2);                             // keep the parity of the head's dW barrier in step
+          dwk = s == 0 ? 1 : 0;
         }
-        // ---------------------------------------------------------------- backward, branches
-        for (int s = 0; s < 2; ++s) {   // B5: df = (do2 Wf3) gelu'(f) mask
-          const int B = SP_BR * s, S0 = SL_BR * s;
+        TSTAMP();
+        // ---------------------------------------------------------------- backward, this warp group's branch
+        {                               // B5: df = (do2 Wf3) gelu'(f) mask
           wait_acc(s);
           float a[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) a[j] = 0.f;
-          if (chunk == 0) {
+          if (ch2 == 0) {
             float g[16];
-            ld16g(slot(S0 + SL_GPF), g);
-            ld_acc16(kColAcc + 64 * s, a);
+            el_ld16(EL_GPF, g);
+            ld_acc16(accS, a);
 #pragma unroll
             for (int j = 0; j < 16; ++j) a[j] = (j < L.ff) ? a[j] * g[j] : 0.f;
-            colsum16(a, sg + B + SP_BF0, lane);
+            colsum16(a, sg + SB + SP_BF0, lane);
           }
           wait_dw(s);                                           // dWf3 (reads dymn[s] = do2) finished
-          if (chunk == 0) tmem_st8(tq + kColA + 64 * s, a);
-          if (chunk < 2) st_dymn(dymn[s], row, col0, a);        // 32 columns: df (16) + zeros (16)
-          signal_a(s);
+          if (ch2 == 0) {
+            tmem_st8(tq + aS, a);
+            st_dymn(dymn[s], row, 0, a);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a[j] = 0.f;
+            st_dymn(dymn[s], row, 16, a);
+          }
+          signal_bwd(s);
           {                                                     // drain dWf3: [64 out] x [ff in]
             float g[16];
-            ld_acc16(dwcol(s), g);
+            ld_acc16(dwcol(), g);
             const int r = 16 * q + lane;
-            if (chunk == 0 && lane < 16) for (int j = 0; j < L.ff; ++j) __stcg(gw + L.wf3[s] + r * L.ff + j, g[j]);
+            if (ch2 == 0 && lane < 16) for (int j = 0; j < L.ff; ++j) __stcg(gw + L.wf3[s] + r * L.ff + j, g[j]);
           }
-          dwk[s] ^= 1;
+          dwk ^= 1;
         }
-        for (int s = 0; s < 2; ++s) {   // B4: dr1 = LN1'(df Wf0 + dr2); do = dr1 mask
-          const int B = SP_BR * s, S0 = SL_BR * s;
-          float res[16], xh[16], ds[16], t[16];
-          ld16g(sl64(S0 + SL_RES), res);
-          ld16g(sl64(S0 + SL_XH1), xh);
-          drop16(rng, L.rng_ln1[s], row, col0, P.p1, ds);
+        TSTAMP();
+        {                               // B4: dr1 = LN1'(df Wf0 + dr2); do = dr1 mask
+          float g[32], xh[32];
+          el_ld32(EL_RES, g);
+          el_ld32(EL_XH1, xh);
           wait_acc(s);
-          float g[16];
-          ld_acc16(kColAcc + 64 * s + col0, g);
           float sa = 0.f, sb = 0.f;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { g[j] += res[j]; t[j] = g[j] * xh[j]; }
-          colsum16(t, sg + B + SP_G1 + col0, lane);
-          colsum16(g, sg + B + SP_BE1 + col0, lane);
+          for (int hf = 0; hf < 2; ++hf) {
+            const int c0 = 32 * ch2 + 16 * hf;
+            float t[16];
+            ld_acc16(accS + c0, t);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { g[j] *= sp[B + SP_G1 + col0 + j]; sa += g[j]; sb += g[j] * xh[j]; }
+            for (int j = 0; j < 16; ++j) { g[16 * hf + j] += t[j]; t[j] = g[16 * hf + j] * xh[16 * hf + j]; }
+            colsum16(t, sg + SB + SP_G1 + c0, lane);
+            colsum16(g + 16 * hf, sg + SB + SP_BE1 + c0, lane);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { g[16 * hf + j] *= sp[SB + SP_G1 + c0 + j]; sa += g[16 * hf + j]; sb += g[16 * hf + j] * xh[16 * hf + j]; }
+          }
           float ta, tb;
-          ln_stats(s, sa, sb, ta, tb);
-          const float rs = rstd_r[s][0];
-          const float m1 = ta * (1.f / 64.f), m2 = tb * (1.f / 64.f);
+          ln_stats2(sa, sb, ta, tb);
+          const float rs = rstd_r[0], m1 = ta * (1.f / 64.f), m2 = tb * (1.f / 64.f);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) g[j] = rs * (g[j] - m1 - xh[j] * m2);            // dL/dr1
-          st16g(sl64(S0 + SL_RES), g);
+          for (int j = 0; j < 32; ++j) g[j] = rs * (g[j] - m1 - xh[j] * m2);             // dL/dr1
+          el_st32(EL_RES, g);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) g[j] *= ds[j];                                    // dL/do
-          colsum16(g, sg + B + SP_BO + col0, lane);
+          for (int j = 0; j < 32; ++j) g[j] *= !rng.on ? 1.f : ((mk1 >> j) & 1u) ? inv1 : 0.f;   // dL/do
+          colsum16(g, sg + SB + SP_BO + 32 * ch2, lane);
+          colsum16(g + 16, sg + SB + SP_BO + 32 * ch2 + 16, lane);
           wait_dw(s);                                           // dWf0 finished
-          tmem_st16(tq + kColA + 64 * s + col0, g);
-          st_dymn(dymn[s], row, col0, g);
-          signal_a(s);
-          drain(dwcol(s), L.wf0[s], L.ff, 64, 64);
-          dwk[s] ^= 1;
+          tmem_st16(tq + aS + 32 * ch2, g);
+          tmem_st16(tq + aS + 32 * ch2 + 16, g + 16);
+          st_dymn(dymn[s], row, 32 * ch2, g);
+          st_dymn(dymn[s], row, 32 * ch2 + 16, g + 16);
+          signal_bwd(s);
+          drain16(dwcol(), gw + L.wf0[s], L.ff, 64, 32 * ch2, 64);
+          drain16(dwcol(), gw + L.wf0[s], L.ff, 64, 32 * ch2 + 16, 64);
+          dwk ^= 1;
         }
-        for (int s = 0; s < 2; ++s) {   // B3: dv = (do Wo) headmask
-          const int B = SP_BR * s;
-          const float ds = drop1(rng, L.rng_head[s], row, chunk, P.p1);
+        TSTAMP();
+        {                               // B3: dv = (do Wo) headmask
           wait_acc(s);
-          float g[16];
-          ld_acc16(kColAcc + 64 * s + col0, g);
+          float g[32];
+          ld_acc16(accS + 32 * ch2, g);
+          ld_acc16(accS + 32 * ch2 + 16, g + 16);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) g[j] *= ds;
-          colsum16(g, sg + B + SP_BV + col0, lane);
+          for (int hf = 0; hf < 2; ++hf) {
+            const float ds = !rng.on ? 1.f : ((mkh >> hf) & 1u) ? inv1 : 0.f;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) g[16 * hf + j] *= ds;
+            colsum16(g + 16 * hf, sg + SB + SP_BV + 32 * ch2 + 16 * hf, lane);
+          }
           wait_dw(s);                                           // dWo finished
-          tmem_st16(tq + kColA + 64 * s + col0, g);
-          st_dymn(dymn[s], row, col0, g);
-          signal_a(s);
-          drain(dwcol(s), L.wo[s], 64, 64, 64);
-          dwk[s] ^= 1;
+          tmem_st16(tq + aS + 32 * ch2, g);
+          tmem_st16(tq + aS + 32 * ch2 + 16, g + 16);
+          st_dymn(dymn[s], row, 32 * ch2, g);
+          st_dymn(dymn[s], row, 32 * ch2 + 16, g + 16);
+          signal_bwd(s);
+          drain16(dwcol(), gw + L.wo[s], 64, 64, 32 * ch2, 64);
+          drain16(dwcol(), gw + L.wo[s], 64, 64, 32 * ch2 + 16, 64);
+          dwk ^= 1;
         }
-        for (int s = 0; s < 2; ++s) {   // B2: da1 = (dv Wv + dr1) gelu'(a1)
-          const int B = SP_BR * s, S0 = SL_BR * s;
-          float res[16], gp[16];
-          ld16g(sl64(S0 + SL_RES), res);
-          ld16g(sl64(S0 + SL_GP1), gp);
+        TSTAMP();
+        {                               // B2: da1 = (dv Wv + dr1) gelu'(a1)
+          float g[32], gp[32];
+          el_ld32(EL_RES, g);
+          el_ld32(EL_GP1, gp);
           wait_acc(s);
-          float g[16];
-          ld_acc16(kColAcc + 64 * s + col0, g);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) g[j] = (g[j] + res[j]) * gp[j];
-          colsum16(g, sg + B + SP_BD + col0, lane);
+          for (int hf = 0; hf < 2; ++hf) {
+            float t[16];
+            ld_acc16(accS + 32 * ch2 + 16 * hf, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) g[16 * hf + j] = (g[16 * hf + j] + t[j]) * gp[16 * hf + j];
+            colsum16(g + 16 * hf, sg + SB + SP_BD + 32 * ch2 + 16 * hf, lane);
+          }
           wait_dw(s);                                           // dWv finished
-          st_dymn(dymn[s], row, col0, g);
-          signal_a(s);
-          drain(dwcol(s), L.wv[s], 64, 64, 64);
-          dwk[s] ^= 1;
+          st_dymn(dymn[s], row, 32 * ch2, g);
+          st_dymn(dymn[s], row, 32 * ch2 + 16, g + 16);
+          signal_bwd(s);
+          drain16(dwcol(), gw + L.wv[s], 64, 64, 32 * ch2, 64);
+          drain16(dwcol(), gw + L.wv[s], 64, 64, 32 * ch2 + 16, 64);
+          dwk ^= 1;
         }
-        for (int s = 0; s < 2; ++s) {   // B1: drain dWd [64 x kin]
+        TSTAMP();
+        {                               // B1: drain dWd [64 x kin]
           wait_dw(s);
           float g[16];
-          ld_acc16(dwcol(s), g);
+          ld_acc16(dwcol(), g);
           const int r = 16 * q + lane, kin = L.kin[s];
-          if (chunk == 0 && lane < 16) for (int j = 0; j < kin; ++j) __stcg(gw + L.wd[s] + r * kin + j, g[j]);
-          dwk[s] ^= 1;
+          if (ch2 == 0 && lane < 16) for (int j = 0; j < kin; ++j) __stcg(gw + L.wd[s] + r * kin + j, g[j]);
+          dwk ^= 1;
         }
         tc_fence_before();
-        bar_named(5, kEpi);
+        bar_named(13, kEpi);
+        TSTAMP();
         // ---------------------------------------------------------------- small gradients -> gradient row
-        for (int s = 0; s < 2; ++s) {
-          const int B = SP_BR * s;
-          for (int i = tid; i < 64; i += kEpi) {
-            gw[L.bd[s] + i] = sg[B + SP_BD + i]; gw[L.bv[s] + i] = sg[B + SP_BV + i]; gw[L.bo[s] + i] = sg[B + SP_BO + i];
-            gw[L.g1[s] + i] = sg[B + SP_G1 + i]; gw[L.be1[s] + i] = sg[B + SP_BE1 + i]; gw[L.bf3[s] + i] = sg[B + SP_BF3 + i];
-            gw[L.g2[s] + i] = sg[B + SP_G2 + i]; gw[L.be2[s] + i] = sg[B + SP_BE2 + i];
-            gw[L.g3[s] + i] = sg[B + SP_G3 + i]; gw[L.be3[s] + i] = sg[B + SP_BE3 + i];
-            if (i < L.ff) gw[L.bf0[s] + i] = sg[B + SP_BF0 + i];
-          }
-        }
-        for (int i = tid; i < 64; i += kEpi) {
-          gw[L.b1 + i] = sg[SP_B1 + i];
-          if (i < 32) { gw[L.b2 + i] = sg[SP_B2 + i]; gw[L.w3 + i] = sg[SP_W3 + i]; }
-          if (i == 0) gw[L.b3] = sg[SP_B3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int i = etid + k * kEpi;
+          if (i < SP_N) { const int o = sp_src(i); if (o >= 0) gw[o] = sg[i]; }
         }
         __threadfence_block();
-        bar_named(5, kEpi);
+        bar_named(13, kEpi);
+        TSTAMP();
         // ---------------------------------------------------------------- optimiser step
         ++opt_steps;
         b1t *= (double)P.beta1; b2t *= (double)P.beta2;
@@ -970,26 +1286,36 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
         o.first_step = opt_steps == 1; o.clip_coef = 1.f;
         if (P.clip_proper) {
           float part = 0.f;
-          for (int r = 0; r < P.n_ranges; ++r) part += afl_reduce_sqnorm(gw, 1, P.d_pad, P.range_lo[r], P.range_hi[r], tid, kEpi);
+          for (int r = 0; r < P.n_ranges; ++r) part += afl_reduce_sqnorm(gw, 1, P.d_pad, P.range_lo[r], P.range_hi[r], etid, kEpi);
           part = warp_sum(part);
-          if (lane == 0) red[warp] = part;
-          bar_named(5, kEpi);
+          if (lane == 0) red[ew] = part;
+          bar_named(13, kEpi);
           float tot = 0.f;
           for (int i = 0; i < kEpi / 32; ++i) tot += red[i];
           const float coef = P.clip / (sqrtf(tot) + 1e-6f);
           o.clip_coef = coef < 1.f ? coef : 1.f;
-          bar_named(5, kEpi);
+          bar_named(13, kEpi);
         }
-        for (int r = 0; r < P.n_ranges; ++r) afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, P.range_lo[r], P.range_hi[r], o, tid, kEpi);
+        for (int r = 0; r < P.n_ranges; ++r) {
+          // two 128-bit chunks per thread and pass: 8 independent loads in flight hide part of the L2 latency of this tail
+          const int64_t lo = P.range_lo[r], hi = P.range_hi[r], span = 4 * (int64_t)kEpi;
+          for (int64_t i = lo + 4 * (int64_t)etid; i < hi; i += 2 * span) {
+            const bool two = i + span < hi;
+            afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, i, i + 4, o, 0, 1);
+            if (two) afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, i + span, i + span + 4, o, 0, 1);
+          }
+        }
         __threadfence_block();
-        bar_named(5, kEpi);
+        bar_named(13, kEpi);
+        TSTAMP();
         load_small();
         fence_async();
-        bar_named(5, kEpi);
+        bar_named(13, kEpi);
         if (lane == 0) mbar_arrive(&bars[B_STEP]);
+        TSTAMP();
       }
     }
-    if (tid == 0) {
+    if (etid == 0) {
       atomicAdd(P.loss_out + 2 * c, loss_acc[0]);
       atomicAdd(P.loss_out + 2 * c + 1, loss_acc[1]);
       P.steps_out[c] = opt_steps;
@@ -1017,7 +1343,12 @@ int make_map3(CUtensorMap* map, const void* base, int64_t d0, int64_t d1, int64_
 
 }  // namespace
 
+static long long* g_tc_dbg = nullptr;
+
 extern "C" {
+
+/* Profiling aid: device buffer of 64 int64 that receives clock64 stamps of the phases of one optimiser step. */
+void afl_tc_set_debug(long long* dev_buf) { g_tc_dbg = dev_buf; }
 
 int afl_tc_stash_floats_per_client(void) { return kNSlot * kSlotF; }
 
@@ -1044,7 +1375,7 @@ int afl_tc_train_round(const int32_t* lay, int lay_words, float* w, float* m, fl
     P.range_lo[r] = ranges[2 * r]; P.range_hi[r] = ranges[2 * r + 1];
     AFL_CHECK_ARG(P.range_lo[r] % 4 == 0 && P.range_hi[r] % 4 == 0 && P.range_hi[r] <= d_pad, "afl_tc_train_round: bad range");
   }
-  P.loss_out = loss_out; P.steps_out = steps_out;
+  P.loss_out = loss_out; P.steps_out = steps_out; P.dbg = g_tc_dbg;
   TcMaps maps;
   const int C = n_clients;
   int rc = 0;

@@ -140,10 +140,31 @@ __global__ void probe_kernel(float* out, long long* cycles, int variant, int a_k
   tc_fence_before();
   __syncthreads();
 
+  if (variant == 10 || variant == 0) {   // issue time of 8 MMAs (K = 64) + commit by one thread, nothing else running
+    tc_fence_after();
+    long long t0 = 0, t1 = 0, t2 = 0;
+    if (tid == 0) {
+      const uint32_t idesc = idesc_tf32(128, 64, 0, 0);
+      const uint64_t ad = desc_k_sw128(smem_u32(sa)), bd = desc_k_sw128(smem_u32(sb));
+      t0 = clock64();
+      for (int ks = 0; ks < 8; ++ks) {
+        if (variant == 10)
+          asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+                       ::"r"(tmem), "r"(tmem + 64 + (ks & 3) * 8), "l"(desc_add(bd, (ks & 3) * 32)), "r"(idesc), "r"((uint32_t)(ks > 0)) : "memory");
+        else umma_tf32(tmem, desc_add(ad, (ks & 3) * 32), desc_add(bd, (ks & 3) * 32), idesc, ks > 0);
+      }
+      umma_commit(&bar);
+      t1 = clock64();
+    }
+    mbar_wait(&bar, 1);
+    if (tid == 0) { t2 = clock64(); cycles[1] = t1 - t0; cycles[2] = t2 - t0; }
+    tc_fence_after();
+    __syncthreads();
+  }
   // ---- latency chain (variant 0 only): 16 dependent phases of [MMA K=64 (8 instr) -> commit -> wait -> ld 64 cols -> st.shared -> fence]
   if (variant == 0) {
     tc_fence_after();
-    uint32_t parity = 1;
+    uint32_t parity = 0;
     long long t0 = clock64();
     for (int it = 0; it < 16; ++it) {
       if (tid == 0) {
@@ -180,7 +201,7 @@ int main(int argc, char** argv) {
   const int only = argc > 1 ? atoi(argv[1]) : -1;
   float* d_out; long long* d_cyc;
   cudaMalloc(&d_out, sizeof(float) * 128 * 64);
-  cudaMalloc(&d_cyc, sizeof(long long));
+  cudaMalloc(&d_cyc, 4 * sizeof(long long));
   std::vector<float> ref(M * N), got(128 * 64);
   for (int m = 0; m < M; ++m)
     for (int n = 0; n < N; ++n) {
@@ -228,6 +249,7 @@ int main(int argc, char** argv) {
       }
       printf("\n");
     }
+    if (vi == 0 || vi == 10) { long long cc[3]; cudaMemcpy(cc, d_cyc, sizeof(cc), cudaMemcpyDeviceToHost); printf("  8 MMAs (128x64x8 tf32, A %s) + commit: issue %lld cycles, issue->complete %lld cycles\n", vi == 10 ? "in TMEM" : "in smem", cc[1], cc[2]); }
     if (vi == 0) { long long c; cudaMemcpy(&c, d_cyc, sizeof(c), cudaMemcpyDeviceToHost); printf("  dependent phase latency: %lld cycles (MMA 128x64x64 tf32 + commit + wait + ld 64 cols + st.shared + fences + bar)\n", c); }
     ++vi;
   }
