@@ -63,16 +63,25 @@ def pairwise_sqdist(rows: torch.Tensor, gram_fn: Optional[GramFn] = None,
     return (d[:, None] + d[None, :] - 2 * g).clamp_min(0)
 
 
-def krum_select(rows: torch.Tensor, f: int = 0, gram_fn: Optional[GramFn] = None) -> int:
-    """Index of the Krum winner: argmin_i of the sum of the ``n-f-2`` smallest ``||v_i-v_j||^2``."""
+def krum_select(rows: torch.Tensor, f: int = 0, gram_fn: Optional[GramFn] = None, reference_slice: bool = False) -> int:
+    """Index of the Krum winner: argmin_i of the sum of the ``n-f-2`` smallest ``||v_i-v_j||^2`` (one top-k, one argmin;
+    no per-client host sync).
+
+    ``reference_slice``: keep the reference's slice semantics for ``n-f-2 < 0`` (``sorted(d)[:n-f-2]`` with a negative
+    bound keeps the first ``len(d) - |n-f-2|`` distances, ``src/Utils.py:326-342``); otherwise the count is clamped at 0.
+    """
     n = rows.shape[0]
     d2 = pairwise_sqdist(rows, gram_fn)
-    m = max(n - f - 2, 0)
-    scores = []
-    for i in range(n):
-        others = torch.cat([d2[i, :i], d2[i, i + 1:]])
-        scores.append(torch.sort(others).values[:m].sum().item())
-    return int(np.argmin(scores))
+    m = n - f - 2
+    if m < 0:
+        m = max((n - 1) + m, 0) if reference_slice else 0
+    m = min(m, n - 1)
+    if m == 0 or n < 2:
+        return 0                                            # every score is 0: argmin returns the first client
+    off = d2.clone()
+    off.fill_diagonal_(float("inf"))                        # a client's distance to itself is not a candidate
+    scores = torch.topk(off, m, dim=1, largest=False).values.sum(1)
+    return int(torch.argmin(scores))
 
 
 def shieldfl_weights(rows: torch.Tensor, gram_fn: Optional[GramFn] = None) -> torch.Tensor:

@@ -54,6 +54,7 @@ class ServerCfg:
     # --- additive keys ---
     common_init: bool = True         # Q4: round-1 START carries one common init (False = reference)
     krum_f: int = 0                  # Q13
+    krum_reference_f: bool = False   # f = int(n * genuine-rate) with the reference's negative-slice semantics (server.py:384)
     max_retries: int = 0             # Q10: 0 = retry forever like the reference
     trim_ratio: float = 0.1          # src/Utils.py:267
     hyper_update: str = "sequential"  # sequential (parity) | batched
@@ -92,6 +93,7 @@ class RuntimeCfg:
     control_host: str = "127.0.0.1"
     backend: str = "auto"            # auto | native | torch  (torch = pure-PyTorch fallback/oracle)
     cta_per_client: int = 0          # 0 = auto
+    trainer: str = "auto"            # auto | ffma (op-program interpreter) | tcgen05 (tensor-core trainer, TransformerModel)
     collectives: str = "fused"       # fused (P2P/multimem kernels) | nccl (debug fall-back)
     synthetic_train_rows: int = 16384
     synthetic_test_rows: int = 4096
@@ -189,6 +191,8 @@ def validate(cfg: Config) -> None:
         raise ValueError(f"attack.search '{cfg.attack.search}' is not valid")
     if s.hyper_update not in ("sequential", "batched"):
         raise ValueError(f"server.hyper-update '{s.hyper_update}' is not valid")
+    if cfg.runtime.trainer not in ("auto", "ffma", "tcgen05"):
+        raise ValueError(f"runtime.trainer '{cfg.runtime.trainer}' is not valid (auto|ffma|tcgen05)")
     for f in cfg.runtime.fault_inject:
         if f.get("kind") not in ("nan-loss", "nan-weights", "stall"):
             raise ValueError(f"runtime.fault-inject kind '{f.get('kind')}' is not valid (nan-loss|nan-weights|stall)")

@@ -150,6 +150,23 @@ class Federation:
                                                          self.device, dropout=l.dropout, module=self.module,
                                                          blocks_per_client=cfg.runtime.cta_per_client)
             self.gpart = z(self.plan.chunk * self.plan.G, self.D)
+        # Tensor-core trainer (csrc/train_tc.cu): one CTA per client, so it wins as soon as the interpreter cannot give
+        # every client 16 blocks (measured on B200: 88 us per optimiser step for any client count up to the SM count,
+        # against 87 us for the interpreter at 8 clients and 943 us at 128).
+        self.trainer = "ffma"
+        self.tc_stash = None
+        want = os.environ.get("ATTACKFL_TRAINER", cfg.runtime.trainer)
+        if backend == "native" and self.device.type == "cuda" and want != "ffma":
+            from .ops import train_tc as TC
+            ok = TC.supported(self.model_name, self.layout, l.batch_size, self.module)
+            if want == "tcgen05" and not ok:
+                raise ValueError("runtime.trainer: tcgen05 supports the default-width TransformerModel with batch <= 128")
+            if ok and (want == "tcgen05" or self.plan.G < 16):
+                self.trainer = "tcgen05"
+                self.TC = TC
+                self.tc_cache: Dict = {}
+                self.tc_gw = z(max(self.CL, 1), self.D)
+                self.tc_stash = z(max(self.CL, 1), TC.stash_floats_per_client(self.device))
 
         # ---- coordinator state (server.py:105-134)
         self.num_round = s.num_round
@@ -267,20 +284,53 @@ class Federation:
     _rows_hold_global = False
 
     # ================================================================================== local training
+    def _cpu_slots(self) -> List[int]:
+        """Local slots whose client registered with ``--device cpu`` while this rank trains on a GPU
+        (``/root/reference/client.py:50-61``: every client picks its own training device)."""
+        if self.device.type != "cuda":
+            return []
+        return [j for j, c in enumerate(self.local) if str(self.specs[c].device or "").startswith("cpu")]
+
     def _train_native(self, sizes_local: List[int]) -> torch.Tensor:
         l = self.cfg.learning
         T = self.T
-        n_data = torch.tensor(sizes_local, dtype=torch.int32, device=self.device)
+        cpu_slots = self._cpu_slots()
+        sizes_dev = [0 if j in cpu_slots else n for j, n in enumerate(sizes_local)]
+        n_data = torch.tensor(sizes_dev, dtype=torch.int32, device=self.device)
         idx = make_round_indices(self.n_train, [max(s, 1) for s in sizes_local], l.epoch, self.dev_gen, self.device)
         self.m[:self.CL].zero_()
         self.v[:self.CL].zero_()
         cids = torch.tensor(self.local, dtype=torch.int32, device=self.device)
         clip_proper = l.clip_mode == "proper" and l.clip_grad_norm > 0
         seed = (int(self.cfg.server.random_seed or 0) << 20) ^ (self.attempt * 2654435761 & 0xFFFFFFFF)
-        loss, steps = T.train_round(self.train_prog, self.plan, self.rows[:self.CL], self.m[:self.CL],
-                                    self.v[:self.CL], self.gpart, self.train_dev, idx, n_data, cids, l.batch_size,
-                                    l.epoch, optimizer=l.optimizer, lr=l.learning_rate, momentum=l.momentum,
-                                    clip_proper=clip_proper, clip=l.clip_grad_norm, seed=seed, dropout=l.dropout)
+        kw = dict(optimizer=l.optimizer, lr=l.learning_rate, momentum=l.momentum, clip_proper=clip_proper,
+                  clip=l.clip_grad_norm, seed=seed, dropout=l.dropout)
+        if self.trainer == "tcgen05":
+            loss, steps = self.TC.train_round_tc(self.layout, self.rows[:self.CL], self.m[:self.CL], self.v[:self.CL],
+                                                 self.tc_gw, self.tc_stash, self.train_dev, idx, n_data, cids,
+                                                 l.batch_size, l.epoch, cache=self.tc_cache, **kw)
+        else:
+            loss, steps = T.train_round(self.train_prog, self.plan, self.rows[:self.CL], self.m[:self.CL],
+                                        self.v[:self.CL], self.gpart, self.train_dev, idx, n_data, cids, l.batch_size,
+                                        l.epoch, **kw)
+        if cpu_slots:
+            # clients that asked for the CPU train on the CPU twin of the same kernel sources (same Philox streams, same
+            # sample indices); their rows are copied out and back in
+            if getattr(self, "_cpu_prog", None) is None:
+                from .models.programs import build_program
+                self._cpu_prog = build_program(self.model_name, self.layout, train=True, dropout=l.dropout, module=self.module)
+                self._cpu_data = self.train_dev.cpu()
+            sel = torch.tensor(cpu_slots, dtype=torch.long, device=self.device)
+            w = self.rows[sel].cpu()
+            m, v = torch.zeros_like(w), torch.zeros_like(w)
+            plan = T.TrainPlan(1, (l.batch_size + self._cpu_prog.S - 1) // self._cpu_prog.S, self._cpu_prog.S, len(cpu_slots))
+            gp = torch.zeros(len(cpu_slots), self.D)
+            closs, _ = T.train_round(self._cpu_prog, plan, w, m, v, gp, self._cpu_data, idx[sel].cpu().contiguous(),
+                                     torch.tensor([sizes_local[j] for j in cpu_slots], dtype=torch.int32),
+                                     torch.tensor([self.local[j] for j in cpu_slots], dtype=torch.int32), l.batch_size,
+                                     l.epoch, **kw)
+            self.rows[sel] = w.to(self.device)
+            loss[sel] = closs.to(self.device)
         return loss
 
     def _train_torch(self, sizes_local: List[int]) -> torch.Tensor:
@@ -521,7 +571,8 @@ class Federation:
             else:
                 self.global_row.copy_(agg.median(sel))
         elif self.mode == "krum":
-            i = agg.krum_select(sel, s.krum_f, gram_fn)
+            kf = int(sel.shape[0] * s.genuine_rate) if s.krum_reference_f else s.krum_f
+            i = agg.krum_select(sel, kf, gram_fn, reference_slice=s.krum_reference_f)
             info["krum_winner"] = reporting[i]
             self.global_row.copy_(sel[i])
         elif self.mode == "shieldfl":
@@ -537,7 +588,12 @@ class Federation:
                 from .ops import flat
                 scores, _ = flat.scion_cosine_distances(sel.contiguous(), self.valid, seed=int(self.cfg.server.random_seed or 0) * 7919 + self.attempt)
                 scores = scores.tolist()
-            out, kept = agg.scionfl(sel, sizes, valid=self.valid.bool(), generator=None, keep=s.scionfl_keep,
+            gen = None
+            if scores is None:
+                # rank-independent stream: every rank of a replicated aggregation must draw the same Bernoulli bits
+                gen = torch.Generator(device=sel.device)
+                gen.manual_seed(int(self.cfg.server.random_seed or 0) * 7919 + self.attempt)
+            out, kept = agg.scionfl(sel, sizes, valid=self.valid.bool(), generator=gen, keep=s.scionfl_keep,
                                     scores=scores)
             info["scionfl_kept"] = [reporting[i] for i in kept]
             self.global_row.copy_(out)
@@ -716,6 +772,9 @@ class Federation:
         s, l = self.cfg.server, self.cfg.learning
         round_no = self.num_round - self.remaining + 1
         t_wall = time.perf_counter()
+        # The rollback snapshot belongs to THIS attempt: a round that fails before aggregation must not restore the
+        # snapshot of an earlier, successful round (that would silently undo a counted and checkpointed update).
+        self._hyper_snap = None
         for _ in self._faults("stall"):                           # exercises the watchdog
             time.sleep(max(self.cfg.runtime.round_timeout_s * 2, 0.2))
         if self.host_train is not None:
@@ -786,6 +845,15 @@ class Federation:
             with self.timer.phase("aggregate"):
                 if fused:
                     self._aggregate_fused(reporting, center, info)
+                    # a peer-barrier time-out leaves glob / lie / the client rows stale: fail the round on every rank
+                    # (the error word is part of the symmetric control block, every rank reads its own copy)
+                    err = self.fused_comm.check_error(raise_on_error=False)
+                    if err:
+                        self._log(f"fused aggregation reported error {err}; the round is discarded", "red")
+                        self.fused_comm.reset_error()
+                        if prev_global is not None:
+                            self.global_row.copy_(prev_global)
+                        info["failed"] = True
                 elif self.mode == "hyper":
                     info.update(self._hyper_round(rows_all, reporting))
                 else:

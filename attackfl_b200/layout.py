@@ -99,15 +99,16 @@ class FlatLayout:
 
     # ------------------------------------------------------------------ conversions
     def flatten(self, sd: Mapping[str, torch.Tensor], out: Optional[torch.Tensor] = None,
-                device=None) -> torch.Tensor:
-        """state_dict -> padded fp32 row (zeros in the padding)."""
+                device=None, strict_shapes: bool = False) -> torch.Tensor:
+        """state_dict -> padded fp32 row (zeros in the padding).  ``strict_shapes``: refuse a tensor whose element count
+        matches but whose shape does not (used for files that come from outside, ``load_pth``)."""
         if out is None:
             out = torch.zeros(self.padded, dtype=torch.float32, device=device)
         else:
             out.zero_()
         for e in self.entries:
             src = sd[e.name]
-            if tuple(src.shape) != e.shape and src.numel() != e.numel:
+            if tuple(src.shape) != e.shape and (strict_shapes or src.numel() != e.numel):
                 raise ValueError(f"shape mismatch for '{e.name}': {tuple(src.shape)} vs {e.shape}")
             out[e.offset:e.offset + e.numel].copy_(src.detach().reshape(-1).to(torch.float32))
         return out
@@ -155,7 +156,7 @@ class FlatLayout:
         missing = [k for k in self.keys() if k not in sd]
         if missing:
             raise KeyError(f"{path}: missing keys {missing[:4]}{'...' if len(missing) > 4 else ''}")
-        return self.flatten(sd, device=device)
+        return self.flatten(sd, device=device, strict_shapes=True)
 
     def describe(self) -> str:
         return f"FlatLayout(T={len(self.entries)}, D={self.numel}, D_pad={self.padded})"

@@ -19,7 +19,9 @@ def gram_torch(a: torch.Tensor) -> torch.Tensor:
 
 
 def gram(a: torch.Tensor, precision: str = "tf32") -> torch.Tensor:
-    if a.is_cuda and precision != "fp32":
+    # the tcgen05 kernel holds the whole R x R tile in one TMEM accumulator: R <= 256 (k + 2 rows for the attacks, one row
+    # per reporter for Krum / ShieldFL / FLTrust); larger problems use the library matmul in fp32
+    if a.is_cuda and precision != "fp32" and a.shape[0] <= 256:
         from . import gram_native
         if gram_native.available():
             return gram_native.gram_tcgen05(a, precision)

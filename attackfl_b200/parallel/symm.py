@@ -138,7 +138,11 @@ class FusedComm:
                                    ctypes.c_int64(sl), ctypes.c_int(1 if mode == "Opt-Fang" else 0), ptr(ops), ptr(mu),
                                    ptr(p), stream_ptr(ops))
         check(lib, rc, "afl_slice_moments")
-        g = gram_native.gram_tcgen05(ops, fed.cfg.attack.gram_precision if fed.cfg.attack.gram_precision != "fp32" else "tf32")
+        prec = fed.cfg.attack.gram_precision
+        if prec == "fp32" or k + 2 > 256:
+            g = ops @ ops.t()                                # configured exact mode (or too many rows for one TMEM tile)
+        else:
+            g = gram_native.gram_tcgen05(ops, prec)
         dist.all_reduce(g)                                   # (k+2)^2 floats: the only cross-rank traffic besides the rows
         g4 = flat.gamma_search(g, k, "sum" if mode == "Min-Sum" else "max", True, paper)
         dst = (ctypes.c_void_p * G)(*[int(b) + slot * D * 4 for b in self.h_craft.buffer_ptrs])
@@ -148,9 +152,19 @@ class FusedComm:
         self._last_gamma = g4
         return self.craft_sym[slot]
 
-    def check_error(self) -> None:
-        if int(self.ctrl[2].item()) != 0:
+    def check_error(self, raise_on_error: bool = True) -> int:
+        """Error word of the fused kernels (non-zero: a cross-GPU flag barrier timed out, the outputs are stale).  The
+        word is summed over ranks so that every rank takes the same decision."""
+        err = self.ctrl[2:3].to(torch.float32)
+        dist.all_reduce(err)
+        code = int(err.item())
+        if code and raise_on_error:
             raise RuntimeError("fused collective timed out waiting for a peer rank")
+        return code
+
+    def reset_error(self) -> None:
+        """Re-arms the kernels after a reported time-out (clears the local grid counter, go flag and error word)."""
+        self.ctrl.zero_()
 
 
 def attach(fed) -> FusedComm:

@@ -40,13 +40,19 @@ __device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
   return v;
 }
 
-// Barrier among the G co-resident blocks of one client (monotonic counter, release/acquire at gpu scope).
-__device__ __forceinline__ void client_barrier(uint32_t* ctr, uint32_t target) {
+// Barrier among the G co-resident blocks of one client (monotonic counter, release/acquire at gpu scope).  The spin is
+// bounded like the cross-GPU barriers of comm.cu: after ~2 s without progress the block raises the NaN flag of the
+// client (loss_out[2c+1], which fails the round on the host) and traps, so a protocol bug cannot hang the GPU.
+__device__ __forceinline__ void client_barrier(uint32_t* ctr, uint32_t target, float* nan_flag) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(ctr, 1u);
-    while (ld_acquire(ctr) < target) { }
+    const long long t0 = clock64();
+    uint32_t it = 0;
+    while (ld_acquire(ctr) < target) {
+      if ((++it & 1023u) == 0u && clock64() - t0 > 4000000000LL) { atomicAdd(nan_flag, 1.0f); __threadfence_system(); __trap(); }
+    }
     __threadfence();
   }
   __syncthreads();
@@ -60,7 +66,7 @@ __device__ __forceinline__ void cluster_barrier() {
 }
 
 #define AFL_CLIENT_BARRIER() do { if (P.use_cluster) { __threadfence(); cluster_barrier(); } \
-  else { bar_target += P.G; client_barrier(bar, bar_target); } } while (0)
+  else { bar_target += P.G; client_barrier(bar, bar_target, P.loss_out + 2 * c + 1); } } while (0)
 
 __global__ void __launch_bounds__(kThreads, 1) train_kernel(TrainParams P) {
   extern __shared__ float4 smem4[];
