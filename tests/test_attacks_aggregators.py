@@ -198,3 +198,31 @@ def test_hyper_step_matches_reference_train_hyper(ref):
     got = fused.export_state_dict()
     for k in want:
         assert torch.allclose(got[k], want[k], atol=2e-6, rtol=1e-5), k
+
+
+def test_krum_vectorised_matches_the_reference_loop():
+    """Vectorised top-k Krum against the reference's Python loop (src/Utils.py:326-342), f = 0 and f > 0."""
+    import numpy as np
+    torch.manual_seed(3)
+    from attackfl_b200.aggregators.core import krum_select
+    for n, f in ((7, 0), (9, 2), (3, 0), (2, 0)):
+        rows = torch.randn(n, 50)
+        vecs = [r.numpy() for r in rows]
+        scores = []
+        for i in range(n):
+            d = sorted(float(np.linalg.norm(vecs[i] - vecs[j]) ** 2) for j in range(n) if j != i)
+            scores.append(sum(d[:n - f - 2]))
+        assert krum_select(rows, f) == int(np.argmin(scores))
+    # negative n - f - 2: the reference's slice keeps len(d) - |n-f-2| distances, the default clamps to 0
+    rows = torch.randn(5, 20)
+    vecs = [r.numpy() for r in rows]
+    f = 4
+    scores = [sum(sorted(float(np.linalg.norm(vecs[i] - vecs[j]) ** 2) for j in range(5) if j != i)[:5 - f - 2]) for i in range(5)]
+    assert krum_select(rows, f, reference_slice=True) == int(np.argmin(scores))
+    assert krum_select(rows, f) == 0
+
+
+def test_gram_falls_back_above_256_rows():
+    from attackfl_b200.ops.gram import gram
+    a = torch.randn(300, 64)
+    assert torch.allclose(gram(a), a @ a.t(), atol=1e-4)

@@ -148,3 +148,29 @@ def test_fault_injection_retries_the_round(tmp_path):
     wd2 = Watchdog(0.05, on_expire=fired.append)
     wd2.arm("x"); wd2.disarm(); time.sleep(0.1)
     assert len(fired) == 1
+
+
+def test_hyper_failed_round_keeps_the_last_successful_hypernet(tmp_path):
+    """A round that fails BEFORE aggregation (client NaN loss) must leave the hyper-network exactly as the previous,
+    successful round left it: the rollback snapshot belongs to the attempt that took it."""
+    cfg = _cfg("hyper", "TransformerModel", 3, rounds=2)
+    cfg.runtime.fault_inject = [{"attempt": 2, "client": 1, "kind": "nan-loss"}]
+    fed = Federation(cfg, [ClientSpec(i) for i in range(3)], device="cpu", workdir=str(tmp_path), verbose=False)
+    r1 = fed.run_round()
+    assert r1.ok
+    after_first = {k: v.clone() for k, v in fed.state_dict().items()}
+    r2 = fed.run_round()
+    assert not r2.ok and r2.round == 2
+    after_failed = fed.state_dict()
+    for k, v in after_first.items():
+        assert torch.equal(v, after_failed[k]), k
+    r3 = fed.run_round()
+    assert r3.ok and r3.round == 2
+
+
+def test_client_device_cpu_is_accepted_on_a_cpu_server(tmp_path):
+    """``client.py --device cpu`` (reference client.py:50-61): on a CPU server it is the server's own path."""
+    cfg = _cfg("fedavg", "TransformerModel", 2, rounds=1)
+    fed = Federation(cfg, [ClientSpec(0, device="cpu"), ClientSpec(1)], device="cpu", workdir=str(tmp_path), verbose=False)
+    assert fed._cpu_slots() == []
+    assert fed.run()[0].ok
