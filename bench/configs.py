@@ -93,7 +93,7 @@ def run_ours(cfg_d, attackers, rounds, warmup, backend="auto"):
            "n_gpus": ctx.world, "clients": C, "rounds": rounds, "warmup": warmup, "model": cfg.server.model,
            "mode": cfg.server.mode, "attackers": {str(k): list(v) for k, v in attackers.items()},
            "phases_ms": {k: round(v, 3) for k, v in phases.items()}, "gpu_launches": native.launch_count(),
-           "metric_last": metric, "plan": ({"G": fed.plan.G, "M": fed.plan.M, "S": fed.plan.S, "chunk": fed.plan.chunk} if getattr(fed, "plan", None)
+           "metric_last": metric, "trainer": getattr(fed, "trainer", None), "plan": ({"G": fed.plan.G, "M": fed.plan.M, "S": fed.plan.S, "chunk": fed.plan.chunk} if getattr(fed, "plan", None)
                                              else {"trainer": "har-native" if fed.har_trainer is not None else "torch"})}
     return out if ctx.rank == 0 else {}
 
