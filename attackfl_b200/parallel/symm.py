@@ -37,7 +37,7 @@ class FusedComm:
         self.rows = symm_mem.empty(self.cpg, D, dtype=torch.float32, device=dev)
         self.glob = symm_mem.empty(D, dtype=torch.float32, device=dev)
         self.lie = symm_mem.empty(self.n_lie, D, dtype=torch.float32, device=dev)
-        self.sig = symm_mem.empty(64, dtype=torch.int32, device=dev)
+        self.sig = symm_mem.empty(2048, dtype=torch.int32, device=dev)     # [2][32 chunks][16 ranks] flag words
         self.part = symm_mem.empty(1 + 2 * min(self.n_lie, MAX_ATT), D, dtype=torch.float32, device=dev)
         self.rows.zero_(); self.lie.zero_(); self.sig.zero_(); self.part.zero_()
         self.rows[:fed.CL].copy_(fed.rows[:fed.CL])
@@ -58,7 +58,7 @@ class FusedComm:
         self.lie_ptrs = PtrArr(*[int(p) for p in self.h_lie.buffer_ptrs])
         self.sig_ptrs = PtrArr(*[int(p) for p in self.h_sig.buffer_ptrs])
         self.part_ptrs = PtrArr(*[int(p) for p in self.h_part.buffer_ptrs])
-        self.ctrl = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.ctrl = torch.zeros(128, dtype=torch.int32, device=dev)            # [2][32] phase counters, then the error word
         self.epoch = 0
         import os
         mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in (self.h_part, self.h_glob, self.h_lie)]
@@ -155,7 +155,7 @@ class FusedComm:
     def check_error(self, raise_on_error: bool = True) -> int:
         """Error word of the fused kernels (non-zero: a cross-GPU flag barrier timed out, the outputs are stale).  The
         word is summed over ranks so that every rank takes the same decision."""
-        err = self.ctrl[2:3].to(torch.float32)
+        err = self.ctrl[64:65].to(torch.float32)
         dist.all_reduce(err)
         code = int(err.item())
         if code and raise_on_error:

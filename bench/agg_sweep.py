@@ -51,7 +51,7 @@ def main():
         D = D // (4 * G * 64) * (4 * G * 64)
         rows = symm_mem.empty(R, D, dtype=torch.float32, device=dev)
         glob = symm_mem.empty(D, dtype=torch.float32, device=dev)
-        sig = symm_mem.empty(64, dtype=torch.int32, device=dev)
+        sig = symm_mem.empty(2048, dtype=torch.int32, device=dev)
         partial = symm_mem.empty(D, dtype=torch.float32, device=dev)
         rows.normal_(); sig.zero_()
         h_rows, h_glob, h_sig, h_part = (symm_mem.rendezvous(t, dist.group.WORLD) for t in (rows, glob, sig, partial))
@@ -59,7 +59,7 @@ def main():
         PA = ctypes.c_void_p * G
         gp, sp = PA(*[int(p) for p in h_glob.buffer_ptrs]), PA(*[int(p) for p in h_sig.buffer_ptrs])
         pp = PA(*[int(p) for p in h_part.buffer_ptrs])
-        ctrl = torch.zeros(4, dtype=torch.int32, device=dev)
+        ctrl = torch.zeros(128, dtype=torch.int32, device=dev)
         w = torch.full((C,), 1.0 / C, device=dev)
         wl = torch.full((R,), 1.0 / C, device=dev)
         epoch = [0]
@@ -124,7 +124,7 @@ def main():
             results.append(rec)
             if rank == 0:
                 print(json.dumps(rec), flush=True)
-        if int(ctrl[2].item()) != 0:
+        if int(ctrl[64].item()) != 0:
             raise RuntimeError("fused collective timed out")
         del rows, glob, sig, part, keep, g1, partial
         torch.cuda.empty_cache()

@@ -17,6 +17,7 @@
 // instead of hanging the GPU.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../include/attackfl_b200.h"
 #include "flat_core.h"
@@ -41,7 +42,8 @@ struct FusedArgs {
   float* glob_mc;                 // NVLS multicast address of the global buffers (null: use P2P stores)
   float* lie_mc;                  // NVLS multicast address of the LIE buffers
   int world, rank;
-  uint32_t epoch;                 // this call uses barrier epochs 2*epoch-1 and 2*epoch
+  uint32_t epoch;                 // flag value of this call (monotonic)
+  int n_chunks;                   // pipeline depth: sub-ranges per owned slice (<= 32, divides the slice into multiples of 4)
   // moments (K2)
   int A;
   const float* ref;               // [d_pad] shift (previous global model, identical on all ranks)
@@ -51,8 +53,7 @@ struct FusedArgs {
   int strict_k1;
   // local phase
   float* local_rows_out;          // [CL][d_pad] fan-out target (nullable)
-  uint32_t* grid_ctr;             // local: blocks arrived (reset by the last block)
-  uint32_t* go_flag;              // local: last barrier epoch published to the local grid
+  uint32_t* grid_ctr;             // local: [2][32] blocks-arrived counters per phase and chunk (reset by the last block)
   int* err;                       // local: set to 1 on spin timeout
 };
 
@@ -83,41 +84,50 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
                ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-// Barrier across all blocks of all ranks: local grid barrier (atomic counter); the last local block signals every
-// peer (st.release.sys into its signal buffer) and waits for every peer's signal, then releases the local grid.
-__device__ __forceinline__ bool cross_gpu_barrier(const FusedArgs& a, uint32_t ep) {
+// ---- chunk-pipelined schedule ------------------------------------------------------------------------------------------
+// Every rank's slice [lo, hi) is cut into NC chunks; "chunk j" is the union over the G owners of sub-range j of their
+// slice, so the three phases of a chunk touch the same coordinates on every rank:
+//   P0(j)  local pre-reduce of this rank's rows over chunk j -> own partial buffer          (local HBM)
+//   P1(j)  owner work on sub-range j of the OWN slice: sum of the G partials (NVLS multimem.ld_reduce or P2P loads),
+//          mean / std / LIE rows, result stored into every rank's global (and LIE) buffer  (NVLink)
+//   P2(j)  fan-out of chunk j of the complete global model to the local client rows         (local HBM)
+// A block runs P0(t), P1(t-1), P2(t-2) in iteration t, so the NVLink phase of one chunk overlaps the HBM phases of its
+// neighbours.  There is no grid-wide or cross-GPU barrier: the last block of a rank to finish P0(j) / P1(j) publishes one
+// flag per peer (st.release.sys, value = epoch) and consumers wait for exactly the G flags they need (ld.acquire.sys,
+// bounded spins).  sig layout per rank: [2][kMaxChunks][kMaxWorld] words; ctrl: [2][kMaxChunks] local counters, then err.
+constexpr int kMaxChunks = 32;
+
+__device__ __forceinline__ bool wait_flags(const uint32_t* flags, int world, uint32_t ep, int* err) {
+  // one thread per block polls; flags[p] >= ep once rank p has published
   __shared__ int s_ok;
-  __threadfence_system();
-  __syncthreads();
   if (threadIdx.x == 0) {
     int ok = 1;
-    const uint32_t arrived = atomicAdd(a.grid_ctr, 1u) + 1u;
-    if (arrived == gridDim.x) {
-      *a.grid_ctr = 0u;
-      __threadfence_system();
-      for (int p = 0; p < a.world; ++p)
-        if (p != a.rank) st_release_sys(a.sig[p] + a.rank, ep);
-      const long long t0 = clock64();
-      for (int p = 0; p < a.world; ++p) {
-        if (p == a.rank) continue;
-        while (ld_acquire_sys(a.sig[a.rank] + p) < ep) {
-          if (clock64() - t0 > kSpinTimeout) { *a.err = 1; ok = 0; break; }
-        }
+    const long long t0 = clock64();
+    for (int p = 0; p < world && ok; ++p) {
+      while (ld_acquire_sys(flags + p) < ep) {
+        if (clock64() - t0 > kSpinTimeout || *reinterpret_cast<volatile int*>(err) != 0) { *err = 1; ok = 0; break; }
       }
-      __threadfence_system();
-      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(a.go_flag), "r"(ok ? ep : 0xFFFFFFFFu) : "memory");
-    } else {
-      const long long t0 = clock64();
-      uint32_t g;
-      while ((g = ld_acquire_gpu(a.go_flag)) < ep) {
-        if (clock64() - t0 > 2 * kSpinTimeout) { *a.err = 1; ok = 0; break; }
-      }
-      if (g == 0xFFFFFFFFu) ok = 0;
     }
     s_ok = ok;
   }
   __syncthreads();
-  return s_ok != 0;
+  const bool ok = s_ok != 0;
+  __syncthreads();
+  return ok;
+}
+
+// A block finished its share of a phase of chunk j: the last one on this rank tells every rank (itself included).
+__device__ __forceinline__ void publish(const FusedArgs& a, uint32_t* counter, int which, int j) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (atomicAdd(counter, 1u) + 1u == gridDim.x) {
+      *counter = 0u;
+      __threadfence_system();
+      for (int p = 0; p < a.world; ++p)
+        st_release_sys(a.sig[p] + ((which * kMaxChunks + j) * kMaxWorld + a.rank), a.epoch);
+    }
+  }
 }
 
 template <int A>
@@ -129,137 +139,167 @@ __global__ void __launch_bounds__(kThreads) fedavg_fused_kernel(FusedArgs a) {
   for (int i = threadIdx.x; i < A * a.CL; i += kThreads) msm[i] = a.member[i];
   __syncthreads();
   const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
-  constexpr int U = A == 0 ? 4 : 1;                  // independent float4 columns per thread (bytes in flight)
-
-  // ---- phase 0: local pre-reduce of this rank's CL rows over ALL coordinates -> own partial buffer (local HBM)
+  constexpr int U = A == 0 ? 4 : (A == 1 ? 2 : 1);   // independent float4 columns per thread (bytes in flight)
+  const int64_t slice = a.hi - a.lo;
+  const int NC = a.n_chunks;
+  const int64_t csz = slice / NC;                    // floats per sub-range (multiple of 4)
   float* mypart = a.part[a.rank];
-  for (int64_t i0 = 4 * tid; i0 < a.d_pad; i0 += 4 * nt * U) {
-    float4 acc[U], s1[A > 0 ? A : 1], s2[A > 0 ? A : 1], rf = afl_f4(0.f);
-#pragma unroll
-    for (int u = 0; u < U; ++u) acc[u] = afl_f4(0.f);
-    if (A > 0) {
-      rf = afl_ld4(a.ref + i0);
-#pragma unroll
-      for (int q = 0; q < A; ++q) { s1[q] = afl_f4(0.f); s2[q] = afl_f4(0.f); }
-    }
-    for (int c = 0; c < a.CL; ++c) {
-      const float* row = a.local_rows_in + (int64_t)c * a.d_pad;
-      const float wc = wsm[c];
-      float4 x[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int64_t i = i0 + (int64_t)u * 4 * nt;
-        x[u] = i < a.d_pad ? afl_ld4(row + i) : afl_f4(0.f);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        acc[u].x += wc * x[u].x; acc[u].y += wc * x[u].y; acc[u].z += wc * x[u].z; acc[u].w += wc * x[u].w;
-      }
-      if (A > 0) {
-        const float dx = x[0].x - rf.x, dy = x[0].y - rf.y, dz = x[0].z - rf.z, dw = x[0].w - rf.w;
-#pragma unroll
-        for (int q = 0; q < A; ++q) {
-          const float mq = msm[q * a.CL + c];
-          s1[q].x += mq * dx; s1[q].y += mq * dy; s1[q].z += mq * dz; s1[q].w += mq * dw;
-          s2[q].x += mq * dx * dx; s2[q].y += mq * dy * dy; s2[q].z += mq * dz * dz; s2[q].w += mq * dw * dw;
-        }
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int64_t i = i0 + (int64_t)u * 4 * nt;
-      if (i < a.d_pad) afl_st4(mypart + i, acc[u]);
-    }
-    if (A > 0) {
-#pragma unroll
-      for (int q = 0; q < A; ++q) {
-        afl_st4(mypart + (int64_t)(1 + 2 * q) * a.d_pad + i0, s1[q]);
-        afl_st4(mypart + (int64_t)(2 + 2 * q) * a.d_pad + i0, s2[q]);
-      }
-    }
-  }
-  if (!cross_gpu_barrier(a, 2 * a.epoch - 1)) return;
+  uint32_t* cnt0 = a.grid_ctr;
+  uint32_t* cnt1 = a.grid_ctr + kMaxChunks;
+  const uint32_t* myflags = a.sig[a.rank];
 
-  // ---- phase 1: owned slice: sum the G partials (P2P loads over NVLink) -> store into every rank (P2P stores)
-  for (int64_t i0 = a.lo + 4 * tid; i0 < a.hi; i0 += 4 * nt * U) {
-    float4 acc[U], s1[A > 0 ? A : 1], s2[A > 0 ? A : 1];
+  for (int t = 0; t < NC + 2; ++t) {
+    // ---------------------------------------------------------------- P0(t): local pre-reduce over chunk t
+    if (t < NC) {
+      // element e of the chunk: owner o = e / csz, offset e % csz inside the sub-range.  One division when the loop starts,
+      // then (owner, offset) advance incrementally: a 64-bit division per 16 bytes would make this streaming loop ALU-bound.
+      const int64_t n = csz * a.world, step = 4 * nt * U;
+      int64_t own[U], off[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) acc[u] = afl_f4(0.f);
-    if (A > 0) {
-#pragma unroll
-      for (int q = 0; q < A; ++q) { s1[q] = afl_f4(0.f); s2[q] = afl_f4(0.f); }
-    }
-    if (a.part_mc) {
-      // in-switch reduction: one multimem.ld_reduce per column returns the sum of the G partials
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int64_t i = i0 + (int64_t)u * 4 * nt;
-        if (i < a.hi) acc[u] = multimem_ld_reduce_add(a.part_mc + i);
-      }
-      if (A > 0) {
-#pragma unroll
-        for (int q = 0; q < A; ++q) {
-          s1[q] = multimem_ld_reduce_add(a.part_mc + (int64_t)(1 + 2 * q) * a.d_pad + i0);
-          s2[q] = multimem_ld_reduce_add(a.part_mc + (int64_t)(2 + 2 * q) * a.d_pad + i0);
-        }
-      }
-    } else {
-      for (int r = 0; r < a.world; ++r) {
-        const float* pr = a.part[r];
-        float4 x[U];
+      for (int u = 0; u < U; ++u) { const int64_t e = 4 * tid + (int64_t)u * 4 * nt; own[u] = e / csz; off[u] = e - own[u] * csz; }
+      for (int64_t e0 = 4 * tid; e0 < n; e0 += step) {
+        float4 acc[U], s1[A > 0 ? A : 1][U], s2[A > 0 ? A : 1][U], rf[U];
+        int64_t idx[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const int64_t i = i0 + (int64_t)u * 4 * nt;
-          x[u] = i < a.hi ? afl_ld4(pr + i) : afl_f4(0.f);
+          idx[u] = own[u] < a.world ? own[u] * slice + (int64_t)t * csz + off[u] : -1;
+          off[u] += step;
+          while (off[u] >= csz) { off[u] -= csz; ++own[u]; }
+          acc[u] = afl_f4(0.f);
+          if (A > 0) {
+            rf[u] = idx[u] >= 0 ? afl_ld4(a.ref + idx[u]) : afl_f4(0.f);
+#pragma unroll
+            for (int q = 0; q < A; ++q) { s1[q][u] = afl_f4(0.f); s2[q][u] = afl_f4(0.f); }
+          }
+        }
+        for (int c = 0; c < a.CL; ++c) {
+          const float* row = a.local_rows_in + (int64_t)c * a.d_pad;
+          const float wc = wsm[c];
+          float4 x[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) x[u] = idx[u] >= 0 ? afl_ld4(row + idx[u]) : afl_f4(0.f);
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            acc[u].x += wc * x[u].x; acc[u].y += wc * x[u].y; acc[u].z += wc * x[u].z; acc[u].w += wc * x[u].w;
+            if (A > 0) {
+              const float dx = x[u].x - rf[u].x, dy = x[u].y - rf[u].y, dz = x[u].z - rf[u].z, dw = x[u].w - rf[u].w;
+#pragma unroll
+              for (int q = 0; q < A; ++q) {
+                const float mq = msm[q * a.CL + c];
+                s1[q][u].x += mq * dx; s1[q][u].y += mq * dy; s1[q][u].z += mq * dz; s1[q][u].w += mq * dw;
+                s2[q][u].x += mq * dx * dx; s2[q][u].y += mq * dy * dy; s2[q][u].z += mq * dz * dz; s2[q][u].w += mq * dw * dw;
+              }
+            }
+          }
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) { acc[u].x += x[u].x; acc[u].y += x[u].y; acc[u].z += x[u].z; acc[u].w += x[u].w; }
-        if (A > 0) {
+        for (int u = 0; u < U; ++u) {
+          if (idx[u] < 0) continue;
+          afl_st4(mypart + idx[u], acc[u]);
+          if (A > 0) {
 #pragma unroll
-          for (int q = 0; q < A; ++q) {
-            const float4 p1 = afl_ld4(pr + (int64_t)(1 + 2 * q) * a.d_pad + i0);
-            const float4 p2 = afl_ld4(pr + (int64_t)(2 + 2 * q) * a.d_pad + i0);
-            s1[q].x += p1.x; s1[q].y += p1.y; s1[q].z += p1.z; s1[q].w += p1.w;
-            s2[q].x += p2.x; s2[q].y += p2.y; s2[q].z += p2.z; s2[q].w += p2.w;
+            for (int q = 0; q < A; ++q) {
+              afl_st4(mypart + (int64_t)(1 + 2 * q) * a.d_pad + idx[u], s1[q][u]);
+              afl_st4(mypart + (int64_t)(2 + 2 * q) * a.d_pad + idx[u], s2[q][u]);
+            }
           }
         }
       }
+      publish(a, cnt0 + t, 0, t);
     }
+    // ---------------------------------------------------------------- P1(t-1): owner reduce + broadcast of sub-range t-1
+    if (t >= 1 && t <= NC) {
+      const int j = t - 1;
+      if (!wait_flags(myflags + (0 * kMaxChunks + j) * kMaxWorld, a.world, a.epoch, a.err)) return;
+      const int64_t b0 = a.lo + (int64_t)j * csz, b1 = b0 + csz;
+      for (int64_t i0 = b0 + 4 * tid; i0 < b1; i0 += 4 * nt * U) {
+        float4 acc[U], s1[A > 0 ? A : 1][U], s2[A > 0 ? A : 1][U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int64_t i = i0 + (int64_t)u * 4 * nt;
-      if (i < a.hi) {
-        if (a.glob_mc) multimem_st(a.glob_mc + i, acc[u]);
-        else
-          for (int r = 0; r < a.world; ++r) afl_st4(a.glob[r] + i, acc[u]);
-      }
-    }
-    if (A > 0) {
-      const float4 rf = afl_ld4(a.ref + i0);
+        for (int u = 0; u < U; ++u) {
+          acc[u] = afl_f4(0.f);
 #pragma unroll
-      for (int q = 0; q < A; ++q) {
-        const float k = a.kcount[q], zz = a.z[q];
-        float4 l;
-#define AFL_LIE1(c) { const float mu = rf.c + s1[q].c / k; float sd; \
+          for (int q = 0; q < (A > 0 ? A : 1); ++q) { s1[q][u] = afl_f4(0.f); s2[q][u] = afl_f4(0.f); }
+        }
+        if (a.part_mc) {
+          // in-switch reduction: one multimem.ld_reduce per column returns the sum of the G partials
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t i = i0 + (int64_t)u * 4 * nt;
+            if (i < b1) {
+              acc[u] = multimem_ld_reduce_add(a.part_mc + i);
+#pragma unroll
+              for (int q = 0; q < A; ++q) {
+                s1[q][u] = multimem_ld_reduce_add(a.part_mc + (int64_t)(1 + 2 * q) * a.d_pad + i);
+                s2[q][u] = multimem_ld_reduce_add(a.part_mc + (int64_t)(2 + 2 * q) * a.d_pad + i);
+              }
+            }
+          }
+        } else {
+          for (int r = 0; r < a.world; ++r) {
+            const float* pr = a.part[r];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int64_t i = i0 + (int64_t)u * 4 * nt;
+              if (i < b1) {
+                const float4 x = afl_ld4(pr + i);
+                acc[u].x += x.x; acc[u].y += x.y; acc[u].z += x.z; acc[u].w += x.w;
+#pragma unroll
+                for (int q = 0; q < A; ++q) {
+                  const float4 p1 = afl_ld4(pr + (int64_t)(1 + 2 * q) * a.d_pad + i);
+                  const float4 p2 = afl_ld4(pr + (int64_t)(2 + 2 * q) * a.d_pad + i);
+                  s1[q][u].x += p1.x; s1[q][u].y += p1.y; s1[q][u].z += p1.z; s1[q][u].w += p1.w;
+                  s2[q][u].x += p2.x; s2[q][u].y += p2.y; s2[q][u].z += p2.z; s2[q][u].w += p2.w;
+                }
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t i = i0 + (int64_t)u * 4 * nt;
+          if (i >= b1) continue;
+          if (a.glob_mc) multimem_st(a.glob_mc + i, acc[u]);
+          else
+            for (int r = 0; r < a.world; ++r) afl_st4(a.glob[r] + i, acc[u]);
+          if (A > 0) {
+            const float4 rf = afl_ld4(a.ref + i);
+#pragma unroll
+            for (int q = 0; q < A; ++q) {
+              const float k = a.kcount[q], zz = a.z[q];
+              float4 l;
+#define AFL_LIE1(c) { const float mu = rf.c + s1[q][u].c / k; float sd; \
           if (k < 2.f) sd = a.strict_k1 ? NAN : 0.f; \
-          else { const float var = (s2[q].c - s1[q].c * s1[q].c / k) / (k - 1.f); sd = sqrtf(var > 0.f ? var : 0.f); } \
+          else { const float var = (s2[q][u].c - s1[q][u].c * s1[q][u].c / k) / (k - 1.f); sd = sqrtf(var > 0.f ? var : 0.f); } \
           l.c = mu + zz * sd; }
-        AFL_LIE1(x) AFL_LIE1(y) AFL_LIE1(z) AFL_LIE1(w)
+              AFL_LIE1(x) AFL_LIE1(y) AFL_LIE1(z) AFL_LIE1(w)
 #undef AFL_LIE1
-        if (a.lie_mc) multimem_st(a.lie_mc + (int64_t)q * a.d_pad + i0, l);
-        else
-          for (int r = 0; r < a.world; ++r) afl_st4(a.lie[r] + (int64_t)q * a.d_pad + i0, l);
+              if (a.lie_mc) multimem_st(a.lie_mc + (int64_t)q * a.d_pad + i, l);
+              else
+                for (int r = 0; r < a.world; ++r) afl_st4(a.lie[r] + (int64_t)q * a.d_pad + i, l);
+            }
+          }
+        }
+      }
+      publish(a, cnt1 + j, 1, j);
+    }
+    // ---------------------------------------------------------------- P2(t-2): fan chunk t-2 out to the local client rows
+    if (t >= 2) {
+      const int j = t - 2;
+      // the flags are awaited even without a fan-out target: the call must not return before every owner has delivered
+      if (!wait_flags(myflags + (1 * kMaxChunks + j) * kMaxWorld, a.world, a.epoch, a.err)) return;
+      if (a.local_rows_out != nullptr) {
+        const float* g = a.glob[a.rank];
+        const int64_t n = csz * a.world, step = 4 * nt;
+        int64_t own = (4 * tid) / csz, off = 4 * tid - own * csz;
+        for (int64_t e = 4 * tid; e < n; e += step) {
+          const int64_t i = own * slice + (int64_t)j * csz + off;
+          off += step;
+          while (off >= csz) { off -= csz; ++own; }
+          const float4 v = afl_ld4(g + i);
+          for (int c = 0; c < a.CL; ++c) afl_st4(a.local_rows_out + (int64_t)c * a.d_pad + i, v);
+        }
       }
     }
-  }
-  if (!cross_gpu_barrier(a, 2 * a.epoch)) return;
-  if (a.local_rows_out == nullptr) return;
-
-  // ---- phase 2: fan the complete global model out to this rank's client rows (local HBM only)
-  const float* g = a.glob[a.rank];
-  for (int64_t i = 4 * tid; i < a.d_pad; i += 4 * nt) {
-    const float4 v = afl_ld4(g + i);
-    for (int c = 0; c < a.CL; ++c) afl_st4(a.local_rows_out + (int64_t)c * a.d_pad + i, v);
   }
 }
 
@@ -342,8 +382,9 @@ int afl_craft_scatter(float* const* dst, int world, const float* mu, const float
 
 // Fused multi-GPU FedAvg (+ LIE moments), two levels in one kernel.  local_rows [CL][d_pad] and weights/member cover
 // the LOCAL clients; part/glob/lie/sig are host arrays of `world` peer-mapped device pointers (part: [1+2A][d_pad]
-// per rank).  ctrl: local device memory, 4 x uint32 {grid_ctr, go_flag, err, pad}, zero-initialised once.  epoch must
-// increase by one per call on every rank.  A <= 4 per call.  part_mc / glob_mc / lie_mc: NVLS multicast addresses of the
+// per rank).  ctrl: local device memory, 65 x uint32 {[2][32] phase counters, err}, zero-initialised once; sig: symmetric
+// uint32 buffers of at least 2 * 32 * 16 words (zero-initialised once).  epoch must increase by one per call on every rank.
+// A <= 4 per call.  part_mc / glob_mc / lie_mc: NVLS multicast addresses of the
 // same symmetric buffers (null => P2P loads / stores); with them phase 1 uses multimem.ld_reduce / multimem.st.
 int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int64_t d_pad, int world, int rank,
                      float* const* part, float* const* glob, float* const* lie, uint32_t* const* sig, uint32_t epoch,
@@ -365,7 +406,16 @@ int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int6
   a.part_mc = part_mc; a.glob_mc = glob_mc; a.lie_mc = (lie && A > 0) ? lie_mc : nullptr;
   a.world = world; a.rank = rank; a.epoch = epoch; a.A = A; a.ref = ref; a.member = member; a.kcount = kcount;
   a.z = z; a.strict_k1 = strict_k1; a.local_rows_out = local_rows_out;
-  a.grid_ctr = ctrl; a.go_flag = ctrl + 1; a.err = reinterpret_cast<int*>(ctrl + 2);
+  a.grid_ctr = ctrl; a.err = reinterpret_cast<int*>(ctrl + 2 * kMaxChunks);
+  // pipeline depth: a chunk costs three flag hand-offs (~10 us), so sub-ranges are kept >= 8 MiB; at most 8 chunks
+  // (ATTACKFL_FUSED_CHUNKS overrides, 1..32); sub-ranges stay multiples of 4 floats
+  int nc = (int)(slice * 4 / (8 << 20));
+  if (nc > 8) nc = 8;
+  if (const char* ev = getenv("ATTACKFL_FUSED_CHUNKS")) nc = atoi(ev);
+  if (nc < 1) nc = 1;
+  if (nc > kMaxChunks) nc = kMaxChunks;
+  while (nc > 1 && (slice % (4 * (int64_t)nc)) != 0) --nc;
+  a.n_chunks = nc;
   const size_t smem = sizeof(float) * (size_t)(CL + A * CL + 2);
   void* args[] = {&a};
   cudaStream_t st = (cudaStream_t)stream;

@@ -40,14 +40,15 @@ int afl_fedavg(const float* rows, const float* weights, int C, int64_t d_pad, fl
                float* sd, float* lie, int strict_k1, void* stream);
 
 /* K1-fused — multi-GPU FedAvg over NVLink peer memory in one kernel per rank (server.py:751-775 reduce +
- * :588-614 broadcast).  Two levels: local pre-reduce of this rank's rows (local_rows [CL][d_pad],
- * weights/member for the LOCAL clients) into its symmetric partial buffer, flag barrier, then rank r sums slice r of
- * the G partials through peer-mapped pointers (part [world], each [1+2A][d_pad]), stores the result into every
- * rank's global buffer (glob [world]) and the LIE rows of up to 4 attackers (lie [world], [A][d_pad]), second barrier
- * (sig [world]: symmetric uint32 buffers, st.release.sys / ld.acquire.sys) and fan-out to local_rows_out.
- * ctrl: 4 zero-initialised local uint32 {grid counter, go flag, error, pad}; epoch increases by 1 per call.
- * part_mc / glob_mc / lie_mc: NVLS multicast addresses of the same buffers (null: P2P); when given, the slice reduce is
- * multimem.ld_reduce (in-switch sum) and the broadcast is multimem.st. */
+ * :588-614 broadcast).  Rank r owns coordinate slice r; the slice is cut into up to 32 chunks and every
+ * block walks a three-stage software pipeline over them: local pre-reduce of this rank's rows (local_rows [CL][d_pad],
+ * weights/member for the LOCAL clients) into its symmetric partial buffer, owner sum of the G partials through
+ * peer-mapped pointers (part [world], each [1+2A][d_pad]) with the result (and the LIE rows of up to 4 attackers, lie
+ * [world], [A][d_pad]) stored into every rank's buffers (glob [world]), fan-out to local_rows_out.  No grid-wide or
+ * cross-GPU barrier: per-chunk flags in sig [world] (symmetric uint32 buffers of >= 1024 words, zero-initialised once;
+ * st.release.sys / ld.acquire.sys, bounded spins).  ctrl: 65 zero-initialised local uint32 {[2][32] phase counters, error};
+ * epoch increases by 1 per call.  part_mc / glob_mc / lie_mc: NVLS multicast addresses of the same buffers (null: P2P);
+ * when given, the slice reduce is multimem.ld_reduce (in-switch sum) and the broadcast is multimem.st. */
 int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int64_t d_pad, int world, int rank,
                      float* const* part, float* const* glob, float* const* lie, uint32_t* const* sig, uint32_t epoch,
                      int A, const float* ref, const float* member, const float* kcount, const float* z, int strict_k1,

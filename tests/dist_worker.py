@@ -18,7 +18,7 @@ def main():
     attack = sys.argv[3] if len(sys.argv) > 3 else ""
     device = os.environ.get("AFL_TEST_DEVICE", "cpu")
     ctx = pctx.init_from_env(device)
-    n = 6
+    n = int(os.environ.get("AFL_TEST_CLIENTS", "6"))
     cfg = from_dict({"server": {"num-round": int(os.environ.get("AFL_TEST_ROUNDS", "2")), "clients": n, "mode": mode, "model": "TransformerModel", "data-name": "ICU",
                                 "data-distribution": {"num-data-range": [200, 260]}, "random-seed": 1},
                      "learning": {"epoch": 1, "batch-size": 64, "learning-rate": 0.004, "hyper-lr": 0.001,
@@ -52,6 +52,7 @@ def main():
            "absmax": float(glob.abs().max()), "local": fed.local, "fused": fed.fused_comm is not None}
     with open(f"{out}.rank{ctx.rank}.json", "w") as fh:
         json.dump(rec, fh)
+    torch.save(glob.detach().float().cpu(), f"{out}.rank{ctx.rank}.pt")           # full vector: compared element-wise
     fed.close()
     if ctx.distributed:
         torch.distributed.barrier()
