@@ -270,7 +270,13 @@ class Federation:
         if self.mode == "hyper":
             with self.timer.phase("hyper_emit"):
                 loc = [c for c in starting if c in self.local]
-                if loc:
+                if self._hyper_sharded():
+                    # every rank emits its row shard of every starting client's model straight into the client's row
+                    if not self._rows_hold_theta:
+                        self.native_hyper.emit_rows(starting, [self.fused_comm.row_ptr(c) for c in starting])
+                        torch.cuda.synchronize(self.device)
+                        self.ctx.barrier()
+                elif loc:
                     if self.native_hyper is not None:
                         theta = self.native_hyper.emit(loc)
                     else:
@@ -280,8 +286,13 @@ class Federation:
         elif self.have_global and not self._rows_hold_global:
             self.rows[:self.CL].copy_(self.global_row[None].expand(self.CL, self.D))
         self._rows_hold_global = False
+        self._rows_hold_theta = False
 
     _rows_hold_global = False
+    _rows_hold_theta = False
+
+    def _hyper_sharded(self) -> bool:
+        return self.fused_comm is not None and getattr(self.fused_comm, "hyper_sharded", False)
 
     # ================================================================================== local training
     def _cpu_slots(self) -> List[int]:
@@ -682,7 +693,21 @@ class Federation:
         snap = self.hyper.snapshot()          # detection rollback (server.py:297-298) and failed-round rollback (Q10)
         self._hyper_snap = snap
         order = [c for c in self.selected if c in reporting]
-        if self.native_hyper is not None and s.hyper_update == "sequential":
+        if self._hyper_sharded():
+            # multi-GPU: row-sharded head, one persistent kernel per rank; client rows are read in place over NVLink and
+            # the personalised models are scattered back into the owners' rows (no all-gather)
+            nh = self.native_hyper
+            nh.round(order, [self.fused_comm.row_ptr(c) for c in order], l.hyper_lr, l.clip_grad_norm)
+            nh.emit_rows(reporting, [self.fused_comm.row_ptr(c) for c in reporting])      # server.py:674-678
+            torch.cuda.synchronize(self.device)
+            if nh.check_round_error():
+                info["failed"] = True
+            self.ctx.barrier()
+            self._rows_hold_theta = True
+        elif self.native_hyper is not None and s.hyper_update == "sequential" and self.device.type == "cuda":
+            # one persistent launch for all clients of the round (4 launches per client before)
+            self.native_hyper.round(order, [rows_all[c].data_ptr() for c in order], l.hyper_lr, l.clip_grad_norm)
+        elif self.native_hyper is not None and s.hyper_update == "sequential":
             for c in order:
                 self.native_hyper.step(c, rows_all[c].contiguous(), l.hyper_lr, l.clip_grad_norm)
         else:
@@ -709,6 +734,18 @@ class Federation:
     # ================================================================================== validation
     def _validate(self, reporting: List[int]) -> bool:
         if self.data_name == "ICU":
+            if self.mode == "hyper" and self._hyper_sharded():
+                # personalised models already sit in their owners' rows: every rank scores its own clients, the
+                # probabilities (n_test floats per client) are gathered and pooled into one ROC-AUC like test_hyper_icu
+                n_rep = len(reporting)
+                mine = [j for j, c in enumerate(self.local) if c < n_rep]
+                cpg = self.ctx.clients_per_rank(self.C)
+                probs_loc = torch.zeros(cpg, self.test_dev.shape[0], device=self.device)
+                if mine:
+                    probs_loc[:len(mine)] = self.T.infer(self.infer_prog, self.rows[mine].contiguous(), self.test_dev)
+                probs_all = self.ctx.all_gather_rows(probs_loc, self.C)[:n_rep]
+                labels = self.test_labels[None].expand(probs_all.shape[0], -1)
+                return self.validator.score_icu(probs_all.reshape(-1), labels.reshape(-1))
             if self.mode == "hyper":
                 ids = list(range(len(reporting)))                 # test_hyper(hnet, len(all_model_parameters))
                 if self.native_hyper is not None:
@@ -828,6 +865,8 @@ class Federation:
         gram_sliced = fused and self.cfg.attack.metric == "flat" and self.have_global
         need_gather = (not fused) or (any(sp.attack and sp.attack_mode in GRAM_MODES for sp in self.specs)
                                       and not gram_sliced)
+        if self._hyper_sharded() and not any(sp.attack for sp in self.specs):
+            need_gather = False                                   # rows are read in place by the sharded hyper kernel
         rows_all = None
         if need_gather:
             with self.timer.phase("gather"):
@@ -878,6 +917,8 @@ class Federation:
                     self.native_hyper.pack()
         else:
             self.failures_in_a_row = 0
+            if self._hyper_sharded() and self.fused_comm.any_rank_saves:
+                self.fused_comm.hyper_sync_full()                # every rank joins; rank 0 then writes the .pth
             if self.save and self.ctx.rank == 0:
                 self.save_checkpoint()
             self.remaining -= 1
@@ -923,6 +964,8 @@ class Federation:
     def state_dict(self) -> Dict[str, torch.Tensor]:
         """Current global model (or, in hyper mode, the hyper-network) with the reference's keys."""
         if self.mode == "hyper":
+            if self._hyper_sharded():
+                self.fused_comm.hyper_sync_full()
             if self.native_hyper is not None:
                 self.native_hyper.unpack()
             return self.hyper.export_state_dict()

@@ -241,3 +241,70 @@ class NativeHyper:
 
     def embedding(self, i: int) -> torch.Tensor:
         return self.small[i * self.E:(i + 1) * self.E].view(1, self.E).clone()
+
+    # ------------------------------------------------------------------ persistent / row-sharded round (csrc/hyper_round.cu)
+    def setup_round(self, lo: int = 0, hi: Optional[int] = None, world: int = 1, rank: int = 0, n_max: int = 0,
+                    xchg_ptrs=None, sig_ptrs=None) -> None:
+        """Row shard ``[lo, hi)`` of the head owned by this rank (``world`` ranks) and the symmetric exchange / flag
+        buffers (host arrays of peer-mapped pointers) for up to ``n_max`` clients per round."""
+        dev = self.small.device
+        hi = self.fused.layout.padded if hi is None else hi
+        self.lo, self.hi, self.world, self.rank = int(lo), int(hi), int(world), int(rank)
+        self.n_max = int(n_max) if n_max else self.n_nodes
+        self.xchg_ptrs, self.sig_ptrs = xchg_ptrs, sig_ptrs
+        self.small_alt = torch.zeros(self.tot, dtype=torch.float32, device=dev)
+        self.delta_s = torch.zeros(self.hi - self.lo, dtype=torch.float32, device=dev)
+        self.red2 = torch.zeros(2 * (self.H + 1), dtype=torch.float32, device=dev)
+        self.bar = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.norms = torch.zeros(self.n_max, dtype=torch.float32, device=dev)
+        self.f_all = torch.zeros(self.n_max * self.H, dtype=torch.float32, device=dev)
+        self.round_epoch = 0
+
+    def _shards(self):
+        lo, hi = self.lo, self.hi
+        return (self.head_w[lo:hi], self.head_b[lo:hi], self.mw[lo:hi], self.vw[lo:hi], self.mb[lo:hi], self.vb[lo:hi])
+
+    def round(self, order: Sequence[int], theta_ptrs: Sequence[int], lr: float, clip: float) -> torch.Tensor:
+        """All sequential pFedHN steps of one round (``server.py:644-670``) in ONE launch on this rank's row shard.
+        ``theta_ptrs[j]``: device address of the full row of client ``order[j]`` (peer-mapped on other ranks).
+        Returns the pre-clip gradient norms (device tensor, no host sync)."""
+        if getattr(self, "lo", None) is None:
+            self.setup_round()
+        lib = lib_for(self.small)
+        dev = self.small.device
+        n = len(order)
+        assert n <= self.n_max
+        od = torch.as_tensor(list(order), dtype=torch.int32, device=dev)
+        tp = torch.as_tensor([int(p) for p in theta_ptrs], dtype=torch.int64, device=dev)
+        hw, hb, mw, vw, mb, vb = self._shards()
+        self.round_epoch += 1
+        rc = lib.afl_hyper_round(ptr(hw), ptr(hb), ptr(mw), ptr(vw), ptr(mb), ptr(vb), c_i64(self.hi - self.lo),
+                                 c_i64(self.lo), ptr(self.small), ptr(self.small_alt), c_i(self.n_nodes), c_i(self.E),
+                                 c_i(self.H), ptr(od), ptr(tp), c_i(n), ptr(self.delta_s), ptr(self.red2),
+                                 self.xchg_ptrs, self.sig_ptrs, c_i(self.world), c_i(self.rank), c_i(self.n_max),
+                                 ctypes.c_uint32(self.round_epoch), ptr(self.bar), c_i(self.fused.step), c_f(lr),
+                                 c_f(BETAS[0]), c_f(BETAS[1]), c_f(EPS), c_f(clip), ptr(self.norms), stream_ptr(self.small))
+        check(lib, rc, "afl_hyper_round")
+        self.fused.step += n
+        return self.norms[:n]
+
+    def emit_rows(self, clients: Sequence[int], theta_ptrs: Sequence[int], chunk: int = 64) -> None:
+        """K5a scatter: this rank's row shard of ``theta_j = h(clients[j])`` stored straight into the clients' rows."""
+        if getattr(self, "lo", None) is None:
+            self.setup_round()
+        lib = lib_for(self.small)
+        dev = self.small.device
+        hw, hb = self.head_w[self.lo:self.hi], self.head_b[self.lo:self.hi]
+        cl = torch.as_tensor(list(clients), dtype=torch.int32, device=dev)
+        tp = torch.as_tensor([int(p) for p in theta_ptrs], dtype=torch.int64, device=dev)
+        for c0 in range(0, len(clients), chunk):
+            c1 = min(len(clients), c0 + chunk)
+            if self.f_all.numel() < (c1 - c0) * self.H:
+                self.f_all = torch.zeros((c1 - c0) * self.H, dtype=torch.float32, device=dev)
+            rc = lib.afl_hyper_emit_rows(ptr(hw), ptr(hb), c_i64(self.hi - self.lo), c_i64(self.lo), ptr(self.small),
+                                         c_i(self.n_nodes), c_i(self.E), c_i(self.H), ptr(cl[c0:c1]), c_i(c1 - c0),
+                                         ptr(self.f_all), ptr(tp[c0:c1]), stream_ptr(self.small))
+            check(lib, rc, "afl_hyper_emit_rows")
+
+    def check_round_error(self) -> int:
+        return int(self.bar[1].item())

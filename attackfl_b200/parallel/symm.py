@@ -67,6 +67,40 @@ class FusedComm:
         want = os.environ.get("ATTACKFL_NVLS", "auto")
         self.multicast = all(mc) and (want == "1" or (want == "auto" and self.world >= 4))
         self.mc_part, self.mc_glob, self.mc_lie = mc if self.multicast else (0, 0, 0)
+        # hyper mode: row-sharded head, one persistent kernel per rank and round (csrc/hyper_round.cu)
+        self.hyper_sharded = False
+        nh = getattr(fed, "native_hyper", None)
+        if fed.mode == "hyper" and nh is not None and fed.cfg.server.hyper_update == "sequential":
+            lib = native.cuda_lib()
+            lib.afl_hyper_round_xchg_floats.restype = ctypes.c_int64
+            lib.afl_hyper_round_sig_words.restype = ctypes.c_int64
+            n_max = fed.C
+            self.hx = symm_mem.empty(int(lib.afl_hyper_round_xchg_floats(n_max, self.world, nh.H)), dtype=torch.float32, device=dev)
+            self.hs = symm_mem.empty(int(lib.afl_hyper_round_sig_words(n_max, self.world)), dtype=torch.int32, device=dev)
+            self.hx.zero_(); self.hs.zero_()
+            self.h_hx = symm_mem.rendezvous(self.hx, group)
+            self.h_hs = symm_mem.rendezvous(self.hs, group)
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            sl = D // self.world
+            nh.setup_round(self.rank * sl, (self.rank + 1) * sl, self.world, self.rank, n_max,
+                           PtrArr(*[int(p) for p in self.h_hx.buffer_ptrs]), PtrArr(*[int(p) for p in self.h_hs.buffer_ptrs]))
+            self.hyper_sharded = True
+            flag = torch.tensor([1.0 if fed.save else 0.0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+            self.any_rank_saves = bool(flag.item() > 0)       # checkpoints need the shards gathered: a collective
+
+    def row_ptr(self, client: int) -> int:
+        """Device address of a client's row on this rank's view of its owner's arena (peer-mapped)."""
+        return int(self.h_rows.buffer_ptrs[client // self.cpg]) + (client % self.cpg) * self.fed.D * 4
+
+    def hyper_sync_full(self) -> None:
+        """Checkpoint / export only: gathers every rank's row shard of the head and its Adam moments into the full
+        tensors (NCCL; off the round path)."""
+        nh = self.fed.native_hyper
+        for t in (nh.head_w, nh.head_b, nh.mw, nh.vw, nh.mb, nh.vb):
+            parts = t.view(self.world, -1)
+            dist.all_gather_into_tensor(parts, parts[self.rank].clone())
 
     def fedavg(self, weights: torch.Tensor, member: Optional[torch.Tensor] = None, z: Optional[torch.Tensor] = None,
                ref: Optional[torch.Tensor] = None, strict_k1: bool = False) -> Optional[torch.Tensor]:

@@ -183,6 +183,27 @@ int afl_gram_bf16(const float* A, int R, int64_t D, int64_t lda, void* a16, floa
 int afl_gram_tf32_workspace(int R, int64_t D, int64_t* partial_floats);
 int afl_gram_tf32(const float* A, int R, int64_t D, int64_t lda, float* partials, float* G, void* stream);
 
+/* K5 persistent + row-sharded: one cooperative launch per rank walks all reporting clients of a round in order
+ * (server.py:637-678).  head_w / head_b / mw / vw / mb / vb are THIS rank's row shard (row 0 = global row lo, `rows` rows);
+ * `small` = params | m | v of the replicated MLP + embedding table, `small_alt` [tot] a second copy of the parameters
+ * (double buffer inside the launch).  order_dev [n]: client ids; theta_dev [n]: device array of the clients' row base
+ * pointers (may be peer-mapped: the kernel reads rows [lo, lo + rows) where they live).  Multi-GPU: xchg / sig are host
+ * arrays of `world` peer-mapped symmetric buffers (afl_hyper_round_xchg_floats / _sig_words for n_max clients), epoch
+ * increases by 1 per call; world = 1: both may be null.  delta [rows], red [2][H+1], bar [2] are local scratch (bar[1] != 0
+ * after the call: a spin timed out).  step0: Adam steps taken before this call.  norms [n]: pre-clip gradient norms. */
+int64_t afl_hyper_round_xchg_floats(int n_max, int world, int H);
+int64_t afl_hyper_round_sig_words(int n_max, int world);
+int afl_hyper_round(float* head_w, float* head_b, float* mw, float* vw, float* mb, float* vb, int64_t rows, int64_t lo,
+                    float* small, float* small_alt, int n_nodes, int E, int H, const int* order_dev,
+                    const float* const* theta_dev, int n, float* delta, float* red, float* const* xchg,
+                    uint32_t* const* sig, int world, int rank, int n_max, uint32_t epoch, uint32_t* bar, int step0, float lr,
+                    float b1, float b2, float eps, float clip, float* norms, void* stream);
+/* K5a scatter: theta_j[lo + d] = W_h[d] . MLP(E[clients[j]]) + b_h[d] on the owned rows, stored through the pointer table
+ * theta_dev [n] (peer-mapped pointers scatter the personalised models to their owner ranks, server.py:589-590,674-678). */
+int afl_hyper_emit_rows(const float* head_w, const float* head_b, int64_t rows, int64_t lo, const float* small, int n_nodes,
+                        int E, int H, const int* clients_dev, int n, float* f_scratch, float* const* theta_dev,
+                        void* stream);
+
 /* Allocation-free variant of afl_hyper_step (no counterpart in the reference: it exists for callers of THIS
  * library that may not allocate device memory -- pre-reserved real-time loops, plugins inside another runtime's
  * memory budget, host callbacks that must not trigger a device synchronisation).  Identical arithmetic and

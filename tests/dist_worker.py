@@ -46,6 +46,8 @@ def main():
                     return _inner(*a, **k)
                 setattr(comm, name, delayed)
     res = fed.run()
+    if mode == "hyper":
+        fed.state_dict()                      # gathers the row shards of a sharded head (no-op otherwise)
     glob = fed.global_row if mode != "hyper" else fed.hyper.head_b
     rec = {"rank": ctx.rank, "world": ctx.world, "ok": [r.ok for r in res], "metric": [r.metric for r in res],
            "attackers": [r.attackers for r in res], "checksum": float(glob.double().sum()),

@@ -67,6 +67,28 @@ def test_gpus_fused_matches_nccl_path(tmp_path, attack, world):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 8])
+def test_gpus_sharded_hyper_matches_gathered_path(tmp_path, world):
+    """Hyper mode: row-sharded head + persistent per-rank kernel reading client rows in place (collectives: fused) vs the
+    all-gather + replicated per-client steps (collectives: nccl).  Full head-bias vectors compared."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    out = {}
+    for collectives in ("nccl", "fused"):
+        d = tmp_path / collectives
+        d.mkdir()
+        recs = _launch(d, world, "hyper", "", {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives,
+                                               "AFL_TEST_CLIENTS": "8", "AFL_TEST_ROUNDS": "3"})
+        a = recs[0]
+        assert a["ok"] == [True] * 3
+        out[collectives] = a
+    diff = float((out["fused"]["vector"] - out["nccl"]["vector"]).abs().max())
+    scale = float(out["nccl"]["vector"].abs().max())
+    assert diff <= 1e-4 * max(scale, 1.0), (diff, scale)
+    assert out["fused"]["metric"] == pytest.approx(out["nccl"]["metric"], abs=5e-3)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_fused_kernel_against_torch_and_flag_stress(tmp_path, world):
     """afl_fedavg_fused itself: one-chunk and multi-chunk pipelines, P2P and NVLS, 1 / 3 rows per rank, LIE moment sets,
