@@ -219,6 +219,18 @@ class NativeHyper:
         out = torch.empty(n, d_pad, dtype=torch.float32, device=dev) if out is None else out
         cl = torch.as_tensor(list(clients), dtype=torch.int32, device=dev)
         f = torch.empty(max(n, 1) * self.H, dtype=torch.float32, device=dev)
+        if dev.type == "cuda":
+            # same arithmetic as pass A of the round kernel (csrc/hyper_round.cu): a coordinate the client did not change
+            # then has delta == 0 exactly, as in the reference (theta - theta_client of identical tensors), instead of
+            # rounding noise that Adam would normalise to +-lr
+            tp = torch.as_tensor([out[j].data_ptr() for j in range(n)], dtype=torch.int64, device=dev)
+            for c0 in range(0, n, chunk):
+                c1 = min(n, c0 + chunk)
+                rc = lib.afl_hyper_emit_rows(ptr(self.head_w), ptr(self.head_b), c_i64(d_pad), c_i64(0), ptr(self.small),
+                                             c_i(self.n_nodes), c_i(self.E), c_i(self.H), ptr(cl[c0:c1]), c_i(c1 - c0),
+                                             ptr(f), ptr(tp[c0:c1]), stream_ptr(self.small))
+                check(lib, rc, "afl_hyper_emit_rows")
+            return out
         for c0 in range(0, n, chunk):
             c1 = min(n, c0 + chunk)
             rc = lib.afl_hyper_emit(ptr(self.head_w), ptr(self.head_b), ptr(self.small), c_i(self.n_nodes), c_i(self.E),
