@@ -48,12 +48,149 @@ def _write_datasets(workdir: str, train_rows: int, test_rows: int):
         pickle.dump(to_ref(synthetic_icu(test_rows, 102)), fh)
 
 
-def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_rows: int) -> dict:
+def _client_process(conn, workdir: str, cfg: dict, dev: str, c: int, attack_cfg):
+    """One OS process per client, as the reference is deployed (client.py:134-142): the unmodified ``RpcClient`` handles
+    START bodies received from the parent and returns the pickled UPDATE bodies it published."""
+    import io as _io
+    import contextlib as _ctx
+    os.environ.setdefault("TQDM_DISABLE", "1")
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from baseline import ref_loader
+    try:
+        with _ctx.redirect_stdout(_io.StringIO()), _ctx.redirect_stderr(_io.StringIO()):
+            _, client_mod = ref_loader.load_server_client(workdir, cfg, device=dev, patch_fedavg=True)
+            import pika
+            rc = client_mod.RpcClient(uuid.UUID(int=c + 1), "127.0.0.1", "admin", "admin", client_mod.train_on_device, dev)
+            if attack_cfg:
+                rc.set_attack_config(*attack_cfg)
+        conn.send("ready")
+        while True:
+            body = conn.recv()
+            if body is None:
+                break
+            with _ctx.redirect_stdout(_io.StringIO()), _ctx.redirect_stderr(_io.StringIO()):
+                rc.response_message(body)
+            q = pika.QUEUES["rpc_queue"]
+            out = list(q)
+            q.clear()
+            conn.send(out)
+    except Exception as e:                                        # noqa: BLE001
+        try:
+            conn.send(("error", repr(e)))
+        except Exception:                                         # noqa: BLE001
+            pass
+
+
+def run_concurrent(cfg: dict, attackers: dict, steps: int, warmup: int, clients_per_gpu: int, train_rows: int,
+                   test_rows: int) -> dict:
+    """Second reference arm (single node, single GPU): the same unmodified code with the clients running CONCURRENTLY, one OS
+    process per client sharing the GPU - how the reference is actually run (client.py:134-142) - instead of one after the
+    other in the harness process.  Wall-clock timed (the clients' kernels run in other processes)."""
+    import multiprocessing as mp
+    import pickle
+
+    import torch
+
+    from baseline import ref_loader
+    cpu_mode = os.environ.get("AFL_REF_DEVICE") == "cpu"          # plumbing test without a GPU
+    if not ref_loader.ensure_installed() or not (torch.cuda.is_available() or cpu_mode):
+        return {"unavailable": "reference or CUDA device missing"}
+    os.environ.setdefault("TQDM_DISABLE", "1")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = "cpu" if cpu_mode else f"cuda:{local}"
+    sync = (lambda: None) if cpu_mode else torch.cuda.synchronize
+    C = clients_per_gpu
+    cfg = dict(cfg)
+    cfg["server"] = dict(cfg["server"], **{"num-round": warmup + steps, "clients": C})
+    cwd = os.getcwd()
+    workdir = tempfile.mkdtemp(prefix="afl_refc_")
+    _write_datasets(workdir, train_rows, test_rows)
+    ctx = mp.get_context("spawn")
+    procs, conns = [], []
+    sink = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(sink), contextlib.redirect_stderr(io.StringIO()):
+            server_mod, _ = ref_loader.load_server_client(workdir, cfg, device=dev, patch_fedavg=True)
+        import pika
+        for c in range(C):
+            a, b = ctx.Pipe()
+            p = ctx.Process(target=_client_process, args=(b, workdir, cfg, dev, c, attackers.get(c)), daemon=True)
+            p.start()
+            procs.append(p); conns.append(a)
+        for a in conns:
+            msg = a.recv()
+            if msg != "ready":
+                return {"unavailable": f"client process failed: {msg}"}
+        ids = [uuid.UUID(int=c + 1) for c in range(C)]
+        with contextlib.redirect_stdout(sink):
+            server = server_mod.Server()
+            for c in range(C):
+                body = pickle.dumps({"action": "REGISTER", "client_id": ids[c], "message": "Hello from Client!",
+                                     "attack": c in attackers})
+                server.on_request(pika.Channel(), pika._Method(0), pika._Props(), body)
+
+        def one_round():
+            with contextlib.redirect_stdout(sink), contextlib.redirect_stderr(io.StringIO()):
+                active = []
+                for c in range(C):
+                    q = pika.QUEUES[f"reply_{ids[c]}"]
+                    if q:
+                        conns[c].send(q.popleft())               # all clients start at once
+                        active.append(c)
+                try:
+                    for c in active:
+                        got = conns[c].recv()
+                        if isinstance(got, tuple):
+                            raise RuntimeError(got[1])
+                        for b in got:
+                            server.on_request(pika.Channel(), pika._Method(0), pika._Props(), b)
+                except SystemExit:
+                    pass
+            sink.seek(0); sink.truncate(0)
+
+        for _ in range(warmup):
+            one_round()
+        sync()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            one_round()
+        sync()
+        wall = time.perf_counter() - t0
+    finally:
+        os.chdir(cwd)
+        for a in conns:
+            try:
+                a.send(None)
+            except Exception:                                     # noqa: BLE001
+                pass
+        for p in procs:
+            p.join(timeout=10)
+            if p.is_alive():
+                p.terminate()
+    return {"value": round(C * steps / wall, 4), "unit": "client-rounds/s", "ms_per_step": round(wall / steps * 1e3, 2),
+            "steps": steps, "warmup": warmup, "clients": C, "timing": "wall clock (client kernels run in other processes)",
+            "what": "same unmodified reference code, one OS process per client sharing the GPU (client.py:134-142)"}
+
+
+def run_bench(args, bench_config, clients_per_gpu: int, train_rows: int, test_rows: int, headline_config=None) -> dict:
     """bench.py --impl reference: BASELINE config 3 (one LIE attacker per 8 clients)."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     C = clients_per_gpu * world
     attackers = {c: ("LIE", 2, [0.74]) for c in range(C) if c % clients_per_gpu == clients_per_gpu - 1}
-    return run_config(bench_config(C), attackers, args.steps, args.warmup, clients_per_gpu, train_rows, test_rows)
+    out = run_config(bench_config(C), attackers, args.steps, args.warmup, clients_per_gpu, train_rows, test_rows)
+    if out and headline_config is not None and "config" in out:
+        # the same ``config`` object as our arm (keys, values, types); arm-specific facts live under impl_detail
+        out["impl_detail"] = {k: out["config"][k] for k in ("transport", "patch") if k in out["config"]}
+        out["impl_detail"]["attackers"] = out["config"].get("attack")
+        out["config"] = headline_config(C, world)
+    if out and world == 1 and os.environ.get("AFL_REF_CONCURRENT", "1") != "0" and os.environ.get("AFL_REF_DEVICE") != "cpu":
+        # second arm: the reference's clients as concurrent OS processes (its real deployment), fewer rounds
+        try:
+            out["concurrent_clients"] = run_concurrent(bench_config(C), attackers, min(args.steps, 4), 2, clients_per_gpu,
+                                                       train_rows, test_rows)
+        except Exception as e:                                    # noqa: BLE001
+            out["concurrent_clients"] = {"unavailable": repr(e)}
+    return out
 
 
 def run_config(cfg: dict, attackers: dict, steps: int, warmup_req: int, clients_per_gpu: int, train_rows: int,
@@ -227,7 +364,15 @@ def run_config(cfg: dict, attackers: dict, steps: int, warmup_req: int, clients_
                    "transport": "in-memory pika stand-in + torch.distributed object collectives (no broker)",
                    "patch": "server.py:289 if->elif (fedavg crash fix, applied in memory)"},
         "e2e": {"value": round(C * args.steps / wall, 4), "unit": "client-rounds/s",
-                "note": "the reference loop already moves every batch host->device and every loss device->host"},
+                # what the stock loop moves per FL round (client.py:88-100, src/Validation.py:98-112), computed from the
+                # tensors it copies: every batch of every epoch host->device as (vitals[7], labs[16], label) fp32, the test
+                # set once per round; device->host the loss (4 B) and the NaN test (1 B) of every step, the test outputs
+                "h2d_bytes_per_step": int(C * cfg["learning"]["epoch"] * sum(cfg["server"]["data-distribution"]["num-data-range"]) / 2 * 24 * 4
+                                          + test_rows * 23 * 4),
+                "d2h_bytes_per_step": int(C * cfg["learning"]["epoch"] * -(-sum(cfg["server"]["data-distribution"]["num-data-range"]) // (2 * cfg["learning"]["batch-size"])) * 5
+                                          + test_rows * 4),
+                "note": "the reference loop already moves every batch host->device and every loss device->host; bytes are "
+                        "computed from the mean num_data of the configured range"},
         "gpu_launches": 0, "roc_auc_last": auc,
     }
     if world > 1:

@@ -56,6 +56,23 @@ def bench_config(n_clients: int) -> dict:
     }
 
 
+def headline_config(n_clients: int, n_gpus: int) -> dict:
+    """The ``config`` object of the JSON line: identical keys, values and types in BOTH arms (our engine and the
+    unmodified reference); everything that is specific to one implementation goes under ``impl_detail``."""
+    return {"model": MODEL, "mode": "fedavg", "attack": "LIE z=0.74, 1 attacker per 8 clients from round 2",
+            "clients": n_clients, "clients_per_gpu": CLIENTS_PER_GPU, "global_batch": 128 * n_clients, "local_epochs": 5,
+            "batch_size": 128, "num_data_range": [12000, 15000], "optimizer_steps_per_client_round": "~525",
+            "seq_len": 1, "validation": "ROC-AUC every round", "parallelism": f"fl-clients x{n_gpus} (dp{n_gpus})"}
+
+
+def _pct(xs, q):
+    xs = sorted(xs)
+    if not xs:
+        return None
+    k = min(len(xs) - 1, max(0, int(round(q * (len(xs) - 1)))))
+    return round(xs[k], 3)
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -162,6 +179,7 @@ def run_ours(args) -> dict:
     ev = []
     metrics = []
     phases = {}
+    agg_ms = []
     for _ in range(args.steps):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -172,13 +190,16 @@ def run_ours(args) -> dict:
         metrics.append(r.metric)
         for k, v in r.timings_ms.items():
             phases[k] = phases.get(k, 0.0) + v / args.steps
+        agg_ms.append(float(r.timings_ms.get("aggregate", 0.0)))
         assert r.ok, "a timed round failed"
     torch.cuda.synchronize()
     launches = native.launch_count()
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    t = torch.tensor([dev_ms], device=ctx.device)
-    ctx.all_reduce_max(t)
-    dev_ms = float(t.item())
+    per_round = torch.tensor([a.elapsed_time(b) for a, b in ev], device=ctx.device)
+    ctx.all_reduce_max(per_round)                                  # per-round max over ranks
+    agg_t = torch.tensor(agg_ms, device=ctx.device)
+    ctx.all_reduce_max(agg_t)
+    per_round, agg_ms = per_round.tolist(), agg_t.tolist()
+    dev_ms = float(sum(per_round))
     # ---------------- end-to-end rounds (pinned host -> device every round, results read back)
     pinned = train.packed().pin_memory()
     fed.set_host_train(pinned)
@@ -204,13 +225,15 @@ def run_ours(args) -> dict:
         "n_gpus": n_gpus, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
         "impl": "ours",
-        "config": {"model": MODEL, "mode": "fedavg", "attack": "LIE z=0.74, 1 attacker per 8 clients from round 2",
-                   "clients": C, "clients_per_gpu": CLIENTS_PER_GPU, "global_batch": 128 * C, "local_epochs": 5,
-                   "batch_size": 128, "num_data_range": [12000, 15000], "optimizer_steps_per_client_round": "~525",
-                   "seq_len": 1, "validation": "ROC-AUC every round", "parallelism": f"fl-clients x{n_gpus} (dp{n_gpus})",
-                   "l2": "flushed with a 256 MiB write between timed rounds",
-                   "blocks_per_client": fed.plan.G, "tile_samples": fed.plan.S, "collectives": cfg.runtime.collectives
-                   if ctx.distributed else "single-gpu"},
+        "config": headline_config(C, n_gpus),
+        "impl_detail": {"l2": "flushed with a 256 MiB write between timed rounds", "trainer": fed.trainer,
+                        "blocks_per_client": fed.plan.G, "tile_samples": fed.plan.S,
+                        "collectives": cfg.runtime.collectives if ctx.distributed else "single-gpu",
+                        "fused_attached": fed.fused_comm is not None,
+                        "nvls": bool(getattr(fed.fused_comm, "multicast", False)) if fed.fused_comm is not None else False,
+                        "launches_per_round": round(launches / max(args.steps, 1), 2)},
+        "round_ms": {"median": _pct(per_round, 0.5), "p95": _pct(per_round, 0.95), "max": _pct(per_round, 1.0)},
+        "aggregate_ms": {"median": _pct(agg_ms, 0.5), "p95": _pct(agg_ms, 0.95), "max": _pct(agg_ms, 1.0)},
         "clocks": clocks,
         "e2e": {"value": round(C * args.steps / e2e_s, 3), "unit": "client-rounds/s",
                 "rounds_per_sec": round(args.steps / e2e_s, 4),
@@ -232,7 +255,7 @@ def run_reference(args) -> dict:
         from baseline import harness_ref
     except Exception as e:                                          # noqa: BLE001
         return {"impl": "reference", "unavailable": f"baseline harness import failed: {e!r}"}
-    return harness_ref.run_bench(args, bench_config, CLIENTS_PER_GPU, TRAIN_ROWS, TEST_ROWS)
+    return harness_ref.run_bench(args, bench_config, CLIENTS_PER_GPU, TRAIN_ROWS, TEST_ROWS, headline_config)
 
 
 def main():
