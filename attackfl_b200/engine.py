@@ -476,8 +476,47 @@ class Federation:
                                                             a_cfg.strict_reference)
                     self.crafted_own[sp.index] = False
         gram_specs = [sp for sp in attackers if sp.attack_mode in GRAM_MODES]
+        for sp in gram_specs:
+            if len(subsets[sp.index]) <= 1:
+                self.crafted_own[sp.index] = True                # "return state_dict" (Utils.py:102-103)
+        live = [sp for sp in gram_specs if len(subsets[sp.index]) > 1]
+        batched = (live and native and self.device.type == "cuda" and a_cfg.metric == "flat"
+                   and len(genuine) + len(live) <= 256 and (rows_all is not None or self.fused_comm is not None))
+        if batched:
+            # ONE Gram for all attackers (csrc/gram_multi.cu): one pass over the genuine rows, one tcgen05 Gram of
+            # [genuine rows ; one direction row per attacker], all bisections in one launch, all crafted rows in one launch
+            from .ops import flat
+            pos = {c: j for j, c in enumerate(genuine)}
+            subs = [[pos[c] for c in subsets[sp.index]] for sp in live]
+            modes = [sp.attack_mode for sp in live]
+            if rows_all is not None:
+                cen = center if center is not None else rows_all[genuine].mean(0)
+                out, gam = flat.multi_gram_attack([rows_all[c].data_ptr() for c in genuine], cen.contiguous(), subs, modes,
+                                                  self.D, paper=a_cfg.search == "paper", precision=a_cfg.gram_precision)
+                for a, sp in enumerate(live):
+                    self.crafted[sp.index] = out[a]
+            else:
+                # multi-GPU: K-slice ownership, genuine rows read in place over NVLink, partial Grams summed by K1-fused,
+                # crafted slices stored into every rank's copy of the crafted rows
+                fc = self.fused_comm
+                fc._ensure_gram_buffers(len(live))
+                sl = self.D // fc.world
+                cen = center if center is not None else self.global_row
+                dst = [[int(b) + a * self.D * 4 for b in fc.h_craft.buffer_ptrs] for a in range(len(live))]
+                _, gam = flat.multi_gram_attack([fc.row_ptr(c) for c in genuine], cen.contiguous(), subs, modes, self.D,
+                                                lo=fc.rank * sl, hi=(fc.rank + 1) * sl, paper=a_cfg.search == "paper",
+                                                precision=a_cfg.gram_precision if len(genuine) + len(live) <= 256 else "fp32",
+                                                dst_ptrs=dst, reduce_gram=fc.allreduce_small)
+                torch.cuda.synchronize(self.device)
+                self.ctx.barrier()                                # every rank's slice has landed in every crafted row
+                for a, sp in enumerate(live):
+                    self.crafted[sp.index] = fc.craft_sym[a].clone()
+            for a, sp in enumerate(live):
+                info[f"gamma_{sp.index}"] = gam[a]
+                self.crafted_own[sp.index] = False
+            return info
         if gram_specs and rows_all is None:
-            # fused multi-GPU path: K-slice ownership, rows are read in place over NVLink (parallel/symm.py)
+            # fused multi-GPU path, one attacker at a time (more than 256 Gram rows): K-slice ownership (parallel/symm.py)
             fc = self.fused_comm
             fc._ensure_gram_buffers(len(gram_specs))
             for slot, sp in enumerate(gram_specs):

@@ -163,6 +163,63 @@ def scion_cosine_distances(rows: torch.Tensor, valid: Optional[torch.Tensor], se
     return (1.0 - cos).to(torch.float32), {"bits": bits, "counts": counts, "minmax": minmax, "lohi": torch.stack([lo, hi], 1)}
 
 
+def multi_gram_attack(row_ptrs: Sequence[int], center: torch.Tensor, subsets: Sequence[Sequence[int]], modes: Sequence[str],
+                      d_pad: int, lo: int = 0, hi: Optional[int] = None, paper: bool = False, precision: str = "tf32",
+                      dst_ptrs: Optional[Sequence[Sequence[int]]] = None, reduce_gram=None):
+    """Min-Max / Min-Sum / Opt-Fang for ALL attackers from one Gram (``csrc/gram_multi.cu``).
+
+    ``row_ptrs``: device addresses of the n genuine rows (peer-mapped addresses allowed); ``subsets[a]``: positions in
+    that list, in the attacker's sample order; ``modes[a]``; slice ``[lo, hi)`` of the coordinates handled by this call
+    (``reduce_gram`` sums the R x R partial Grams across ranks when the slices are distributed).  Crafted slices are
+    written through ``dst_ptrs[a][w]`` (every rank's copy of attacker ``a``'s row) or returned as ``[A, hi-lo]``.
+    Returns ``(crafted or None, gammas [A,4] device tensor)``.
+    """
+    from . import gram as gram_mod
+    dev = center.device
+    lib = lib_for(center)
+    hi = d_pad if hi is None else hi
+    n, A = len(row_ptrs), len(subsets)
+    ld = hi - lo
+    kmax = max(len(s) for s in subsets)
+    rp = torch.as_tensor([int(p) for p in row_ptrs], dtype=torch.int64, device=dev)
+    member = torch.zeros(A, n, dtype=torch.float32)
+    sub = torch.zeros(A, kmax, dtype=torch.int32)
+    for a, s in enumerate(subsets):
+        member[a, list(s)] = 1.0
+        sub[a, :len(s)] = torch.as_tensor(list(s), dtype=torch.int32)
+    member, sub = member.to(dev), sub.to(dev)
+    kc = torch.tensor([float(len(s)) for s in subsets], device=dev)
+    kk = torch.tensor([len(s) for s in subsets], dtype=torch.int32, device=dev)
+    sgn = torch.tensor([1 if m == "Opt-Fang" else 0 for m in modes], dtype=torch.int32, device=dev)
+    rule = torch.tensor([1 if m == "Min-Sum" else 0 for m in modes], dtype=torch.int32, device=dev)
+    X = torch.empty(n + A, ld, dtype=torch.float32, device=dev)
+    mu = torch.empty(A, ld, dtype=torch.float32, device=dev)
+    p = torch.empty(A, ld, dtype=torch.float32, device=dev)
+    rc = lib.afl_multi_moments(ptr(rp), c_i(n), ptr(center), c_i64(lo), c_i64(hi), c_i64(ld), ptr(member), ptr(kc), ptr(sgn),
+                               c_i(A), ptr(X), ptr(mu), ptr(p), stream_ptr(center))
+    check(lib, rc, "afl_multi_moments")
+    G = gram_mod.gram(X, precision=precision)
+    if reduce_gram is not None:
+        G = reduce_gram(G)
+    G = G.to(torch.float32).contiguous()
+    gam = torch.zeros(A, 4, dtype=torch.float32, device=dev)
+    rc = lib.afl_multi_gamma(ptr(G), c_i(n + A), c_i(n), ptr(sub), ptr(kk), c_i(kmax), ptr(rule), c_i(A),
+                             c_i(1 if paper else 0), ptr(gam), stream_ptr(center))
+    check(lib, rc, "afl_multi_gamma")
+    out = None
+    if dst_ptrs is None:
+        out = torch.empty(A, ld, dtype=torch.float32, device=dev)
+        dst = torch.as_tensor([out[a].data_ptr() - lo * 4 for a in range(A)], dtype=torch.int64, device=dev)
+        world = 1
+    else:
+        world = len(dst_ptrs[0])
+        dst = torch.as_tensor([int(x) for row in dst_ptrs for x in row], dtype=torch.int64, device=dev)
+    rc = lib.afl_multi_craft(ptr(dst), c_i(world), ptr(mu), ptr(p), c_i64(ld), ptr(gam), c_i(A), c_i64(lo), c_i64(hi),
+                             stream_ptr(center))
+    check(lib, rc, "afl_multi_craft")
+    return out, gam
+
+
 # ---------------------------------------------------------------------------------------- hyper-network
 class NativeHyper:
     """Device-side state of a ``FusedHyperNet`` in the layout the K5 kernels expect.

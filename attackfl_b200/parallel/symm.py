@@ -186,6 +186,42 @@ class FusedComm:
         self._last_gamma = g4
         return self.craft_sym[slot]
 
+    # ------------------------------------------------------------------ small all-reduce through K1-fused (no NCCL)
+    def allreduce_small(self, t: torch.Tensor) -> torch.Tensor:
+        """Sum of a small fp32 tensor (<= 65,536 elements, e.g. an R x R partial Gram) over all ranks with the fused
+        FedAvg kernel itself: every rank contributes one "client row" of weight 1, the result lands in every rank's
+        symmetric buffer.  Stays on the stream, no host sync."""
+        import torch.distributed._symmetric_memory as symm_mem
+        n = t.numel()
+        cap = 65536
+        assert n <= cap, "allreduce_small: at most 65,536 elements"
+        if getattr(self, "g_rows", None) is None:
+            dev = self.fed.device
+            self.g_rows = symm_mem.empty(1, cap, dtype=torch.float32, device=dev)
+            self.g_part = symm_mem.empty(1, cap, dtype=torch.float32, device=dev)
+            self.g_glob = symm_mem.empty(cap, dtype=torch.float32, device=dev)
+            for b in (self.g_rows, self.g_part, self.g_glob):
+                b.zero_()
+            hs = [symm_mem.rendezvous(b, dist.group.WORLD) for b in (self.g_part, self.g_glob)]
+            symm_mem.rendezvous(self.g_rows, dist.group.WORLD)
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            PtrArr = ctypes.c_void_p * self.world
+            self.g_part_ptrs = PtrArr(*[int(p) for p in hs[0].buffer_ptrs])
+            self.g_glob_ptrs = PtrArr(*[int(p) for p in hs[1].buffer_ptrs])
+            self.g_one = torch.ones(1, dtype=torch.float32, device=dev)
+        lib = native.cuda_lib()
+        self.g_rows.view(-1)[:n].copy_(t.reshape(-1))
+        d = (n + 4 * self.world * 8 - 1) // (4 * self.world * 8) * (4 * self.world * 8)
+        self.epoch += 1
+        rc = lib.afl_fedavg_fused(ptr(self.g_rows), ptr(self.g_one), ctypes.c_int(1), ctypes.c_int64(d), ctypes.c_int(self.world),
+                                  ctypes.c_int(self.rank), self.g_part_ptrs, self.g_glob_ptrs, None, self.sig_ptrs,
+                                  ctypes.c_uint32(self.epoch), ctypes.c_int(0), None, None, None, None, ctypes.c_int(0),
+                                  None, ptr(self.ctrl), ctypes.c_void_p(0), ctypes.c_void_p(0), ctypes.c_void_p(0),
+                                  stream_ptr(self.g_rows))
+        check(lib, rc, "afl_fedavg_fused (small all-reduce)")
+        return self.g_glob[:n].view(t.shape).clone()
+
     def check_error(self, raise_on_error: bool = True) -> int:
         """Error word of the fused kernels (non-zero: a cross-GPU flag barrier timed out, the outputs are stale).  The
         word is summed over ranks so that every rank takes the same decision."""

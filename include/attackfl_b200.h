@@ -183,6 +183,21 @@ int afl_gram_bf16(const float* A, int R, int64_t D, int64_t lda, void* a16, floa
 int afl_gram_tf32_workspace(int R, int64_t D, int64_t* partial_floats);
 int afl_gram_tf32(const float* A, int R, int64_t D, int64_t lda, float* partials, float* G, void* stream);
 
+/* One Gram for all attackers (src/Utils.py:83-98,108-113,142-147,176-185; the per-attacker samples of server.py:596-600 all
+ * come from the same n genuine rows).  afl_multi_moments: one pass over the genuine rows of slice [lo, hi) (row_ptrs_dev [n],
+ * peer-mapped pointers allowed) -> X [n + A][ld] = centred genuine rows followed by the direction rows p_a, mu_out / p_out
+ * [A][ld]; member_dev [A][n] 0/1, kcount_dev [A], sign_mode_dev [A] (1: p = sign(mu), Opt-Fang).  afl_multi_gamma: G [R][R]
+ * (R = n + A) -> per attacker the (k+2)^2 sub-Gram of its sample (subsets_dev [A][kmax]: positions in the genuine list, in
+ * sample order; k_dev [A]; rule_dev [A]: 0 max / 1 sum) and the reference's bisection, out [A][4] as afl_gamma_search_dev.
+ * afl_multi_craft: mu_a - gamma_a p_a of slice [lo, hi) stored to dst_dev [A][world] row pointers (null entries skipped). */
+int afl_multi_moments(const float* const* row_ptrs_dev, int n, const float* center, int64_t lo, int64_t hi, int64_t ld,
+                      const float* member_dev, const float* kcount_dev, const int* sign_mode_dev, int A, float* X,
+                      float* mu_out, float* p_out, void* stream);
+int afl_multi_gamma(const float* G, int R, int n, const int* subsets_dev, const int* k_dev, int kmax, const int* rule_dev,
+                    int A, int paper, float* out, void* stream);
+int afl_multi_craft(float* const* dst_dev, int world, const float* mu, const float* p, int64_t ld, const float* gammas,
+                    int A, int64_t lo, int64_t hi, void* stream);
+
 /* K5 persistent + row-sharded: one cooperative launch per rank walks all reporting clients of a round in order
  * (server.py:637-678).  head_w / head_b / mw / vw / mb / vb are THIS rank's row shard (row 0 = global row lo, `rows` rows);
  * `small` = params | m | v of the replicated MLP + embedding table, `small_alt` [tot] a second copy of the parameters
