@@ -687,6 +687,68 @@ class Federation:
         self.have_global = True
         self._rows_hold_global = True
 
+    SLICED_MODES = ("median", "trimmed_mean", "krum", "shieldfl", "FLTrust")
+
+    def _aggregate_sliced(self, reporting: List[int], info: Dict[str, object]) -> None:
+        """Defences on N GPUs without gathering a row: rank r owns coordinate slice r.  Median / trimmed mean read the C
+        values of their coordinates from the clients' rows in place (peer pointers) and store the result into every
+        rank's global model (K6); Krum / ShieldFL / FLTrust need only an n x n Gram: every rank computes the Gram of its
+        K-slice (tcgen05), the partials are summed by K1-fused, the weights are replicated scalars and the weighted
+        aggregation is the K1-fused kernel (``/root/reference/src/Utils.py:267-302,326-357``; ``server.py:306-350,703-743``)."""
+        from .ops import flat
+        s, fc = self.cfg.server, self.fused_comm
+        sl = self.D // fc.world
+        lo, hi = fc.rank * sl, (fc.rank + 1) * sl
+        ptrs = [fc.row_ptr(c) for c in reporting]
+        n = len(reporting)
+        if self.mode in ("median", "trimmed_mean"):
+            k = int(n * s.trim_ratio) if self.mode == "trimmed_mean" else 0
+            if self.mode == "trimmed_mean" and 2 * k >= n:
+                raise ValueError("too few clients for the chosen trim_ratio")
+            flat.coord_select_ptrs(ptrs, lo, hi, [int(p) for p in fc.h_glob.buffer_ptrs],
+                                   "median" if self.mode == "median" else "trimmed", k, self.device)
+            torch.cuda.synchronize(self.device)
+            self.ctx.barrier()                                    # every owner's slice has landed in every global buffer
+            self.have_global = True
+            return
+        prec = self.cfg.attack.gram_precision
+        zero = getattr(self, "_zero_row", None)
+        if zero is None:
+            zero = self._zero_row = torch.zeros(self.D, device=self.device)
+        w = torch.zeros(self.C, dtype=torch.float32)
+        g0_weight = 0.0
+        if self.mode == "krum":
+            cen = self.global_row if self.have_global else zero
+            G = flat.sliced_gram(ptrs, cen.contiguous(), lo, hi, prec, fc.allreduce_small)
+            kf = int(n * s.genuine_rate) if s.krum_reference_f else s.krum_f
+            i = agg.krum_select(torch.zeros(n, 1, device=self.device), kf, lambda _r: G, reference_slice=s.krum_reference_f)
+            info["krum_winner"] = reporting[i]
+            w[reporting[i]] = 1.0
+        elif self.mode == "shieldfl":
+            G = flat.sliced_gram(ptrs, zero, lo, hi, prec, fc.allreduce_small)      # cosines of the raw vectors: no centring
+            a = agg.shieldfl_weights(torch.zeros(n, 1, device=self.device), lambda _r: G).cpu()
+            for j, c in enumerate(reporting):
+                w[c] = float(a[j])
+        else:                                                    # FLTrust: deltas against the round's base model
+            base = self._fltrust_base
+            G = flat.sliced_gram(ptrs + [self.server_row.data_ptr()], base.contiguous(), lo, hi, prec,
+                                 fc.allreduce_small).to(torch.float64)
+            norms = torch.diagonal(G).clamp_min(0).sqrt()
+            cos = G[:n, n] / torch.clamp(norms[:n] * norms[n], min=1e-8)
+            ts = cos.clamp_min(0)
+            scale = ((norms[n] / (norms[:n] + 1e-6)) * ts / (ts.sum() + 1e-6)).cpu()
+            info["trust"] = ts.to(torch.float32).tolist()
+            for j, c in enumerate(reporting):
+                w[c] = float(scale[j])
+            g0_weight = 1.0 - float(scale.sum())                  # new = g0 + sum a_i (w_i - g0)
+        fc.fedavg(w, None, None, zero, False)
+        if g0_weight != 0.0:
+            self.global_row.add_(self._fltrust_base, alpha=g0_weight)
+            self._rows_hold_global = False
+        else:
+            self._rows_hold_global = True
+        self.have_global = True
+
     def _fltrust_server_update(self) -> None:
         """Server trains on the root set: first 200 test samples, batch 100, no shuffle (server.py:289-294,711)."""
         s, l = self.cfg.server, self.cfg.learning
@@ -906,6 +968,12 @@ class Federation:
                                       and not gram_sliced)
         if self._hyper_sharded() and not any(sp.attack for sp in self.specs):
             need_gather = False                                   # rows are read in place by the sharded hyper kernel
+        sliced = (self.fused_comm is not None and self.backend == "native" and self.mode in self.SLICED_MODES
+                  and len(starting) <= 256 and self.cfg.attack.metric == "flat")
+        has_lie = any(sp.attack and sp.attack_mode == "LIE" for sp in self.specs)
+        if sliced and not has_lie and (self.have_global or not any(sp.attack and sp.attack_mode in GRAM_MODES for sp in self.specs)):
+            need_gather = False                                   # slice-owned defences read the rows in place
+            gram_sliced = self.have_global
         rows_all = None
         if need_gather:
             with self.timer.phase("gather"):
@@ -921,7 +989,14 @@ class Federation:
                 info.update(self._prepare_crafts(rows_all, genuine, center, defer_lie=fused))
             self.genuine_prev = genuine
             with self.timer.phase("aggregate"):
-                if fused:
+                if sliced and rows_all is None:
+                    self._aggregate_sliced(reporting, info)
+                    err = self.fused_comm.check_error(raise_on_error=False)
+                    if err:
+                        self._log(f"fused aggregation reported error {err}; the round is discarded", "red")
+                        self.fused_comm.reset_error()
+                        info["failed"] = True
+                elif fused:
                     self._aggregate_fused(reporting, center, info)
                     # a peer-barrier time-out leaves glob / lie / the client rows stale: fail the round on every rank
                     # (the error word is part of the symmetric control block, every rank reads its own copy)

@@ -163,6 +163,41 @@ def scion_cosine_distances(rows: torch.Tensor, valid: Optional[torch.Tensor], se
     return (1.0 - cos).to(torch.float32), {"bits": bits, "counts": counts, "minmax": minmax, "lohi": torch.stack([lo, hi], 1)}
 
 
+def coord_select_ptrs(row_ptrs: Sequence[int], lo: int, hi: int, dst_ptrs: Sequence[int], mode: str, trim: int,
+                      device) -> None:
+    """K6 on a coordinate slice with the rows given by device addresses (peer-mapped addresses allowed); the result is
+    stored into every buffer of ``dst_ptrs``."""
+    lib = lib_for(torch.empty(0, device=device))
+    rp = torch.as_tensor([int(p) for p in row_ptrs], dtype=torch.int64, device=device)
+    dp = torch.as_tensor([int(p) for p in dst_ptrs], dtype=torch.int64, device=device)
+    rc = lib.afl_coord_select_ptrs(ptr(rp), c_i(len(row_ptrs)), c_i64(lo), c_i64(hi), ptr(dp), c_i(len(dst_ptrs)),
+                                   c_i(0 if mode == "median" else 1), c_i(trim), stream_ptr(rp))
+    check(lib, rc, "afl_coord_select_ptrs")
+
+
+def sliced_gram(row_ptrs: Sequence[int], center: torch.Tensor, lo: int, hi: int, precision: str = "tf32",
+                reduce_gram=None) -> torch.Tensor:
+    """Gram of ``rows - center`` from the coordinate slice ``[lo, hi)`` of rows given by device addresses (read in place,
+    also over NVLink); ``reduce_gram`` sums the partial Grams of the ranks.  Serves Krum / ShieldFL / FLTrust."""
+    from . import gram as gram_mod
+    dev = center.device
+    lib = lib_for(center)
+    n, ld = len(row_ptrs), hi - lo
+    rp = torch.as_tensor([int(p) for p in row_ptrs], dtype=torch.int64, device=dev)
+    X = torch.empty(n + 1, ld, dtype=torch.float32, device=dev)
+    mu = torch.empty(1, ld, dtype=torch.float32, device=dev)
+    p = torch.empty(1, ld, dtype=torch.float32, device=dev)
+    one = torch.ones(1, n, dtype=torch.float32, device=dev)
+    rc = lib.afl_multi_moments(ptr(rp), c_i(n), ptr(center), c_i64(lo), c_i64(hi), c_i64(ld), ptr(one),
+                               ptr(torch.tensor([float(n)], device=dev)), ptr(torch.zeros(1, dtype=torch.int32, device=dev)),
+                               c_i(1), ptr(X), ptr(mu), ptr(p), stream_ptr(center))
+    check(lib, rc, "afl_multi_moments")
+    G = gram_mod.gram(X[:n], precision=precision if n <= 256 else "fp32")
+    if reduce_gram is not None:
+        G = reduce_gram(G)
+    return G
+
+
 def multi_gram_attack(row_ptrs: Sequence[int], center: torch.Tensor, subsets: Sequence[Sequence[int]], modes: Sequence[str],
                       d_pad: int, lo: int = 0, hi: Optional[int] = None, paper: bool = False, precision: str = "tf32",
                       dst_ptrs: Optional[Sequence[Sequence[int]]] = None, reduce_gram=None):

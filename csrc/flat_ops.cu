@@ -146,21 +146,28 @@ __global__ void __launch_bounds__(256) scion_scores_kernel(const uint32_t* __res
 // compare-exchange distances < VPT stay inside a lane, larger ones use shfl.xor.  No local memory, no global re-reads.
 template <int VPT>
 __global__ void __launch_bounds__(256) select_warp_kernel(const float* __restrict__ rows, int C, int64_t d_pad,
-                                                          float* __restrict__ out, int mode, int trim) {
+                                                          float* __restrict__ out, int mode, int trim,
+                                                          const float* const* row_ptrs = nullptr, int64_t lo = 0,
+                                                          int64_t hi = -1, float* const* dsts = nullptr, int n_dst = 0) {
+  // row_ptrs (optional): one base pointer per row instead of a dense [C][d_pad] matrix - the rows may live on other GPUs
+  // (peer-mapped); [lo, hi): coordinate slice handled by this launch; dsts: the result is stored into every listed buffer
+  // (every rank's copy of the global model) instead of `out`.
   extern __shared__ float tile[];                    // [C][33]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int P = 32 * VPT;                        // padded element count (power of two >= C)
-  const int64_t n_tiles = (d_pad + 31) / 32;
-  for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
+  if (hi < 0) hi = d_pad;
+  const int64_t t0 = lo / 32, n_tiles = (hi + 31) / 32;
+  for (int64_t tIdx = t0 + blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
     const int64_t d0 = tIdx * 32;
     __syncthreads();
     for (int i = threadIdx.x; i < C * 32; i += 256) {
       const int c = i >> 5, x = i & 31;
-      tile[c * 33 + x] = (d0 + x < d_pad) ? rows[(int64_t)c * d_pad + d0 + x] : 0.f;
+      const float* src = row_ptrs ? row_ptrs[c] : rows + (int64_t)c * d_pad;
+      tile[c * 33 + x] = (d0 + x < hi) ? src[d0 + x] : 0.f;
     }
     __syncthreads();
     for (int col = warp; col < 32; col += 8) {
-      if (d0 + col >= d_pad) break;
+      if (d0 + col >= hi) break;
       float v[VPT];
 #pragma unroll
       for (int r = 0; r < VPT; ++r) {
@@ -217,7 +224,10 @@ __global__ void __launch_bounds__(256) select_warp_kernel(const float* __restric
         for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
         res = sum / (float)(C - 2 * trim);
       }
-      if (lane == 0) out[d0 + col] = res;
+      if (lane == 0) {
+        if (dsts) { for (int w = 0; w < n_dst; ++w) dsts[w][d0 + col] = res; }
+        else out[d0 + col] = res;
+      }
     }
   }
 }
@@ -524,6 +534,22 @@ int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mo
   else select_warp_kernel<8><<<grid, 256, smem, st>>>(rows, C, d_pad, out, mode, trim);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_coord_select");
+}
+
+int afl_coord_select_ptrs(const float* const* row_ptrs_dev, int C, int64_t lo, int64_t hi, float* const* dst_dev, int n_dst,
+                          int mode, int trim, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && C <= AFL_SEL_MAX, "afl_coord_select_ptrs: 1 <= C <= 256");
+  AFL_CHECK_ARG(mode == 0 || 2 * trim < C, "afl_coord_select_ptrs: 2*trim must be < C");
+  AFL_CHECK_ARG(lo % 32 == 0 && hi > lo && n_dst >= 1, "afl_coord_select_ptrs: lo must be a multiple of 32, hi > lo");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = sizeof(float) * (size_t)C * 33;
+  const int grid = grid_for((hi - lo + 31) / 32, 1, 8);
+  if (C <= 32) select_warp_kernel<1><<<grid, 256, smem, st>>>(nullptr, C, hi, nullptr, mode, trim, row_ptrs_dev, lo, hi, dst_dev, n_dst);
+  else if (C <= 64) select_warp_kernel<2><<<grid, 256, smem, st>>>(nullptr, C, hi, nullptr, mode, trim, row_ptrs_dev, lo, hi, dst_dev, n_dst);
+  else if (C <= 128) select_warp_kernel<4><<<grid, 256, smem, st>>>(nullptr, C, hi, nullptr, mode, trim, row_ptrs_dev, lo, hi, dst_dev, n_dst);
+  else select_warp_kernel<8><<<grid, 256, smem, st>>>(nullptr, C, hi, nullptr, mode, trim, row_ptrs_dev, lo, hi, dst_dev, n_dst);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_coord_select_ptrs");
 }
 
 int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void* stream) {

@@ -78,6 +78,11 @@ int afl_craft_random(float* out, const float* w, const float* valid, float pertu
 /* K6 — per-coordinate selection over C rows: mode 0 lower median (src/Utils.py:344-357), mode 1 trimmed mean
  * dropping `trim` values per side (src/Utils.py:267-302). */
 int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mode, int trim, void* stream);
+/* K6 slice-owned: the same selection on coordinates [lo, hi) with the C rows given as a device array of base pointers (rows
+ * on other GPUs are read in place through peer-mapped pointers) and the result stored into every buffer of dst_dev [n_dst]
+ * (every rank's copy of the global model): src/Utils.py:267-302,344-357 without gathering any row. */
+int afl_coord_select_ptrs(const float* const* row_ptrs_dev, int C, int64_t lo, int64_t hi, float* const* dst_dev, int n_dst,
+                          int mode, int trim, void* stream);
 
 /* HAR linear layers on tcgen05 (kind::tf32 on fp32 data, fp32 accumulate): nn.Linear inside nn.TransformerEncoderLayer
  * and its autograd (src/Model.py:435-458, client.py:114-131).  All matrices row-major and contiguous, N and K multiples

@@ -67,6 +67,31 @@ def test_gpus_fused_matches_nccl_path(tmp_path, attack, world):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("mode,attack", [("median", "Random"), ("trimmed_mean", ""), ("krum", "Min-Max"), ("shieldfl", ""),
+                                         ("FLTrust", "Random")])
+def test_gpus_slice_owned_defences_match_gathered_path(tmp_path, mode, attack, world):
+    """Defences without gathering rows (K6 over peer rows, K-slice Gram + K1-fused weights) vs all-gather + replicated
+    aggregation; full global vectors compared."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    out = {}
+    for collectives in ("nccl", "fused"):
+        d = tmp_path / collectives
+        d.mkdir()
+        recs = _launch(d, world, mode, attack, {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives,
+                                                "AFL_TEST_CLIENTS": "8", "AFL_TEST_ROUNDS": "3"})
+        a = recs[0]
+        assert a["ok"] == [True] * 3
+        for b in recs[1:]:
+            assert float((a["vector"] - b["vector"]).abs().max()) < 1e-6
+        out[collectives] = a
+    diff = float((out["fused"]["vector"] - out["nccl"]["vector"]).abs().max())
+    scale = float(out["nccl"]["vector"].abs().max())
+    assert diff <= 2e-3 * scale, (mode, diff, scale)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("world", [2, 8])
 def test_gpus_sharded_hyper_matches_gathered_path(tmp_path, world):
     """Hyper mode: row-sharded head + persistent per-rank kernel reading client rows in place (collectives: fused) vs the
