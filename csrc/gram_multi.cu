@@ -93,13 +93,72 @@ __global__ void __launch_bounds__(128) multi_gamma_kernel(const float* G, int R,
     gs[i * Rs + k + 1] = gp; gs[(k + 1) * Rs + i] = gp;                // <g_i, p>
   }
   __syncthreads();
+  __shared__ double s_red[128];
+  __shared__ double s_thr, s_gamma, s_step, s_succ, s_last;
+  __shared__ int s_probes, s_go;
   if (threadIdx.x == 0) {
     double mm = 0.0, mp = 0.0;
     for (int i = 0; i < k; ++i) { mm += (double)gs[i * Rs + k]; mp += (double)gs[i * Rs + k + 1]; }
     gs[k * Rs + k] = (float)(mm * inv);                                // <mu, mu> = mean_i <g_i, mu>
     gs[k * Rs + k + 1] = gs[(k + 1) * Rs + k] = (float)(mp * inv);     // <mu, p>
     gs[(k + 1) * Rs + k + 1] = G[(int64_t)pa * R + pa];
-    afl_gamma_search(gs, k, rule[a], 1, paper, out + 4 * a);
+  }
+  __syncthreads();
+  // The reference's bisection (afl_gamma_search, src/Utils.py:115-130) with the O(k^2) threshold and the O(k) acceptance
+  // test of every probe spread over the block; same arithmetic (double), same order of the per-row terms.
+  const int rl = rule[a];
+  {
+    double best = 0.0;
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+      double rowsum = 0.0, rowmax = 0.0;
+      for (int j = 0; j < k; ++j) {
+        if (i == j) continue;
+        double d2 = (double)gs[i * Rs + i] + (double)gs[j * Rs + j] - 2.0 * (double)gs[i * Rs + j];
+        d2 = d2 > 0.0 ? d2 : 0.0;
+        if (rl == 0) { const double d = sqrt(d2); rowmax = d > rowmax ? d : rowmax; }
+        else rowsum += d2;
+      }
+      const double v = rl == 0 ? rowmax : rowsum;
+      best = v > best ? v : best;
+    }
+    s_red[threadIdx.x] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double thr = 0.0;
+      for (int t = 0; t < blockDim.x; ++t) thr = s_red[t] > thr ? s_red[t] : thr;
+      s_thr = thr; s_gamma = 50.0; s_step = 50.0; s_succ = 0.0; s_last = 50.0; s_probes = 0;
+      s_go = fabs(s_succ - s_gamma) > 1.0;
+    }
+    __syncthreads();
+  }
+  const double gmm = gs[k * Rs + k], gpp = gs[(k + 1) * Rs + (k + 1)], gmp = gs[k * Rs + (k + 1)];
+  while (s_go) {
+    const double gamma = s_gamma;
+    double worst = 0.0, total = 0.0;
+    for (int j = 1 + threadIdx.x; j < k; j += blockDim.x) {           // j = 0 is excluded (aliasing in the reference)
+      double d2 = gmm + gamma * gamma * gpp + (double)gs[j * Rs + j] - 2.0 * gamma * gmp
+                  - 2.0 * (double)gs[k * Rs + j] + 2.0 * gamma * (double)gs[(k + 1) * Rs + j];
+      d2 = d2 > 0.0 ? d2 : 0.0;
+      total += d2;
+      const double d = sqrt(d2);
+      worst = d > worst ? d : worst;
+    }
+    __syncthreads();
+    s_red[threadIdx.x] = rl == 0 ? worst : total;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double acc = 0.0;
+      for (int t = 0; t < blockDim.x; ++t) acc = rl == 0 ? (s_red[t] > acc ? s_red[t] : acc) : acc + s_red[t];
+      s_last = gamma;
+      if (acc < s_thr) { s_succ = gamma; s_gamma = gamma + s_step / 2; } else { s_gamma = gamma - s_step / 2; }
+      s_step /= 2; ++s_probes;
+      s_go = fabs(s_succ - s_gamma) > 1.0 && s_probes < 64;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    out[4 * a] = (float)(paper ? s_succ : s_last); out[4 * a + 1] = (float)s_succ; out[4 * a + 2] = (float)s_thr;
+    out[4 * a + 3] = (float)s_probes;
   }
 }
 

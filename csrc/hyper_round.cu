@@ -28,7 +28,8 @@
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 256;          // emit / feature kernels
+constexpr int kRT = 1024;              // round kernel: one block per SM, 32 warps streaming rows, one grid barrier per 148 blocks
 constexpr int kTR = 64;
 constexpr int kMaxWorld = 16;
 constexpr long long kSpinTimeout = 4000000000LL;
@@ -87,7 +88,20 @@ __device__ __forceinline__ int off_w(int n_nodes, int E, int H, int layer) {
   return o + H * H + H;
 }
 
-__global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
+// <W[d], f> with lane l holding W[d][l + 32 j] and f[l + 32 j]: used by pass A of the round kernel AND by the emit kernel, so
+// that theta emitted for a client and theta recomputed in its step are bit-identical (a coordinate the client did not
+// change then has delta == 0 exactly, as in the reference, instead of rounding noise that Adam would normalise to +-lr).
+template <int J>
+__device__ __forceinline__ float row_dot(const float* wv, const float* fl) {
+  float v = 0.f;
+#pragma unroll
+  for (int j = 0; j < J; ++j) v += wv[j] * fl[j];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(kRT) hyper_round_kernel(HRArgs a) {
   extern __shared__ float sm[];
   const int E = a.E, H = a.H, tid = threadIdx.x;
   float* e = sm;                    // [E]          embedding of the client
@@ -101,12 +115,14 @@ __global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
   float* g0 = g1 + H;               // [H]
   float* ge = g0 + H;               // [E]
   float* dl = ge + E;               // [kTR]
-  float* tile = dl + kTR;           // [kTR][H + 1]
-  float* sred = tile + kTR * (H + 1);   // [H + 1] block-local partial sums
+  float* sred = dl + kTR;           // [H + 1] block-local partial sums
+  // MLP weights of the current step staged in shared memory (coalesced load once per step; the matvecs below would
+  // otherwise walk ~20 K parameters in L2 with a 400-byte stride between threads): W0 [H][E] b0 | W1 [H][H+1] b1 | W2 [H][H+1] b2
+  float* wsm = sred + (H + 1);
+  const int so1 = H * E + H, so2 = so1 + H * (H + 1) + H;
   __shared__ float s_coef;
   float* Mm = a.small + a.tot;
   float* Vv = a.small + 2 * (int64_t)a.tot;
-  const int64_t n_tiles = (a.rows + kTR - 1) / kTR;
   uint32_t bar_n = 0;
 
   for (int k = 0; k < a.n; ++k) {
@@ -121,17 +137,32 @@ __global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
     const float bc1 = 1.f - powf(a.b1, (float)t_adam), bc2 = 1.f - powf(a.b2, (float)t_adam);
 
     // ---- features (every block, redundantly): e -> z0/a0 -> z1/a1 -> f
-    for (int i = tid; i < E; i += kThreads) e[i] = __ldcg(P + c * E + i);
-    for (int i = tid; i <= H; i += kThreads) sred[i] = 0.f;
+    for (int i = tid; i < E; i += kRT) e[i] = __ldcg(P + c * E + i);
+    for (int i = tid; i <= H; i += kRT) sred[i] = 0.f;
+    {
+      const float* P0 = P + off_w(a.n_nodes, E, H, 0);
+      for (int i = tid; i < H * E + H; i += kRT) wsm[i] = __ldcg(P0 + i);
+      const float* P1 = P + off_w(a.n_nodes, E, H, 1);
+      const float* P2 = P + off_w(a.n_nodes, E, H, 2);
+      for (int i = tid; i < H * H; i += kRT) {
+        const int j = i / H, q = i - j * H;
+        wsm[so1 + j * (H + 1) + q] = __ldcg(P1 + i);
+        wsm[so2 + j * (H + 1) + q] = __ldcg(P2 + i);
+      }
+      for (int i = tid; i < H; i += kRT) {
+        wsm[so1 + H * (H + 1) + i] = __ldcg(P1 + H * H + i);
+        wsm[so2 + H * (H + 1) + i] = __ldcg(P2 + H * H + i);
+      }
+    }
     __syncthreads();
     for (int layer = 0; layer < 3; ++layer) {
-      const int in = layer == 0 ? E : H;
+      const int in = layer == 0 ? E : H, ldw = layer == 0 ? E : H + 1;
       const float* x = layer == 0 ? e : (layer == 1 ? a0 : a1);
-      const float* W = P + off_w(a.n_nodes, E, H, layer);
-      const float* B = W + H * in;
-      for (int j = tid; j < H; j += kThreads) {
-        float acc = __ldcg(B + j);
-        for (int i = 0; i < in; ++i) acc += __ldcg(W + j * in + i) * x[i];
+      const float* W = wsm + (layer == 0 ? 0 : (layer == 1 ? so1 : so2));
+      const float* B = W + H * ldw;
+      for (int j = tid; j < H; j += kRT) {
+        float acc = B[j];
+        for (int i = 0; i < in; ++i) acc += W[j * ldw + i] * x[i];
         if (layer == 0) { z0[j] = acc; a0[j] = acc > 0.f ? acc : 0.f; }
         else if (layer == 1) { z1[j] = acc; a1[j] = acc > 0.f ? acc : 0.f; }
         else f[j] = acc;
@@ -139,38 +170,43 @@ __global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
       __syncthreads();
     }
 
-    // ---- pass A: delta on the owned rows, partial |delta|^2 and W^T delta
-    float acc_h = 0.f, acc_sq = 0.f;
-    for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
-      const int64_t d0 = tIdx * kTR;
-      const int rows = (int)AFL_MIN((int64_t)kTR, a.rows - d0);
-      __syncthreads();
-      for (int i = tid; i < rows * H; i += kThreads) {
-        const int r = i / H, h = i - r * H;
-        tile[r * (H + 1) + h] = a.head_w[d0 * H + i];
+    // ---- pass A: delta on the owned rows, partial |delta|^2 and W^T delta.  One warp per row: lane l holds W[d][l + 32 j],
+    // the dot product is a shuffle reduction and the same registers feed W^T delta, so W_h is read exactly once, fully
+    // coalesced (a row is H contiguous floats), four rows in flight per warp.
+    {
+      const int lane = tid & 31, wib = tid >> 5, nwarp = kRT / 32;
+      const int64_t gw = (int64_t)blockIdx.x * nwarp + wib, nw = (int64_t)gridDim.x * nwarp;
+      constexpr int J = 4;                                  // H <= 128
+      float fl[J], acc[J];
+#pragma unroll
+      for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; fl[j] = h < H ? f[h] : 0.f; acc[j] = 0.f; }
+      float acc_sq = 0.f;
+      for (int64_t d = gw; d < a.rows; d += 4 * nw) {
+        float wv[4][J];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t dd = d + u * nw;
+#pragma unroll
+          for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; wv[u][j] = (dd < a.rows && h < H) ? a.head_w[dd * H + h] : 0.f; }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t dd = d + u * nw;
+          if (dd >= a.rows) break;
+          const float v = row_dot<J>(wv[u], fl);
+          const float dlt = (v + a.head_b[dd]) - theta[dd];
+          if (lane == 0) { a.delta[dd] = dlt; acc_sq += dlt * dlt; }
+#pragma unroll
+          for (int j = 0; j < J; ++j) acc[j] += wv[u][j] * dlt;
+        }
       }
       __syncthreads();
-      if (tid < rows) {
-        const float* tr = tile + tid * (H + 1);
-        float v = a.head_b[d0 + tid];
-        for (int h = 0; h < H; ++h) v += tr[h] * f[h];
-        const float d = v - theta[d0 + tid];
-        a.delta[d0 + tid] = d;
-        dl[tid] = d;
-        acc_sq += d * d;
-      }
+      if (lane == 0) atomicAdd(sred, acc_sq);
+#pragma unroll
+      for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; if (h < H) atomicAdd(sred + 1 + h, acc[j]); }
       __syncthreads();
-      if (tid < H) {
-        float v = 0.f;
-        for (int r = 0; r < rows; ++r) v += tile[r * (H + 1) + tid] * dl[r];
-        acc_h += v;
-      }
+      if (tid <= H) atomicAdd(red + tid, sred[tid]);
     }
-    __syncthreads();
-    if (tid < kTR) atomicAdd(sred, acc_sq);
-    if (tid < H) sred[1 + tid] = acc_h;
-    __syncthreads();
-    if (tid <= H) atomicAdd(red + tid, sred[tid]);
     if (!grid_sync(a.bar, ++bar_n * gridDim.x)) return;
 
     // ---- cross-rank sum of the H + 1 scalars (identical order on every rank)
@@ -211,24 +247,24 @@ __global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
     if (tid < H) g2[tid] = sred[1 + tid];
     __syncthreads();
     {
-      const float* W2 = P + off_w(a.n_nodes, E, H, 2);
-      for (int i = tid; i < H; i += kThreads) {
+      const float* W2 = wsm + so2;
+      for (int i = tid; i < H; i += kRT) {
         float v = 0.f;
-        for (int j = 0; j < H; ++j) v += __ldcg(W2 + j * H + i) * g2[j];
+        for (int j = 0; j < H; ++j) v += W2[j * (H + 1) + i] * g2[j];
         g1[i] = z1[i] > 0.f ? v : 0.f;
       }
       __syncthreads();
-      const float* W1 = P + off_w(a.n_nodes, E, H, 1);
-      for (int i = tid; i < H; i += kThreads) {
+      const float* W1 = wsm + so1;
+      for (int i = tid; i < H; i += kRT) {
         float v = 0.f;
-        for (int j = 0; j < H; ++j) v += __ldcg(W1 + j * H + i) * g1[j];
+        for (int j = 0; j < H; ++j) v += W1[j * (H + 1) + i] * g1[j];
         g0[i] = z0[i] > 0.f ? v : 0.f;
       }
       __syncthreads();
-      const float* W0 = P + off_w(a.n_nodes, E, H, 0);
-      for (int i = tid; i < E; i += kThreads) {
+      const float* W0 = wsm;
+      for (int i = tid; i < E; i += kRT) {
         float v = 0.f;
-        for (int j = 0; j < H; ++j) v += __ldcg(W0 + j * E + i) * g0[j];
+        for (int j = 0; j < H; ++j) v += W0[j * E + i] * g0[j];
         ge[i] = v;
       }
       __syncthreads();
@@ -258,7 +294,7 @@ __global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
     // ---- Adam on the replicated small parameters: the blocks share the index range (dense: every entry moves)
     {
       const int o0 = off_w(a.n_nodes, E, H, 0), o1 = off_w(a.n_nodes, E, H, 1), o2 = off_w(a.n_nodes, E, H, 2);
-      for (int i = blockIdx.x * kThreads + tid; i < a.tot; i += gridDim.x * kThreads) {
+      for (int i = blockIdx.x * kRT + tid; i < a.tot; i += gridDim.x * kRT) {
         float g = 0.f;
         if (i < o0) { const int r = i / E; g = r == c ? ge[i - r * E] : 0.f; }
         else if (i < o1) { const int q = i - o0; g = q < H * E ? g0[q / E] * e[q % E] : g0[q - H * E]; }
@@ -272,32 +308,45 @@ __global__ void __launch_bounds__(kThreads) hyper_round_kernel(HRArgs a) {
       }
     }
 
-    // ---- pass B: Adam on the owned rows of W_h / b_h (same tiles as pass A: no cross-block dependency on W_h)
-    for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
-      const int64_t d0 = tIdx * kTR;
-      const int rows = (int)AFL_MIN((int64_t)kTR, a.rows - d0);
-      for (int i = tid; i < rows * H; i += kThreads) {
-        const int r = i / H, h = i - r * H;
-        const int64_t it = d0 * H + i;
-        const float g = coef * a.delta[d0 + r] * f[h];
-        const float mi = a.b1 * a.mw[it] + (1.f - a.b1) * g;
-        const float vi = a.b2 * a.vw[it] + (1.f - a.b2) * g * g;
-        a.mw[it] = mi; a.vw[it] = vi;
-        a.head_w[it] -= stepsz * (mi / (sqrtf(vi) * isq + a.eps));
-      }
-      if (tid < rows) {
-        const int64_t d = d0 + tid;
-        const float g = coef * a.delta[d];
-        const float mi = a.b1 * a.mb[d] + (1.f - a.b1) * g;
-        const float vi = a.b2 * a.vb[d] + (1.f - a.b2) * g * g;
-        a.mb[d] = mi; a.vb[d] = vi;
-        a.head_b[d] -= stepsz * (mi / (sqrtf(vi) * isq + a.eps));
+    // ---- pass B: Adam on the owned rows of W_h / b_h (same row -> warp map as pass A: no cross-block dependency on W_h)
+    {
+      const int lane = tid & 31, wib = tid >> 5, nwarp = kRT / 32;
+      const int64_t gw = (int64_t)blockIdx.x * nwarp + wib, nw = (int64_t)gridDim.x * nwarp;
+      constexpr int J = 4;
+      float fl[J];
+#pragma unroll
+      for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; fl[j] = h < H ? f[h] : 0.f; }
+      for (int64_t d = gw; d < a.rows; d += 2 * nw) {
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int64_t dd = d + u * nw;
+          if (dd >= a.rows) break;
+          const float cd = coef * a.delta[dd];
+#pragma unroll
+          for (int j = 0; j < J; ++j) {
+            const int h = lane + 32 * j;
+            if (h < H) {
+              const int64_t it = dd * H + h;
+              const float g = cd * fl[j];
+              const float mi = a.b1 * a.mw[it] + (1.f - a.b1) * g;
+              const float vi = a.b2 * a.vw[it] + (1.f - a.b2) * g * g;
+              a.mw[it] = mi; a.vw[it] = vi;
+              a.head_w[it] -= stepsz * (mi / (sqrtf(vi) * isq + a.eps));
+            }
+          }
+          if (lane == 0) {
+            const float mi = a.b1 * a.mb[dd] + (1.f - a.b1) * cd;
+            const float vi = a.b2 * a.vb[dd] + (1.f - a.b2) * cd * cd;
+            a.mb[dd] = mi; a.vb[dd] = vi;
+            a.head_b[dd] -= stepsz * (mi / (sqrtf(vi) * isq + a.eps));
+          }
+        }
       }
     }
     if (!grid_sync(a.bar, ++bar_n * gridDim.x)) return;
   }
   if (a.n & 1)   // the current parameters ended in the second copy
-    for (int i = blockIdx.x * kThreads + tid; i < a.tot; i += gridDim.x * kThreads) a.small[i] = __ldcg(a.small_alt + i);
+    for (int i = blockIdx.x * kRT + tid; i < a.tot; i += gridDim.x * kRT) a.small[i] = __ldcg(a.small_alt + i);
 }
 
 // f [n][H] for n clients: one block per client (tiny)
@@ -329,31 +378,29 @@ __global__ void __launch_bounds__(kThreads) hyper_feat_kernel(const float* small
   }
 }
 
-// theta_j[lo + d] = W_h[d] . f_j + b_h[d] for the owned rows d, written through the pointer table
+// theta_j[lo + d] = W_h[d] . f_j + b_h[d] for the owned rows d, written through the pointer table.  One warp per row, the
+// row is loaded once and reused for all n clients; same arithmetic as pass A of the round kernel (row_dot).
 __global__ void __launch_bounds__(kThreads) hyper_emit_rows_kernel(const float* head_w, const float* head_b, int64_t rows,
                                                                    int64_t lo, const float* f_all, int n, int H,
                                                                    float* const* theta) {
   extern __shared__ float sm[];
   float* fs = sm;                       // [n][H]
-  float* tile = sm + n * H;             // [kTR][H + 1]
   for (int i = threadIdx.x; i < n * H; i += kThreads) fs[i] = f_all[i];
-  const int64_t n_tiles = (rows + kTR - 1) / kTR;
-  for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
-    const int64_t d0 = tIdx * kTR;
-    const int rr = (int)AFL_MIN((int64_t)kTR, rows - d0);
-    __syncthreads();
-    for (int i = threadIdx.x; i < rr * H; i += kThreads) {
-      const int r = i / H, h = i - r * H;
-      tile[r * (H + 1) + h] = head_w[d0 * H + i];
-    }
-    __syncthreads();
-    for (int it = threadIdx.x; it < rr * n; it += kThreads) {
-      const int j = it / rr, r = it - j * rr;          // consecutive threads -> consecutive rows of one client (coalesced)
-      const float* tr = tile + r * (H + 1);
-      const float* fj = fs + j * H;
-      float v = head_b[d0 + r];
-      for (int h = 0; h < H; ++h) v += tr[h] * fj[h];
-      theta[j][lo + d0 + r] = v;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nwarp = kThreads / 32;
+  const int64_t gw = (int64_t)blockIdx.x * nwarp + wib, nw = (int64_t)gridDim.x * nwarp;
+  constexpr int J = 4;
+  for (int64_t d = gw; d < rows; d += nw) {
+    float wv[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; wv[j] = h < H ? head_w[d * H + h] : 0.f; }
+    const float b = head_b[d];
+    for (int c = 0; c < n; ++c) {
+      float fl[J];
+#pragma unroll
+      for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; fl[j] = h < H ? fs[c * H + h] : 0.f; }
+      const float v = row_dot<J>(wv, fl);
+      if (lane == 0) theta[c][lo + d] = v + b;
     }
   }
 }
@@ -373,7 +420,7 @@ int afl_hyper_round(float* head_w, float* head_b, float* mw, float* vw, float* m
                     float clip, float* norms, void* stream) {
   AFL_CHECK_ARG(world >= 1 && world <= kMaxWorld, "afl_hyper_round: world size must be 1..16");
   AFL_CHECK_ARG(n >= 0 && n <= n_max, "afl_hyper_round: more clients than the exchange buffer holds");
-  AFL_CHECK_ARG(H <= kThreads - 1 && H >= 1 && E >= 1, "afl_hyper_round: hidden width must be < 256");
+  AFL_CHECK_ARG(H <= 128 && H >= 1 && E >= 1, "afl_hyper_round: hidden width must be <= 128");
   if (n == 0) return 0;
   HRArgs a;
   a.head_w = head_w; a.head_b = head_b; a.mw = mw; a.vw = vw; a.mb = mb; a.vb = vb; a.rows = rows; a.lo = lo;
@@ -389,17 +436,17 @@ int afl_hyper_round(float* head_w, float* head_b, float* mw, float* vw, float* m
   cudaStream_t st = (cudaStream_t)stream;
   AFL_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * (size_t)(H + 1), st));
   AFL_CUDA(cudaMemsetAsync(bar, 0, sizeof(uint32_t) * 2, st));
-  const size_t smem = sizeof(float) * (size_t)(2 * E + 9 * H + kTR + kTR * (H + 1) + (H + 1));
+  const size_t smem = sizeof(float) * (size_t)(2 * E + 9 * H + kTR + (H + 1) + H * E + H + 2 * (H * (H + 1) + H));
   AFL_CUDA(cudaFuncSetAttribute(hyper_round_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 1;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hyper_round_kernel, kThreads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
-  if (per_sm > 4) per_sm = 4;
-  const int64_t tiles = (rows + kTR - 1) / kTR;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hyper_round_kernel, kRT, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (per_sm > 2) per_sm = 2;
+  const int64_t tiles = (rows + 127) / 128;               // at least 4 rows per warp before a block is worth launching
   int64_t cap = (int64_t)per_sm * afl_rt::num_sms();
   int grid = (int)(tiles < cap ? tiles : cap);
   if (grid < 1) grid = 1;
   void* args[] = {&a};
-  AFL_CUDA(cudaLaunchCooperativeKernel((const void*)hyper_round_kernel, dim3(grid), dim3(kThreads), args, smem, st));
+  AFL_CUDA(cudaLaunchCooperativeKernel((const void*)hyper_round_kernel, dim3(grid), dim3(kRT), args, smem, st));
   afl_rt::count_launch();
   return afl_rt::check_last("afl_hyper_round");
 }
@@ -410,11 +457,11 @@ int afl_hyper_emit_rows(const float* head_w, const float* head_b, int64_t rows, 
   if (n == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
   hyper_feat_kernel<<<n, kThreads, sizeof(float) * 2 * (size_t)AFL_MAX(H, E), st>>>(small, n_nodes, E, H, clients_dev, n, f_scratch);
-  const size_t smem = sizeof(float) * ((size_t)n * H + (size_t)kTR * (H + 1));
-  AFL_CHECK_ARG(smem <= 200 * 1024, "afl_hyper_emit_rows: too many clients per call for shared memory (chunk them)");
+  const size_t smem = sizeof(float) * (size_t)n * H;
+  AFL_CHECK_ARG(smem <= 200 * 1024 && H <= 128, "afl_hyper_emit_rows: too many clients per call for shared memory (chunk them)");
   AFL_CUDA(cudaFuncSetAttribute(hyper_emit_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t tiles = (rows + kTR - 1) / kTR;
-  int64_t cap = 2LL * afl_rt::num_sms();
+  const int64_t tiles = (rows + 7) / 8;
+  int64_t cap = 4LL * afl_rt::num_sms();
   int grid = (int)(tiles < cap ? tiles : cap);
   if (grid < 1) grid = 1;
   hyper_emit_rows_kernel<<<grid, kThreads, smem, st>>>(head_w, head_b, rows, lo, f_scratch, n, H, theta_dev);
