@@ -433,6 +433,7 @@ int afl_fedavg_fused(const float* local_rows, const float* weights, int CL, int6
   if (per_sm > 4) per_sm = 4;
   const int64_t items = (d_pad / 4 + kThreads - 1) / kThreads;
   int64_t cap = (int64_t)per_sm * afl_rt::num_sms();
+  if (const char* ev = getenv("ATTACKFL_FUSED_MAX_BLOCKS")) { const int64_t m = atoi(ev); if (m >= 1 && m < cap) cap = m; }   // tests: several emulated ranks on one GPU
   int grid = (int)(items < cap ? items : cap);
   if (grid < 1) grid = 1;
   AFL_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, smem, st));

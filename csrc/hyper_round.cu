@@ -21,6 +21,7 @@
 // (pointer table; peer-mapped pointers make it the scatter of the personalised models, server.py:589-590).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../include/attackfl_b200.h"
 #include "flat_core.h"
@@ -443,6 +444,7 @@ int afl_hyper_round(float* head_w, float* head_b, float* mw, float* vw, float* m
   if (per_sm > 2) per_sm = 2;
   const int64_t tiles = (rows + 127) / 128;               // at least 4 rows per warp before a block is worth launching
   int64_t cap = (int64_t)per_sm * afl_rt::num_sms();
+  if (const char* ev = getenv("ATTACKFL_FUSED_MAX_BLOCKS")) { const int64_t m = atoi(ev); if (m >= 1 && m < cap) cap = m; }   // tests: emulated ranks on one GPU
   int grid = (int)(tiles < cap ? tiles : cap);
   if (grid < 1) grid = 1;
   void* args[] = {&a};

@@ -60,3 +60,46 @@ def test_sharded_rows_give_the_same_update_as_one_shard():
         nat.emit_rows(ids, [out[j].data_ptr() for j in range(len(ids))])
     torch.cuda.synchronize()
     assert torch.allclose(out, dense, atol=1e-6)
+
+
+def test_two_emulated_ranks_share_one_round(monkeypatch):
+    """Row-sharded round on ONE GPU: two "ranks" (disjoint row shards, concurrent cooperative launches on two streams) exchange
+    their H + 1 partial sums through the flag protocol, exactly as two GPUs do (minus the NVLink hop).  The result must equal
+    the unsharded round."""
+    import ctypes
+    monkeypatch.setenv("ATTACKFL_FUSED_MAX_BLOCKS", "60")        # both grids must be co-resident
+    n = 4
+    lay, fused_a = _net(n)
+    fused_b, fused_ref = copy.deepcopy(fused_a), copy.deepcopy(fused_a)
+    torch.manual_seed(3)
+    rows = torch.stack([lay.flatten(models.build("TransformerModel").state_dict()) for _ in range(n)]).cuda()
+    order = [1, 3, 0, 2]
+    ptrs = [rows[c].data_ptr() for c in order]
+    ref = NativeHyper(fused_ref)
+    ref.round(order, ptrs, 1e-3, 1.0)
+    half = lay.padded // 2
+    H = fused_a.H
+    xch = [torch.zeros(n * 2 * (H + 1), device="cuda") for _ in range(2)]
+    sig = [torch.zeros(n * 2, dtype=torch.int32, device="cuda") for _ in range(2)]
+    PA = ctypes.c_void_p * 2
+    xp, sp = PA(*[t.data_ptr() for t in xch]), PA(*[t.data_ptr() for t in sig])
+    nats = [NativeHyper(fused_a), NativeHyper(fused_b)]
+    nats[0].setup_round(0, half, 2, 0, n, xp, sp)
+    nats[1].setup_round(half, lay.padded, 2, 1, n, xp, sp)
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    torch.cuda.synchronize()
+    for r in range(2):
+        with torch.cuda.stream(streams[r]):
+            nats[r].round(order, ptrs, 1e-3, 1.0)
+    torch.cuda.synchronize()
+    for r in range(2):
+        assert nats[r].check_round_error() == 0
+        nats[r].unpack()
+    ref.unpack()
+    lo_hi = ((0, half), (half, lay.padded))
+    for r, f in enumerate((fused_a, fused_b)):
+        lo, hi = lo_hi[r]
+        assert torch.allclose(f.head_w[lo:hi], fused_ref.head_w[lo:hi], atol=2e-6, rtol=1e-4)
+        assert torch.allclose(f.head_b[lo:hi], fused_ref.head_b[lo:hi], atol=2e-6, rtol=1e-4)
+        for k in ("emb", "mlp_w0", "mlp_w2", "mlp_b1"):          # the replicated small parameters stay identical on both ranks
+            assert torch.allclose(f.trainable()[k], fused_ref.trainable()[k], atol=2e-6, rtol=1e-4), k
