@@ -45,6 +45,8 @@ def bench_config(n_clients: int) -> dict:
         "name": "bench: BASELINE config 3",
         "server": {"num-round": 10 ** 6, "clients": n_clients, "mode": "fedavg", "model": MODEL, "data-name": "ICU",
                    "validation": True, "genuine-rate": 0.5, "random-seed": 1,
+                   "common-init": False,      # reference semantics: every client starts from its own random init
+
                    "data-distribution": {"num-data-range": [12000, 15000]},
                    "hyper-detection": {"enable": False, "cosine-search": 10, "n_components": 3, "eps": 0.007,
                                        "min_samples": 3},
