@@ -92,6 +92,12 @@ def stash_floats_per_client(device) -> int:
     return int(lib.afl_tc_stash_floats_per_client())
 
 
+def last_cluster(device) -> int:
+    """CTAs per client the last ``train_round_tc`` call of this process used (1, 2, 4 or 8)."""
+    lib = lib_for(torch.empty(0, device=device))
+    return int(lib.afl_tc_last_cluster())
+
+
 def train_round_tc(layout: FlatLayout, w: torch.Tensor, m: torch.Tensor, v: Optional[torch.Tensor], gw: torch.Tensor,
                    stash: torch.Tensor, data: torch.Tensor, idx: torch.Tensor, n_data: torch.Tensor,
                    client_ids: torch.Tensor, batch: int, epochs: int, *, optimizer: str = "adam", lr: float = 0.004,

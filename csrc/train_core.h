@@ -1017,6 +1017,20 @@ struct AflOpt {
   float clip_coef;     // gradient scale (1 = none)
 };
 
+// One 128-bit chunk of the update (stepsz = lr / bc1, isq = 1 / sqrt(bc2)); vv is only touched by Adam.
+AFL_DEV void afl_opt_apply4(float4& wv, float4& mv, float4& vv, const float4& g, const AflOpt& o, float stepsz, float isq) {
+  if (o.kind == 0) {
+#define AFL_UPD(c) { const float gg = g.c * o.clip_coef; mv.c = o.beta1 * mv.c + (1.f - o.beta1) * gg; \
+      vv.c = o.beta2 * vv.c + (1.f - o.beta2) * gg * gg; wv.c -= stepsz * (mv.c / (sqrtf(vv.c) * isq + o.eps)); }
+    AFL_UPD(x) AFL_UPD(y) AFL_UPD(z) AFL_UPD(w)
+#undef AFL_UPD
+  } else {
+#define AFL_UPD(c) { const float gg = g.c * o.clip_coef; mv.c = o.first_step ? gg : o.momentum * mv.c + gg; wv.c -= o.lr * mv.c; }
+    AFL_UPD(x) AFL_UPD(y) AFL_UPD(z) AFL_UPD(w)
+#undef AFL_UPD
+  }
+}
+
 // Reduce G partial rows over [lo, hi) and apply the update.  gpart: [G][d_pad].
 AFL_DEV void afl_reduce_update(float* w, float* m, float* v, const float* gpart, int G, int64_t d_pad,
                                int64_t lo, int64_t hi, const AflOpt& o, int tid, int nt) {
@@ -1038,18 +1052,10 @@ AFL_DEV void afl_reduce_update(float* w, float* m, float* v, const float* gpart,
     }
     float4 mv = *reinterpret_cast<const float4*>(m + i);
     float4 wv = *reinterpret_cast<const float4*>(w + i);
-    if (o.kind == 0) {
-      float4 vv = *reinterpret_cast<const float4*>(v + i);
-#define AFL_UPD(c) { const float gg = g.c * o.clip_coef; mv.c = o.beta1 * mv.c + (1.f - o.beta1) * gg; \
-        vv.c = o.beta2 * vv.c + (1.f - o.beta2) * gg * gg; wv.c -= stepsz * (mv.c / (sqrtf(vv.c) * isq + o.eps)); }
-      AFL_UPD(x) AFL_UPD(y) AFL_UPD(z) AFL_UPD(w)
-#undef AFL_UPD
-      *reinterpret_cast<float4*>(v + i) = vv;
-    } else {
-#define AFL_UPD(c) { const float gg = g.c * o.clip_coef; mv.c = o.first_step ? gg : o.momentum * mv.c + gg; wv.c -= o.lr * mv.c; }
-      AFL_UPD(x) AFL_UPD(y) AFL_UPD(z) AFL_UPD(w)
-#undef AFL_UPD
-    }
+    float4 vv; vv.x = vv.y = vv.z = vv.w = 0.f;
+    if (o.kind == 0) vv = *reinterpret_cast<const float4*>(v + i);
+    afl_opt_apply4(wv, mv, vv, g, o, stepsz, isq);
+    if (o.kind == 0) *reinterpret_cast<float4*>(v + i) = vv;
     *reinterpret_cast<float4*>(m + i) = mv;
     *reinterpret_cast<float4*>(w + i) = wv;
   }

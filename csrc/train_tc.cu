@@ -55,7 +55,8 @@ enum { TM_WV_K = 0, TM_WO_K = 2, TM_WF0_K = 4, TM_W1_K = 6, TM_W2_K = 7, TM_WV_M
 
 // ---- mbarriers
 enum { B_STEP = 0, B_A = 1 /*V,L,H*/, B_ACC = 4, B_DW = 7, B_WF_V = 10 /*Wv*/, B_WF_O = 12 /*Wo*/, B_WF_W1 = 14, B_WF_W2 = 15,
-       B_WB = 16 /*[s][2]*/, B_X = 20 /*[s]*/, B_N = 22 };
+       B_WB = 16 /*[s][2]*/, B_X = 20 /*[s]*/, B_GO = 22 /*helper CTAs: optimiser pass may start*/,
+       B_DONE = 23 /*main CTA: every helper finished its share*/, B_N = 24 };
 
 // ---- TMEM columns
 constexpr uint32_t kColA = 0;             // A operands: V 0..63, L 64..127 (cat = 0..127)
@@ -81,6 +82,7 @@ struct TcParams {
   int n_ranges; int range_lo[16], range_hi[16];
   float* loss_out; int32_t* steps_out;
   long long* dbg;        // optional [64] clock64 stamps of thread 0 of client 0 at step 5 (profiling aid), or null
+  int cluster;           // CTAs per client: rank 0 trains, ranks 1.. take a share of the optimiser pass (L2-bandwidth bound on one SM)
 };
 
 struct TcMaps { CUtensorMap m[TM_N]; };
@@ -154,6 +156,36 @@ __device__ __forceinline__ void mbar_wait_to(uint64_t* bar, uint32_t parity) {
 }
 
 __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// ---- cluster helpers (optimiser pass shared between the CTAs of a client's cluster)
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(const void* smem_ptr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(smem_ptr)), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void remote_arrive(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void remote_st_f32(uint32_t cluster_addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(cluster_addr), "f"(v) : "memory");
+}
+// wait on a barrier of this CTA that CTAs of the cluster arrive on (cluster-scope acquire); same time-out as mbar_wait_to
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  const long long t0 = clock64();
+  for (uint32_t it = 0;; ++it) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
+        : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    if (ok) return;
+    if ((it & 255u) == 255u && clock64() - t0 > 4000000000LL) __trap();
+  }
+}
 __device__ __forceinline__ void bar_named(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
 // One lane of a converged warp.  ptxas recognises elect.sync, so a tcgen05 / TMA instruction guarded by it is issued once
@@ -380,8 +412,11 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int c = blockIdx.x;
+  const int CS = P.cluster;
+  const uint32_t crank = CS > 1 ? cluster_rank() : 0u;
+  const int c = blockIdx.x / CS;
   const TcLay& L = P.L;
+  float* ccoef = reinterpret_cast<float*>(smem + kOffMisc + 100);   // clip coefficient handed to a helper CTA
 
   // ---- one-time set-up
   for (uint32_t i = tid; i < (kOffBar) / 4; i += kThreads) reinterpret_cast<uint32_t*>(smem)[i] = 0u;
@@ -390,23 +425,150 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
   float* vrow = P.v ? P.v + (int64_t)c * P.d_pad : nullptr;
   float* gw = P.gw + (int64_t)c * P.d_pad;
   float* stash = P.stash + (int64_t)c * kNSlot * kSlotF;
-  for (int64_t i = tid; i < P.d_pad; i += kThreads) gw[i] = 0.f;
+  if (crank == 0) for (int64_t i = tid; i < P.d_pad; i += kThreads) gw[i] = 0.f;
   __syncthreads();
   if (tid == 0) {
     for (int b = 0; b < B_N; ++b) {
-      const uint32_t cnt = (b == B_STEP || b == B_A + 2) ? 16u : (b == B_A || b == B_A + 1) ? 8u : 1u;
+      const uint32_t cnt = (b == B_STEP || b == B_A + 2) ? 16u : (b == B_A || b == B_A + 1) ? 8u
+                         : (b == B_DONE && CS > 1) ? (uint32_t)(CS - 1) : 1u;
       mbar_init(&bars[b], cnt);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 0) tmem_alloc(tslot, 512);
+  if (warp == 0 && crank == 0) tmem_alloc(tslot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (CS > 1) cluster_sync_all();            // every CTA's barriers exist before a peer arrives on them
   const uint32_t tmem = *tslot;
 
   const int n = P.n_data[c];
   const int steps_per_epoch = (n + P.batch - 1) / P.batch;
+
+  // This thread's share of one optimiser pass: the merged parameter ranges are dealt out in 128-bit chunks over the
+  // element-wise threads of all CTAs of the cluster, two chunks per thread and pass (8 independent loads in flight).
+  auto opt_share = [&](const AflOpt& o, int vt, int nvt) {
+    for (int r = 0; r < P.n_ranges; ++r) {
+      const int64_t lo = P.range_lo[r], hi = P.range_hi[r], span = 4 * (int64_t)nvt;
+      for (int64_t i = lo + 4 * (int64_t)vt; i < hi; i += 2 * span) {
+        const bool two = i + span < hi;
+        afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, i, i + 4, o, 0, 1);
+        if (two) afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, i + span, i + span + 4, o, 0, 1);
+      }
+    }
+  };
+
+  if (crank != 0) {
+    // =================================================================================== helper CTA of the cluster
+    // The optimiser pass reads g, w, m, v and writes w, m, v of every parameter: on one SM it is bound by that SM's L2
+    // bandwidth (27 K of the step's 172 K cycles).  The helpers wait for the main CTA's gradients, update their share
+    // of the row and report back; they own no TMEM, no tensor maps and no data.
+    if (warp == 0) return;
+    const int etid = tid - 32;
+    const int skipped = (n % P.batch) == 1 ? 1 : 0;            // a trailing batch of one sample is skipped (client.py:86-87)
+    const int total = P.batch == 1 ? 0 : P.epochs * (steps_per_epoch - skipped);
+    const uint32_t done0 = map_to_rank(&bars[B_DONE], 0);
+    // The merged ranges as one flat list of 128-bit chunks, dealt out over the threads of all helpers: chunk q of thread
+    // vt in batch j is q = (4 j' + j) * NT + vt.  A thread's chunks never change, so the optimiser state of its first
+    // batch is fetched BEFORE the hand-over (while the main CTA is still in its backward pass) and only the gradient is
+    // read after it: one L2 round trip on the critical path instead of one per range.
+    const int NT = (CS - 1) * kEpi, vt = ((int)crank - 1) * kEpi + etid;
+    int total_chunks = 0;
+    for (int r = 0; r < P.n_ranges; ++r) total_chunks += (P.range_hi[r] - P.range_lo[r]) >> 2;
+    auto chunk_off = [&](int q) -> int {
+      if (q >= total_chunks) return -1;
+      for (int r = 0; r < P.n_ranges; ++r) {
+        const int nr = (P.range_hi[r] - P.range_lo[r]) >> 2;
+        if (q < nr) return P.range_lo[r] + 4 * q;
+        q -= nr;
+      }
+      return -1;
+    };
+    int off0[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) off0[j] = chunk_off(j * NT + vt);
+    const bool adam = P.opt_kind == 0;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    // With one batch per thread (clusters of 8 on this model) the share stays in registers for the whole round: no state
+    // loads at all after the first step, and the moments are written back once at the end.
+    const bool resident = total_chunks <= 4 * NT;
+    double b1t = 1.0, b2t = 1.0;
+    float4 W[4], M[4], V[4], G[4];
+    for (int k = 0; k < total; ++k) {
+      if (k == 0 || !resident) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          W[j] = M[j] = V[j] = z4;
+          if (off0[j] >= 0) {
+            W[j] = __ldcg(reinterpret_cast<const float4*>(w + off0[j]));
+            M[j] = __ldcg(reinterpret_cast<const float4*>(mrow + off0[j]));
+            if (adam) V[j] = __ldcg(reinterpret_cast<const float4*>(vrow + off0[j]));
+          }
+        }
+      }
+      const bool put_state = !resident || k == total - 1;
+      b1t *= (double)P.beta1; b2t *= (double)P.beta2;
+      AflOpt o;
+      o.kind = P.opt_kind; o.lr = P.lr; o.beta1 = P.beta1; o.beta2 = P.beta2; o.eps = P.eps;
+      o.momentum = P.momentum; o.bc1 = (float)(1.0 - b1t); o.bc2 = (float)(1.0 - b2t);
+      o.first_step = k == 0;
+      const float stepsz = o.lr / o.bc1, isq = 1.0f / sqrtf(o.bc2);
+#define HS(i) do { if (P.dbg && c == 0 && crank == 1 && etid == 0 && k == 5) P.dbg[52 + (i)] = clock64(); } while (0)
+      HS(0);
+      mbar_wait_cluster(&bars[B_GO], (uint32_t)k & 1u);      // acquire: the gradient row (read below with L2 loads)
+      HS(1);
+      o.clip_coef = P.clip_proper ? *ccoef : 1.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) G[j] = off0[j] >= 0 ? __ldcg(reinterpret_cast<const float4*>(gw + off0[j])) : z4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (off0[j] >= 0) {
+          afl_opt_apply4(W[j], M[j], V[j], G[j], o, stepsz, isq);
+          __stcg(reinterpret_cast<float4*>(w + off0[j]), W[j]);
+          if (put_state) {
+            __stcg(reinterpret_cast<float4*>(mrow + off0[j]), M[j]);
+            if (adam) __stcg(reinterpret_cast<float4*>(vrow + off0[j]), V[j]);
+          }
+        }
+      }
+      for (int base = 4 * NT; base < total_chunks; base += 4 * NT) {        // small clusters: further batches
+        int off[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) off[j] = chunk_off(base + j * NT + vt);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          W[j] = M[j] = V[j] = G[j] = z4;
+          if (off[j] >= 0) {
+            G[j] = __ldcg(reinterpret_cast<const float4*>(gw + off[j]));
+            W[j] = __ldcg(reinterpret_cast<const float4*>(w + off[j]));
+            M[j] = __ldcg(reinterpret_cast<const float4*>(mrow + off[j]));
+            if (adam) V[j] = __ldcg(reinterpret_cast<const float4*>(vrow + off[j]));
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (off[j] >= 0) {
+            afl_opt_apply4(W[j], M[j], V[j], G[j], o, stepsz, isq);
+            __stcg(reinterpret_cast<float4*>(w + off[j]), W[j]);
+            __stcg(reinterpret_cast<float4*>(mrow + off[j]), M[j]);
+            if (adam) __stcg(reinterpret_cast<float4*>(vrow + off[j]), V[j]);
+          }
+        }
+      }
+      HS(2);
+      bar_named(13, kEpi);
+      HS(3);
+      if (etid == 0) {
+        // one cumulative release for the whole CTA (the barrier ordered every thread's stores before this fence); the
+        // proxy fence covers the main CTA's TMA re-read of the weights this CTA just wrote
+        __threadfence();
+        fence_async();
+        remote_arrive(done0);
+        HS(4);
+      }
+    }
+    return;
+  }
 
   if (warp == 0) {
     // =================================================================================== producer warp
@@ -1296,16 +1458,25 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
           o.clip_coef = coef < 1.f ? coef : 1.f;
           bar_named(13, kEpi);
         }
-        for (int r = 0; r < P.n_ranges; ++r) {
-          // two 128-bit chunks per thread and pass: 8 independent loads in flight hide part of the L2 latency of this tail
-          const int64_t lo = P.range_lo[r], hi = P.range_hi[r], span = 4 * (int64_t)kEpi;
-          for (int64_t i = lo + 4 * (int64_t)etid; i < hi; i += 2 * span) {
-            const bool two = i + span < hi;
-            afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, i, i + 4, o, 0, 1);
-            if (two) afl_reduce_update(w, mrow, vrow, gw, 1, P.d_pad, i + span, i + span + 4, o, 0, 1);
+        TS2(8);
+        if (CS > 1) {
+          // The helpers take the whole pass.  Lane 0's fence is the one cumulative GPU-scope release for the gradient row
+          // (the barrier above ordered every thread's stores before it); after the warp sync, lane r hands over to rank r.
+          if (ew == 0) {
+            if (lane == 0) __threadfence();
+            __syncwarp();
+            if (lane >= 1 && lane < CS) {
+              if (P.clip_proper) remote_st_f32(map_to_rank(ccoef, (uint32_t)lane), o.clip_coef);
+              remote_arrive(map_to_rank(&bars[B_GO], (uint32_t)lane));
+            }
           }
+          TS2(9);
+          mbar_wait_cluster(&bars[B_DONE], (uint32_t)(opt_steps - 1) & 1u);
+        } else {
+          opt_share(o, etid, kEpi);
+          __threadfence_block();
         }
-        __threadfence_block();
+        TS2(11);
         bar_named(13, kEpi);
         TSTAMP();
         load_small();
@@ -1323,7 +1494,7 @@ tc_train_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcP
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+  if (warp == 0) tmem_dealloc(tmem, 512);      // (helper CTAs returned above: only the main CTA owns TMEM)
 }
 
 int make_map3(CUtensorMap* map, const void* base, int64_t d0, int64_t d1, int64_t d2, int64_t ld1_elems, int64_t ld2_elems,
@@ -1344,6 +1515,7 @@ int make_map3(CUtensorMap* map, const void* base, int64_t d0, int64_t d1, int64_
 }  // namespace
 
 static long long* g_tc_dbg = nullptr;
+static int g_tc_last_cluster = 1;
 
 extern "C" {
 
@@ -1351,6 +1523,9 @@ extern "C" {
 void afl_tc_set_debug(long long* dev_buf) { g_tc_dbg = dev_buf; }
 
 int afl_tc_stash_floats_per_client(void) { return kNSlot * kSlotF; }
+
+/* CTAs per client (cluster size) chosen by the last afl_tc_train_round call of this process. */
+int afl_tc_last_cluster(void) { return g_tc_last_cluster; }
 
 int afl_tc_train_round(const int32_t* lay, int lay_words, float* w, float* m, float* v, float* gw, float* stash, int64_t d_pad,
                        const float* data, int rec, const int32_t* idx, int64_t idx_stride_c, int64_t idx_stride_e,
@@ -1398,7 +1573,40 @@ int afl_tc_train_round(const int32_t* lay, int lay_words, float* w, float* m, fl
   AFL_CUDA(cudaFuncSetAttribute(tc_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
   cudaStream_t st = (cudaStream_t)stream;
   AFL_CUDA(cudaMemsetAsync(loss_out, 0, sizeof(float) * 2 * (size_t)n_clients, st));
-  tc_train_kernel<<<n_clients, kThreads, kSmemBytes, st>>>(maps, P);
+  // CTAs per client: clusters of 8 (the portable limit) when every client's cluster can be resident at once, else one CTA
+  // per client.  Measured on B200 (8 clients, us / optimiser step): 1 CTA 83.4, 2 CTAs 95.5, 4 CTAs 85.6, 8 CTAs 81.7 -- the
+  // hand-over costs two fences and two DSMEM round trips, which only seven helpers' worth of parallel update math repays.
+  // ATTACKFL_TC_CLUSTER=1|2|4|8 overrides (tests).
+  int cs = 1;
+  {
+    int forced = 0;
+    if (const char* e = getenv("ATTACKFL_TC_CLUSTER")) forced = atoi(e);
+    for (int cand = 8; cand > 1; cand >>= 1) {
+      if (forced ? cand != forced : cand != 8) continue;
+      cudaLaunchConfig_t q = {};
+      q.gridDim = dim3((unsigned)(n_clients * cand)); q.blockDim = dim3(kThreads); q.dynamicSmemBytes = kSmemBytes;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = (unsigned)cand; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+      q.attrs = qa; q.numAttrs = 1;
+      int max_clusters = 0;
+      if (cudaOccupancyMaxActiveClusters(&max_clusters, tc_train_kernel, &q) != cudaSuccess) { (void)cudaGetLastError(); continue; }
+      if (max_clusters >= n_clients) { cs = cand; break; }
+    }
+  }
+  g_tc_last_cluster = cs;
+  P.cluster = cs;
+  if (cs == 1) {
+    tc_train_kernel<<<n_clients, kThreads, kSmemBytes, st>>>(maps, P);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(n_clients * cs)); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = kSmemBytes; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    AFL_CUDA(cudaLaunchKernelEx(&cfg, tc_train_kernel, maps, P));
+  }
   afl_rt::count_launch();
   return afl_rt::check_last("afl_tc_train_round");
 }

@@ -252,6 +252,22 @@ int afl_train_round(const int32_t* ops_dev, int n_ops, int pool_floats, float* w
                     int M, int S, int batch, int epochs, int opt_kind, float lr, float beta1, float beta2, float eps,
                     float momentum, int clip_proper, float clip, uint64_t seed, int dropout, float* loss_out,
                     int32_t* steps_out, uint32_t* bar, float* gnorm, int chain, void* stream);
+/* Tensor-core trainer of the ICU TransformerModel (client.py:75-111, src/Model.py:184-246): one cluster of CTAs per client,
+ * the whole batch (<= 128 samples) is one tcgen05 M tile, every contraction a tf32 MMA with fp32 TMEM accumulators.  `lay`
+ * is the TcLay word list built by attackfl_b200/ops/train_tc.py:build_layout; `ranges` [2 * n_ranges] the merged parameter
+ * ranges the optimiser walks; gw [n_clients][d_pad] and stash [n_clients][afl_tc_stash_floats_per_client()] are scratch
+ * (stash zero-initialised once by the caller).  loss_out [n_clients][2] = (sum of batch losses, NaN count).  The CTAs of a
+ * cluster beyond the first share the optimiser pass; afl_tc_last_cluster() reports the size the last call chose
+ * (ATTACKFL_TC_CLUSTER=1|2|4|8 forces one). */
+int afl_tc_train_round(const int32_t* lay, int lay_words, float* w, float* m, float* v, float* gw, float* stash,
+                       int64_t d_pad, const float* data, int rec, const int32_t* idx, int64_t idx_stride_c,
+                       int64_t idx_stride_e, const int32_t* n_data, const int32_t* client_ids, int n_clients, int batch,
+                       int epochs, int opt_kind, float lr, float beta1, float beta2, float eps, float momentum,
+                       int clip_proper, float clip, uint64_t seed, int dropout, float p1, float p3, const int32_t* ranges,
+                       int n_ranges, float* loss_out, int32_t* steps_out, void* stream);
+int afl_tc_stash_floats_per_client(void);
+int afl_tc_last_cluster(void);
+void afl_tc_set_debug(long long* dev_buf);
 /* Batched inference of n_models rows over the same records (src/Validation.py:92-122,178-213); probs [n_models][n_rows]. */
 int afl_infer(const int32_t* ops_dev, int n_ops, int pool_floats, const float* w, int64_t d_pad, int n_models,
               const float* data, int rec, int64_t n_rows, float* probs, int S, void* stream);

@@ -31,7 +31,7 @@ for C in [int(x) for x in os.environ.get("PROF_CLIENTS", "8").split(",")]:
         e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         st = int(steps[0])
-        print(f"C={C} tc train launch {ms:.3f} ms, {st} steps/client, {1e3 * ms / max(st,1):.1f} us/step, loss {float(loss[0,0])/n/epochs:.4f}")
+        print(f"C={C} cluster={TC.last_cluster(dev)} tc train launch {ms:.3f} ms, {st} steps/client, {1e3 * ms / max(st,1):.1f} us/step, loss {float(loss[0,0])/n/epochs:.4f}")
 if os.environ.get("PROF_STAMPS"):
     import ctypes
     from attackfl_b200.ops import native
@@ -48,3 +48,5 @@ if os.environ.get("PROF_STAMPS"):
     print("stamps (cycles):", " ".join(f"{names[i] if i < len(names) else i}:{t[i + 1] - t[i]}" for i in range(k)), "total", t[k] - t[0])
     print("E3 detail:", [t[32 + i + 1] - t[32 + i] for i in range(6)], "abs0", t[32] - t[0])
     print("producer P3(V): start", t[48] - t[0], "wait_a", t[49] - t[48], "wait_w", t[50] - t[49], "issue", t[51] - t[50], "; E3 TS2(0) at", t[32] - t[0], "TS2(5) at", t[37] - t[0])
+    print("optimiser hand-over (main): fence+arrives", t[41] - t[40], "wait helpers", t[43] - t[41])
+    print("optimiser hand-over (helper 1): early for", t[53] - t[52], "grad load+update+stores", t[54] - t[53], "barrier", t[55] - t[54], "fence+arrive", t[56] - t[55])

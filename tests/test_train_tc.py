@@ -139,3 +139,48 @@ def test_proper_clip_and_sgd_momentum():
     for c in range(2):
         d_ref, d_got = ref[c] - rows[c], got[c] - rows[c]
         assert float((d_got - d_ref).norm() / d_ref.norm()) < 1e-2
+
+
+@pytest.mark.parametrize("cluster", [2, 4, 8])
+def test_cluster_shared_optimiser_pass_matches_one_cta(cluster, monkeypatch):
+    """The helper CTAs of a client's cluster only take shares of the element-wise optimiser pass, so every cluster size
+    must reproduce the one-CTA result up to the run-to-run noise of the kernel's floating-point atomics (column sums and
+    the loss are accumulated with shared-memory atomics); a lost or early hand-over would show up as a stale gradient or
+    weight, orders of magnitude above that noise.
+    Ragged clients (one with a skipped trailing batch of one sample), dropout on, then SGD-momentum with the proper clip
+    (the clip coefficient travels to the helpers through distributed shared memory)."""
+    _, lay = _setup(5)
+    ds = synthetic_icu(1500, 17)
+    n_data = [300, 257, 1024, 128, 640]
+    epochs = 3
+    idx = make_round_indices(1500, n_data, epochs, torch.Generator().manual_seed(11))
+    rows = torch.stack([lay.flatten(models.build(NAME).state_dict()) for _ in n_data])
+    runs = [dict(lr=0.004, seed=5), dict(optimizer="sgd", lr=0.05, momentum=0.5, clip_proper=True, clip=0.05, seed=6)]
+    for kw in runs:
+        monkeypatch.setenv("ATTACKFL_TC_CLUSTER", "1")
+        ref, rloss, rsteps, _ = _tc(lay, rows, ds, idx, n_data, 128, epochs, True, **kw)
+        ref2, _, _, _ = _tc(lay, rows, ds, idx, n_data, 128, epochs, True, **kw)
+        assert TC.last_cluster("cuda") == 1
+        monkeypatch.setenv("ATTACKFL_TC_CLUSTER", str(cluster))
+        got, loss, steps, _ = _tc(lay, rows, ds, idx, n_data, 128, epochs, True, **kw)
+        assert TC.last_cluster("cuda") == cluster
+        assert steps.tolist() == rsteps.tolist()
+        assert torch.allclose(loss, rloss, rtol=1e-4)
+        for c in range(len(n_data)):
+            upd = float((ref[c] - rows[c]).norm())
+            noise = float((ref2[c] - ref[c]).norm()) / upd
+            diff = float((got[c] - ref[c]).norm()) / upd
+            assert diff <= max(4 * noise, 2e-4), (c, diff, noise)
+
+
+def test_cluster_size_is_chosen_from_the_client_count(monkeypatch):
+    """Few clients: clusters of 8; more clients than the GPU has room for clusters of 8: one CTA per client."""
+    monkeypatch.delenv("ATTACKFL_TC_CLUSTER", raising=False)
+    _, lay = _setup(6)
+    ds = synthetic_icu(400, 19)
+    for C, want in ((2, 8), (32, 1), (160, 1)):
+        n_data = [128] * C
+        idx = make_round_indices(400, n_data, 1, torch.Generator().manual_seed(3))
+        rows = torch.stack([lay.flatten(models.build(NAME).state_dict())] * C)
+        _tc(lay, rows, ds, idx, n_data, 128, 1, False, lr=0.004)
+        assert TC.last_cluster("cuda") == want
