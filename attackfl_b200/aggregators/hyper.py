@@ -37,6 +37,7 @@ def _adam_inplace(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Te
 
 
 def hyper_grads_torch(h: FusedHyperNet, client: int, theta_client: torch.Tensor) -> Dict[str, torch.Tensor]:
+    h._need_full("hyper_grads_torch")
     idx = torch.tensor([client], device=h.device)
     f, acts = h.features(idx)                    # f [1,H]
     f = f[0]

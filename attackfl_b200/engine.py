@@ -1031,10 +1031,11 @@ class Federation:
                     self.native_hyper.pack()
         else:
             self.failures_in_a_row = 0
+            head_full = None
             if self._hyper_sharded() and self.fused_comm.any_rank_saves:
-                self.fused_comm.hyper_sync_full()                # every rank joins; rank 0 then writes the .pth
+                head_full = self.fused_comm.hyper_gather_full()  # every rank joins; rank 0 then writes the .pth
             if self.save and self.ctx.rank == 0:
-                self.save_checkpoint()
+                self.save_checkpoint(head_full)
             self.remaining -= 1
         timings = self.timer.collect()
         timings["wall"] = (time.perf_counter() - t_wall) * 1e3
@@ -1060,13 +1061,15 @@ class Federation:
         return out
 
     # ================================================================================== checkpoint
-    def save_checkpoint(self) -> None:
+    def save_checkpoint(self, head_full: Optional[Dict[str, torch.Tensor]] = None) -> None:
+        """Writes ``<model>.pth`` / ``<model>_hyper_<C>.pth``.  With a row-sharded hyper-network ``head_full`` is the
+        gathered head (``FusedComm.hyper_gather_full``, a collective the caller runs on every rank first)."""
         import json
         if self.mode == "hyper":
             if self.native_hyper is not None:
                 self.native_hyper.unpack()
             path = os.path.join(self.workdir, f"{self.model_name}_hyper_{self.C}.pth")
-            torch.save(self.hyper.export_state_dict(), path + ".tmp")
+            torch.save(self.hyper.export_state_dict(head_full=head_full), path + ".tmp")
             os.replace(path + ".tmp", path)
         else:
             self.layout.save_pth(self.global_row, os.path.join(self.workdir, f"{self.model_name}.pth"))
@@ -1078,11 +1081,12 @@ class Federation:
     def state_dict(self) -> Dict[str, torch.Tensor]:
         """Current global model (or, in hyper mode, the hyper-network) with the reference's keys."""
         if self.mode == "hyper":
-            if self._hyper_sharded():
-                self.fused_comm.hyper_sync_full()
+            head_full = None
+            if self._hyper_sharded():                            # a collective: call on every rank
+                head_full = self.fused_comm.hyper_gather_full(all_ranks=True)
             if self.native_hyper is not None:
                 self.native_hyper.unpack()
-            return self.hyper.export_state_dict()
+            return self.hyper.export_state_dict(head_full=head_full)
         return self.layout.unflatten(self.global_row, device="cpu")
 
     def close(self) -> None:

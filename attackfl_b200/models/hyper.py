@@ -117,6 +117,7 @@ class FusedHyperNet:
         self.head_b = z(layout.padded)
         self.target = z(layout.padded)
         self.step = 0
+        self.row_lo, self.row_hi = 0, layout.padded         # rows of the head held by this object (all of them by default)
         self._init_adam()
 
     # -- parameters in torch's ``hnet.parameters()`` order minus the grad-less ``target_model.*``
@@ -134,6 +135,27 @@ class FusedHyperNet:
         self.m = OrderedDict((k, torch.zeros_like(v)) for k, v in self.trainable().items())
         self.v = OrderedDict((k, torch.zeros_like(v)) for k, v in self.trainable().items())
         self.step = 0
+
+    # ------------------------------------------------------------------ row sharding (multi-GPU, SURVEY 2.11 ZeRO row)
+    @property
+    def sharded(self) -> bool:
+        return self.row_lo != 0 or self.row_hi != self.layout.padded
+
+    def shard_rows(self, lo: int, hi: int) -> None:
+        """Keep only rows ``[lo, hi)`` of ``W_h`` / ``b_h`` and of their Adam moments; the rest of the storage is
+        released.  From then on this object holds ``1 / world`` of the head (the MLP / embedding stay replicated) and the
+        full head only exists transiently when a checkpoint gathers it (``export_state_dict(head_full=...)``)."""
+        assert not self.sharded and 0 <= lo < hi <= self.layout.padded
+        for name in ("head_w", "head_b"):
+            setattr(self, name, getattr(self, name)[lo:hi].clone())
+            self.m[name] = self.m[name][lo:hi].clone()
+            self.v[name] = self.v[name][lo:hi].clone()
+        self.row_lo, self.row_hi = int(lo), int(hi)
+
+    def _need_full(self, what: str) -> None:
+        if self.sharded:
+            raise RuntimeError(f"{what} needs the whole hyper-network head, but this rank holds rows "
+                               f"[{self.row_lo}, {self.row_hi}) only")
 
     # ------------------------------------------------------------------ conversion
     @classmethod
@@ -156,14 +178,25 @@ class FusedHyperNet:
         self.target.zero_()
         for e in self.layout.entries:
             safe = e.name.replace(".", "__")
-            self.head_w[e.offset:e.offset + e.numel].copy_(sd[f"hyper_layers.{safe}.weight"].to(dev))
-            self.head_b[e.offset:e.offset + e.numel].copy_(sd[f"hyper_layers.{safe}.bias"].to(dev))
+            a, b = max(e.offset, self.row_lo), min(e.offset + e.numel, self.row_hi)    # part of the entry held here
+            if a < b:
+                self.head_w[a - self.row_lo:b - self.row_lo].copy_(
+                    sd[f"hyper_layers.{safe}.weight"][a - e.offset:b - e.offset].to(dev))
+                self.head_b[a - self.row_lo:b - self.row_lo].copy_(
+                    sd[f"hyper_layers.{safe}.bias"][a - e.offset:b - e.offset].to(dev))
             tk = f"target_model.{e.name}"
             if tk in sd:
                 self.target[e.offset:e.offset + e.numel].copy_(sd[tk].reshape(-1).to(dev))
 
-    def export_state_dict(self, device="cpu") -> "OrderedDict[str, torch.Tensor]":
-        """Same keys and order as ``HyperNetwork(...).state_dict()`` of the reference."""
+    def export_state_dict(self, device="cpu", head_full: Optional[Mapping[str, torch.Tensor]] = None
+                          ) -> "OrderedDict[str, torch.Tensor]":
+        """Same keys and order as ``HyperNetwork(...).state_dict()`` of the reference.  A row-sharded object needs
+        ``head_full = {"head_w": [D_pad, H], "head_b": [D_pad]}`` (the shards gathered by the caller)."""
+        if head_full is None:
+            self._need_full("export_state_dict")
+            head_w, head_b = self.head_w, self.head_b
+        else:
+            head_w, head_b = head_full["head_w"], head_full["head_b"]
         out = OrderedDict()
         for e in self.layout.entries:
             out[f"target_model.{e.name}"] = self.target[e.offset:e.offset + e.numel].view(e.shape).to(device).clone()
@@ -173,8 +206,8 @@ class FusedHyperNet:
             out[f"mlp.{2 * i}.bias"] = self.mlp_b[i].to(device).clone()
         for e in self.layout.entries:
             safe = e.name.replace(".", "__")
-            out[f"hyper_layers.{safe}.weight"] = self.head_w[e.offset:e.offset + e.numel].to(device).clone()
-            out[f"hyper_layers.{safe}.bias"] = self.head_b[e.offset:e.offset + e.numel].to(device).clone()
+            out[f"hyper_layers.{safe}.weight"] = head_w[e.offset:e.offset + e.numel].to(device).clone()
+            out[f"hyper_layers.{safe}.bias"] = head_b[e.offset:e.offset + e.numel].to(device).clone()
         return out
 
     def to_module(self, target_model: nn.Module) -> HyperNetwork:
@@ -219,5 +252,6 @@ class FusedHyperNet:
 
     def emit_torch(self, idx: torch.Tensor) -> torch.Tensor:
         """``theta[n, D_pad] = f @ W_h^T + b_h`` (padding rows of W_h/b_h are zero)."""
+        self._need_full("emit_torch")
         f, _ = self.features(idx)
         return f @ self.head_w.t() + self.head_b

@@ -271,15 +271,19 @@ class NativeHyper:
         self.n_nodes, self.E, self.H = fused.n_nodes, fused.E, fused.H
         self.tot = self.n_nodes * self.E + self.H * self.E + self.H + 2 * (self.H * self.H + self.H)
         self.small = torch.zeros(3 * self.tot, dtype=torch.float32, device=dev)
-        self.head_w, self.head_b = fused.head_w, fused.head_b
-        self.mw, self.vw = fused.m["head_w"], fused.v["head_w"]
-        self.mb, self.vb = fused.m["head_b"], fused.v["head_b"]
+        self._bind_head()
         self.delta = torch.zeros(fused.layout.padded, dtype=torch.float32, device=dev)
         self.acts = torch.zeros(self.E + 5 * self.H, dtype=torch.float32, device=dev)
         self.red = torch.zeros(self.H + 3, dtype=torch.float32, device=dev)
         self.f1 = torch.zeros(self.H, dtype=torch.float32, device=dev)
         self._client_idx = torch.arange(self.n_nodes, dtype=torch.int32, device=dev)
         self.pack()
+
+    def _bind_head(self) -> None:
+        fused = self.fused
+        self.head_w, self.head_b = fused.head_w, fused.head_b
+        self.mw, self.vw = fused.m["head_w"], fused.v["head_w"]
+        self.mb, self.vb = fused.m["head_b"], fused.v["head_b"]
 
     def _names(self) -> List[str]:
         return ["emb", "mlp_w0", "mlp_b0", "mlp_w1", "mlp_b1", "mlp_w2", "mlp_b2"]
@@ -304,6 +308,7 @@ class NativeHyper:
 
     def emit(self, clients: Sequence[int], out: Optional[torch.Tensor] = None, chunk: int = 64) -> torch.Tensor:
         """K5a: rows ``theta[j] = h(clients[j])``; ``out [n, D_pad]`` may be a slice of the client arena."""
+        self.fused._need_full("NativeHyper.emit")
         dev = self.small.device
         lib = lib_for(self.small)
         d_pad = self.fused.layout.padded
@@ -333,6 +338,7 @@ class NativeHyper:
 
     def step(self, client: int, theta_client: torch.Tensor, lr: float, clip: float) -> None:
         """K5b: one sequential pFedHN step (no host sync; the clip coefficient stays on the device)."""
+        self.fused._need_full("NativeHyper.step")
         lib = lib_for(self.small)
         self.fused.step += 1
         rc = lib.afl_hyper_step(ptr(self.head_w), ptr(self.head_b), ptr(self.mw), ptr(self.vw), ptr(self.mb),
@@ -348,11 +354,17 @@ class NativeHyper:
 
     # ------------------------------------------------------------------ persistent / row-sharded round (csrc/hyper_round.cu)
     def setup_round(self, lo: int = 0, hi: Optional[int] = None, world: int = 1, rank: int = 0, n_max: int = 0,
-                    xchg_ptrs=None, sig_ptrs=None) -> None:
+                    xchg_ptrs=None, sig_ptrs=None, shard_storage: bool = False) -> None:
         """Row shard ``[lo, hi)`` of the head owned by this rank (``world`` ranks) and the symmetric exchange / flag
-        buffers (host arrays of peer-mapped pointers) for up to ``n_max`` clients per round."""
+        buffers (host arrays of peer-mapped pointers) for up to ``n_max`` clients per round.  ``shard_storage``: also
+        release the rows this rank does not own (``FusedHyperNet.shard_rows``): W_h, b_h and both Adam moments then take
+        ``1 / world`` of their size on every GPU."""
         dev = self.small.device
         hi = self.fused.layout.padded if hi is None else hi
+        if shard_storage and not self.fused.sharded and (lo, hi) != (0, self.fused.layout.padded):
+            self.fused.shard_rows(int(lo), int(hi))
+            self._bind_head()
+            self.delta = None                      # full-length scratch of the one-GPU step: not used any more
         self.lo, self.hi, self.world, self.rank = int(lo), int(hi), int(world), int(rank)
         self.n_max = int(n_max) if n_max else self.n_nodes
         self.xchg_ptrs, self.sig_ptrs = xchg_ptrs, sig_ptrs
@@ -365,6 +377,9 @@ class NativeHyper:
         self.round_epoch = 0
 
     def _shards(self):
+        if self.fused.sharded:                     # the tensors ARE the shard
+            assert (self.fused.row_lo, self.fused.row_hi) == (self.lo, self.hi)
+            return (self.head_w, self.head_b, self.mw, self.vw, self.mb, self.vb)
         lo, hi = self.lo, self.hi
         return (self.head_w[lo:hi], self.head_b[lo:hi], self.mw[lo:hi], self.vw[lo:hi], self.mb[lo:hi], self.vb[lo:hi])
 
@@ -398,7 +413,7 @@ class NativeHyper:
             self.setup_round()
         lib = lib_for(self.small)
         dev = self.small.device
-        hw, hb = self.head_w[self.lo:self.hi], self.head_b[self.lo:self.hi]
+        hw, hb = self._shards()[:2]
         cl = torch.as_tensor(list(clients), dtype=torch.int32, device=dev)
         tp = torch.as_tensor([int(p) for p in theta_ptrs], dtype=torch.int64, device=dev)
         for c0 in range(0, len(clients), chunk):

@@ -12,7 +12,7 @@ handles), builds the pointer tables and installs ``fed.fused_comm``.
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
+from typing import Dict, List, Optional
 
 import torch
 import torch.distributed as dist
@@ -84,7 +84,8 @@ class FusedComm:
             dist.barrier()
             sl = D // self.world
             nh.setup_round(self.rank * sl, (self.rank + 1) * sl, self.world, self.rank, n_max,
-                           PtrArr(*[int(p) for p in self.h_hx.buffer_ptrs]), PtrArr(*[int(p) for p in self.h_hs.buffer_ptrs]))
+                           PtrArr(*[int(p) for p in self.h_hx.buffer_ptrs]), PtrArr(*[int(p) for p in self.h_hs.buffer_ptrs]),
+                           shard_storage=True)
             self.hyper_sharded = True
             flag = torch.tensor([1.0 if fed.save else 0.0], device=dev)
             dist.all_reduce(flag, op=dist.ReduceOp.MAX)
@@ -94,13 +95,22 @@ class FusedComm:
         """Device address of a client's row on this rank's view of its owner's arena (peer-mapped)."""
         return int(self.h_rows.buffer_ptrs[client // self.cpg]) + (client % self.cpg) * self.fed.D * 4
 
-    def hyper_sync_full(self) -> None:
-        """Checkpoint / export only: gathers every rank's row shard of the head and its Adam moments into the full
-        tensors (NCCL; off the round path)."""
+    def hyper_gather_full(self, all_ranks: bool = False) -> Optional[Dict[str, torch.Tensor]]:
+        """Checkpoint / export only (a collective, off the round path): the row shards of ``W_h`` / ``b_h`` gathered
+        into full host tensors on rank 0 (on every rank with ``all_ranks``); the Adam moments stay sharded."""
         nh = self.fed.native_hyper
-        for t in (nh.head_w, nh.head_b, nh.mw, nh.vw, nh.mb, nh.vb):
-            parts = t.view(self.world, -1)
-            dist.all_gather_into_tensor(parts, parts[self.rank].clone())
+        out: Dict[str, torch.Tensor] = {}
+        for name, t in (("head_w", nh.head_w), ("head_b", nh.head_b)):
+            if all_ranks:
+                full = torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+                dist.all_gather_into_tensor(full, t.contiguous())
+                out[name] = full.cpu()
+            else:
+                parts = [torch.empty_like(t) for _ in range(self.world)] if self.rank == 0 else None
+                dist.gather(t.contiguous(), parts, dst=0)
+                if self.rank == 0:
+                    out[name] = torch.cat([p.cpu() for p in parts])
+        return out if (all_ranks or self.rank == 0) else None
 
     def fedavg(self, weights: torch.Tensor, member: Optional[torch.Tensor] = None, z: Optional[torch.Tensor] = None,
                ref: Optional[torch.Tensor] = None, strict_k1: bool = False) -> Optional[torch.Tensor]:

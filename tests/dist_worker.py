@@ -46,12 +46,19 @@ def main():
                     return _inner(*a, **k)
                 setattr(comm, name, delayed)
     res = fed.run()
+    head_rows = None
     if mode == "hyper":
-        fed.state_dict()                      # gathers the row shards of a sharded head (no-op otherwise)
-    glob = fed.global_row if mode != "hyper" else fed.hyper.head_b
+        sd = fed.state_dict()                 # a collective: gathers the row shards of a sharded head
+        # the head bias in arena order, rebuilt from the exported per-tensor entries (full length on every rank)
+        glob = torch.zeros(fed.layout.padded)
+        for e in fed.layout.entries:
+            glob[e.offset:e.offset + e.numel] = sd["hyper_layers." + e.name.replace(".", "__") + ".bias"].float().cpu()
+        head_rows = int(fed.hyper.head_w.shape[0])        # rows of W_h this rank actually stores
+    else:
+        glob = fed.global_row
     rec = {"rank": ctx.rank, "world": ctx.world, "ok": [r.ok for r in res], "metric": [r.metric for r in res],
            "attackers": [r.attackers for r in res], "checksum": float(glob.double().sum()),
-           "absmax": float(glob.abs().max()), "local": fed.local, "fused": fed.fused_comm is not None}
+           "absmax": float(glob.abs().max()), "local": fed.local, "fused": fed.fused_comm is not None, "head_rows": head_rows, "d_pad": int(fed.layout.padded)}
     with open(f"{out}.rank{ctx.rank}.json", "w") as fh:
         json.dump(rec, fh)
     torch.save(glob.detach().float().cpu(), f"{out}.rank{ctx.rank}.pt")           # full vector: compared element-wise

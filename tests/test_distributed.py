@@ -107,6 +107,10 @@ def test_gpus_sharded_hyper_matches_gathered_path(tmp_path, world):
         a = recs[0]
         assert a["ok"] == [True] * 3
         out[collectives] = a
+        if collectives == "fused":       # W_h / b_h / both moments are stored as 1 / world row shards on every rank
+            assert all(r["head_rows"] == r["d_pad"] // world for r in recs), [(r["head_rows"], r["d_pad"]) for r in recs]
+        else:
+            assert all(r["head_rows"] == r["d_pad"] for r in recs)
     # Adam normalises gradients: a coordinate whose gradient is rounding noise can move by +-lr per step in either run, so
     # require that almost all coordinates agree tightly and that none is off by more than a few steps of hyper-lr = 1e-3
     d = (out["fused"]["vector"] - out["nccl"]["vector"]).abs()

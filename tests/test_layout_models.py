@@ -102,3 +102,42 @@ def test_cnnhyper_keys(ref):
     wa, _ = a(torch.tensor([1]))
     wb, _ = b(torch.tensor([1]))
     assert all(torch.allclose(wa[k], wb[k]) for k in wb)
+
+
+def test_fused_hypernet_row_shards_round_trip():
+    """Row-sharded storage (ZeRO row): two objects holding half of the head each export, once their shards
+    are gathered, exactly what the full object exports; import is shard-aware; whole-head operations refuse."""
+    torch.manual_seed(1)
+    h = models.HyperNetwork(models.TransformerModel(), 3, 8, 100, False, 2)
+    full = FusedHyperNet.from_module(h)
+    D = full.layout.padded
+    shards = []
+    for r in range(2):
+        f = FusedHyperNet.from_module(h)
+        f.m["head_w"].fill_(float(r + 1))
+        f.shard_rows(r * D // 2, (r + 1) * D // 2)
+        assert f.sharded and f.head_w.shape == (D // 2, 100) and f.m["head_w"].shape == (D // 2, 100)
+        assert f.v["head_b"].shape == (D // 2,) and float(f.m["head_w"][0, 0]) == r + 1
+        assert torch.equal(f.head_w, full.head_w[r * D // 2:(r + 1) * D // 2])
+        shards.append(f)
+    with pytest.raises(RuntimeError, match="whole hyper-network head"):
+        shards[0].emit_torch(torch.tensor([0]))
+    with pytest.raises(RuntimeError, match="whole hyper-network head"):
+        shards[0].export_state_dict()
+    gathered = {"head_w": torch.cat([s.head_w for s in shards]), "head_b": torch.cat([s.head_b for s in shards])}
+    want = full.export_state_dict()
+    for s in shards:
+        got = s.export_state_dict(head_full=gathered)
+        assert list(got) == list(want) and all(torch.equal(got[k], want[k]) for k in want)
+    # snapshot / restore stay shard-local; import writes only the rows held here
+    snap = shards[1].snapshot()
+    shards[1].head_w.add_(1.0)
+    shards[1].restore(snap)
+    assert torch.equal(shards[1].head_w, full.head_w[D // 2:])
+    torch.manual_seed(2)
+    other = models.HyperNetwork(models.TransformerModel(), 3, 8, 100, False, 2).state_dict()
+    ref2 = FusedHyperNet.from_module(h)
+    ref2.import_state_dict(other)
+    shards[1].import_state_dict(other)
+    assert torch.equal(shards[1].head_w, ref2.head_w[D // 2:]) and torch.equal(shards[1].head_b, ref2.head_b[D // 2:])
+    assert torch.equal(shards[1].emb, ref2.emb)
