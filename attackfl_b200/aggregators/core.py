@@ -142,20 +142,24 @@ def scionfl(rows: torch.Tensor, sizes: Sequence[float], valid: Optional[torch.Te
     ``keep='similar'`` keeps the closest half.  ``scores``: cosine distances already computed by the
     bit-packed native pass (``ops.flat.scion_cosine_distances``); otherwise the plain torch restatement below.
     """
-    n = rows.shape[0]
     if scores is None:
         scores = scion_scores_torch(rows, valid, generator, mu_threshold)
+    kept = scionfl_keep(scores, keep, topk_ratio)
+    sz = torch.as_tensor([sizes[i] for i in kept], dtype=torch.float32, device=rows.device)
+    out = (rows[kept] * sz[:, None]).sum(0) / sz.sum()
+    return out, kept
+
+
+def scionfl_keep(scores: Sequence[float], keep: str = "reference", topk_ratio: float = 0.5) -> List[int]:
+    """The keep rule of server.py:467-480 on the cosine distances (see ``scionfl``)."""
     scores = [float(x) for x in scores]
+    n = len(scores)
     thr = sorted(scores, reverse=True)[int(topk_ratio * n)]
     if keep == "reference":
         kept = [i for i, s in enumerate(scores) if s > thr]
     else:
         kept = [i for i, s in enumerate(scores) if s <= thr]
-    if not kept:
-        kept = list(range(n))
-    sz = torch.as_tensor([sizes[i] for i in kept], dtype=torch.float32, device=rows.device)
-    out = (rows[kept] * sz[:, None]).sum(0) / sz.sum()
-    return out, kept
+    return kept or list(range(n))
 
 
 def scion_dequant_scores(sigma: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor) -> torch.Tensor:

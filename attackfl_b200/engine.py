@@ -687,7 +687,7 @@ class Federation:
         self.have_global = True
         self._rows_hold_global = True
 
-    SLICED_MODES = ("median", "trimmed_mean", "krum", "shieldfl", "FLTrust")
+    SLICED_MODES = ("median", "trimmed_mean", "krum", "shieldfl", "FLTrust", "scionfl")
 
     def _aggregate_sliced(self, reporting: List[int], info: Dict[str, object]) -> None:
         """Defences on N GPUs without gathering a row: rank r owns coordinate slice r.  Median / trimmed mean read the C
@@ -724,6 +724,14 @@ class Federation:
             i = agg.krum_select(torch.zeros(n, 1, device=self.device), kf, lambda _r: G, reference_slice=s.krum_reference_f)
             info["krum_winner"] = reporting[i]
             w[reporting[i]] = 1.0
+        elif self.mode == "scionfl":
+            # only the 1-bit codes cross NVLink (server.py:436-492); the kept clients are averaged by K1-fused
+            cosd = fc.scion_distances(reporting, int(s.random_seed or 0) * 7919 + self.attempt)
+            kept = agg.scionfl_keep(cosd.tolist(), s.scionfl_keep)
+            info["scionfl_kept"] = [reporting[i] for i in kept]
+            tot = float(sum(self.sizes[reporting[i]] for i in kept))
+            for i in kept:
+                w[reporting[i]] = float(self.sizes[reporting[i]]) / tot
         elif self.mode == "shieldfl":
             G = flat.sliced_gram(ptrs, zero, lo, hi, prec, fc.allreduce_small)      # cosines of the raw vectors: no centring
             a = agg.shieldfl_weights(torch.zeros(n, 1, device=self.device), lambda _r: G).cpu()

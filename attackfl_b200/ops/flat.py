@@ -114,21 +114,62 @@ def coord_select(rows: torch.Tensor, mode: str, trim: int = 0, out: Optional[tor
     return out
 
 
-def scion_quantize(rows: torch.Tensor, valid: Optional[torch.Tensor], seed: int):
+def scion_quantize(rows: torch.Tensor, valid: Optional[torch.Tensor], seed: int, row0: int = 0,
+                   bits: Optional[torch.Tensor] = None):
     """ScionFL 1-bit stochastic quantisation of every row (``src/Utils.py:372-376``), packed 32 coordinates per word.
 
-    Returns ``(bits [C, d_pad/32] int32, counts [C] int32, minmax [C, 2])``; ``valid`` is the layout's 0/1 float mask."""
+    Returns ``(bits [C, d_pad/32] int32, counts [C] int32, minmax [C, 2])``; ``valid`` is the layout's 0/1 float mask.
+    ``row0``: Philox stream id of row 0 (N GPUs: the position of this rank's first row in the round's reporting list, so
+    that the bits equal those of the one-GPU pass over all rows); ``bits``: optional output buffer (symmetric memory)."""
     C, d_pad = rows.shape
     lib = lib_for(rows)
     dev = rows.device
     minmax = torch.empty(C, 2, dtype=torch.float32, device=dev)
-    bits = torch.empty(C, d_pad // 32, dtype=torch.int32, device=dev)
+    bits = torch.empty(C, d_pad // 32, dtype=torch.int32, device=dev) if bits is None else bits
+    assert bits.shape[0] >= C and bits.shape[1] == d_pad // 32 and bits.is_contiguous()
     counts = torch.empty(C, dtype=torch.int32, device=dev)
     check(lib, lib.afl_scion_minmax(ptr(rows), ptr(valid), c_i(C), c_i64(d_pad), ptr(minmax), stream_ptr(rows)),
           "afl_scion_minmax")
-    check(lib, lib.afl_scion_quantize(ptr(rows), ptr(valid), ptr(minmax), c_i(C), c_i64(d_pad), c_u64(seed), ptr(bits),
-                                      ptr(counts), stream_ptr(rows)), "afl_scion_quantize")
-    return bits, counts, minmax
+    check(lib, lib.afl_scion_quantize_rows(ptr(rows), ptr(valid), ptr(minmax), c_i(C), c_i64(d_pad), c_u64(seed),
+                                           c_i(int(row0)), ptr(bits), ptr(counts), stream_ptr(rows)), "afl_scion_quantize")
+    return bits[:C], counts, minmax
+
+
+def scion_scores_ptrs(bits_ptrs: Sequence[int], words: int, w_lo: int, w_hi: int, valid: Optional[torch.Tensor],
+                      lohi: torch.Tensor) -> torch.Tensor:
+    """``scion_scores`` restricted to the words ``[w_lo, w_hi)`` with every client's packed row given by address
+    (peer-mapped addresses allowed): the partial sums of a slice owner."""
+    C = len(bits_ptrs)
+    dev = lohi.device
+    lib = lib_for(lohi)
+    out = torch.empty(C + 2, dtype=torch.float32, device=dev)
+    lohi = lohi.to(torch.float32).contiguous()
+    bp = torch.as_tensor([int(p) for p in bits_ptrs], dtype=torch.int64, device=dev)
+    check(lib, lib.afl_scion_scores_ptrs(ptr(bp), ptr(valid), ptr(lohi), c_i(C), c_i64(words * 32), c_i64(w_lo), c_i64(w_hi),
+                                         ptr(out), stream_ptr(lohi)), "afl_scion_scores_ptrs")
+    return out
+
+
+def scion_distances_from_sums(sums: torch.Tensor, counts: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor, d: float):
+    """Cosine distances from ``sums = [S_0..S_{C-1}, sum agg, sum agg^2]`` and the (clipped) levels (server.py:455-466)."""
+    C = counts.numel()
+    out = sums.to(torch.float64)
+    s, a_sum, a_sq = out[:C], out[C], out[C + 1]
+    c1 = counts.to(torch.float64)
+    dots = lo * a_sum + (hi - lo) * s
+    n_deq = torch.sqrt((d - c1) * lo * lo + c1 * hi * hi)
+    cos = dots / (n_deq.clamp_min(1e-8) * torch.sqrt(a_sq).clamp_min(1e-8))
+    return (1.0 - cos).to(torch.float32)
+
+
+def scion_clipped_levels(counts: torch.Tensor, minmax: torch.Tensor, d: float, mu_threshold: float = 3.0):
+    """L2 norms from the bit counts and the levels after the ``mu_threshold`` x mean clip (server.py:443-454)."""
+    c1 = counts.to(torch.float64)
+    lo, hi = minmax[:, 0].to(torch.float64), minmax[:, 1].to(torch.float64)
+    l2 = torch.sqrt((d - c1) * lo * lo + c1 * hi * hi)
+    cap = mu_threshold * l2.mean()
+    fct = torch.where(l2 > cap, cap / l2, torch.ones_like(l2))
+    return lo * fct, hi * fct
 
 
 def scion_scores(bits: torch.Tensor, valid: Optional[torch.Tensor], lohi: torch.Tensor) -> torch.Tensor:
@@ -149,18 +190,10 @@ def scion_cosine_distances(rows: torch.Tensor, valid: Optional[torch.Tensor], se
     C, d_pad = rows.shape
     bits, counts, minmax = scion_quantize(rows, valid, seed)
     d = float(valid.sum().item()) if valid is not None else float(d_pad)
-    c1 = counts.to(torch.float64)
-    lo, hi = minmax[:, 0].to(torch.float64), minmax[:, 1].to(torch.float64)
-    l2 = torch.sqrt((d - c1) * lo * lo + c1 * hi * hi)
-    cap = mu_threshold * l2.mean()
-    fct = torch.where(l2 > cap, cap / l2, torch.ones_like(l2))
-    lo, hi = lo * fct, hi * fct
-    out = scion_scores(bits, valid, torch.stack([lo, hi], dim=1)).to(torch.float64)
-    s, a_sum, a_sq = out[:C], out[C], out[C + 1]
-    dots = lo * a_sum + (hi - lo) * s
-    n_deq = torch.sqrt((d - c1) * lo * lo + c1 * hi * hi)
-    cos = dots / (n_deq.clamp_min(1e-8) * torch.sqrt(a_sq).clamp_min(1e-8))
-    return (1.0 - cos).to(torch.float32), {"bits": bits, "counts": counts, "minmax": minmax, "lohi": torch.stack([lo, hi], 1)}
+    lo, hi = scion_clipped_levels(counts, minmax, d, mu_threshold)
+    out = scion_scores(bits, valid, torch.stack([lo, hi], dim=1))
+    cosd = scion_distances_from_sums(out, counts, lo, hi, d)
+    return cosd, {"bits": bits, "counts": counts, "minmax": minmax, "lohi": torch.stack([lo, hi], 1)}
 
 
 def coord_select_ptrs(row_ptrs: Sequence[int], lo: int, hi: int, dst_ptrs: Sequence[int], mode: str, trim: int,

@@ -232,6 +232,50 @@ class FusedComm:
         check(lib, rc, "afl_fedavg_fused (small all-reduce)")
         return self.g_glob[:n].view(t.shape).clone()
 
+    def scion_distances(self, reporting: List[int], seed: int, mu_threshold: float = 3.0) -> torch.Tensor:
+        """ScionFL scoring on N GPUs (server.py:443-466) without moving a row: every rank quantises its own reporting
+        rows to 1-bit codes in a symmetric buffer, the per-client scalars (min, max, bit count) are summed into place by
+        the small fused all-reduce, every rank scores its slice of the packed words reading all clients' codes where
+        their owner wrote them (peer pointers), and the C + 2 partial sums are all-reduced.  Returns the cosine distances
+        ``[len(reporting)]`` (replicated).  Only D / 32 words per client ever cross NVLink."""
+        import torch.distributed._symmetric_memory as symm_mem
+        from ..ops import flat
+        fed = self.fed
+        dev = fed.device
+        D, words = fed.D, fed.D // 32
+        if getattr(self, "sc_bits", None) is None:
+            self.sc_bits = symm_mem.empty(self.cpg, words, dtype=torch.int32, device=dev)
+            self.sc_bits.zero_()
+            self.h_sc = symm_mem.rendezvous(self.sc_bits, dist.group.WORLD)
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+        n = len(reporting)
+        pos = {c: j for j, c in enumerate(reporting)}
+        mine = [c for c in fed.local if c in pos]                 # ascending ids -> consecutive positions
+        scal = torch.zeros(n, 3, dtype=torch.float32, device=dev)
+        if mine:
+            assert [pos[c] for c in mine] == list(range(pos[mine[0]], pos[mine[0]] + len(mine)))
+            loc = [c - fed.local[0] for c in mine]
+            rows = fed.rows[loc[0]:loc[-1] + 1] if loc == list(range(loc[0], loc[-1] + 1)) else fed.rows[loc]
+            _, counts, minmax = flat.scion_quantize(rows.contiguous(), fed.valid, seed, row0=pos[mine[0]], bits=self.sc_bits)
+            scal[pos[mine[0]]:pos[mine[0]] + len(mine), :2] = minmax
+            scal[pos[mine[0]]:pos[mine[0]] + len(mine), 2] = counts.to(torch.float32)
+        scal = self.allreduce_small(scal)       # also orders every rank's codes before any peer reads them (flag barrier)
+        counts, minmax = scal[:, 2].round().to(torch.int32), scal[:, :2]
+        d = float(fed.valid.sum().item())
+        lo, hi = flat.scion_clipped_levels(counts, minmax, d, mu_threshold)
+        slot = {c: k for k, c in enumerate(mine)}
+        ptrs = []
+        for c in reporting:                                        # slot of a client inside its owner's code buffer
+            owner = c // self.cpg
+            first = next(j for j, cc in enumerate(reporting) if cc // self.cpg == owner)
+            ptrs.append(int(self.h_sc.buffer_ptrs[owner]) + (pos[c] - first) * words * 4)
+        wl = words // self.world
+        part = flat.scion_scores_ptrs(ptrs, words, self.rank * wl, (self.rank + 1) * wl if self.rank < self.world - 1 else words,
+                                      fed.valid, torch.stack([lo, hi], 1).to(dev))
+        sums = self.allreduce_small(part)
+        return flat.scion_distances_from_sums(sums, counts, lo, hi, d)
+
     def check_error(self, raise_on_error: bool = True) -> int:
         """Error word of the fused kernels (non-zero: a cross-GPU flag barrier timed out, the outputs are stale).  The
         word is summed over ranks so that every rank takes the same decision."""

@@ -105,9 +105,9 @@ int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad
   return 0;
 }
 
-int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
-                       uint32_t* bits, int* counts, void*) {
-  CHECK_ARG(C >= 1 && d_pad % 32 == 0, "afl_scion_quantize: C >= 1, d_pad % 32 == 0");
+int afl_scion_quantize_rows(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                            int row0, uint32_t* bits, int* counts, void*) {
+  CHECK_ARG(C >= 1 && d_pad % 32 == 0 && row0 >= 0, "afl_scion_quantize: C >= 1, d_pad % 32 == 0, row0 >= 0");
   const int64_t words = d_pad / 32;
   for (int c = 0; c < C; ++c) {
     const float mn = minmax[2 * c], inv = 1.0f / (minmax[2 * c + 1] - mn + 1e-6f);
@@ -117,7 +117,7 @@ int afl_scion_quantize(const float* rows, const float* valid, const float* minma
       for (int b = 0; b < 32; ++b) {
         const int64_t j = w * 32 + b;
         if ((!valid || valid[j] != 0.f) &&
-            afl_scion_bit(rows[(int64_t)c * d_pad + j], mn, inv, (uint32_t)seed, (uint32_t)(seed >> 32), (uint32_t)c, (uint32_t)j)) {
+            afl_scion_bit(rows[(int64_t)c * d_pad + j], mn, inv, (uint32_t)seed, (uint32_t)(seed >> 32), (uint32_t)(row0 + c), (uint32_t)j)) {
           word |= 1u << b; ++cnt;
         }
       }
@@ -128,19 +128,36 @@ int afl_scion_quantize(const float* rows, const float* valid, const float* minma
   return 0;
 }
 
-int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out, void*) {
-  CHECK_ARG(C >= 1 && C <= 4096 && d_pad % 32 == 0, "afl_scion_scores: 1 <= C <= 4096, d_pad % 32 == 0");
-  const int64_t words = d_pad / 32;
+int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                       uint32_t* bits, int* counts, void* stream) {
+  return afl_scion_quantize_rows(rows, valid, minmax, C, d_pad, seed, 0, bits, counts, stream);
+}
+
+int afl_scion_scores_ptrs(const uint32_t* const* bits_ptrs, const float* valid, const float* lohi, int C, int64_t d_pad,
+                          int64_t w_lo, int64_t w_hi, float* out, void*) {
+  CHECK_ARG(C >= 1 && C <= 4096 && d_pad % 32 == 0 && 0 <= w_lo && w_lo <= w_hi && w_hi <= d_pad / 32,
+            "afl_scion_scores_ptrs: 1 <= C <= 4096, d_pad % 32 == 0, 0 <= w_lo <= w_hi <= d_pad / 32");
   std::vector<double> acc((size_t)C + 2, 0.0);
-  for (int64_t w = 0; w < words; ++w)
+  for (int64_t w = w_lo; w < w_hi; ++w)
     for (int b = 0; b < 32; ++b) {
       if (valid && valid[w * 32 + b] == 0.f) continue;
-      const float a = afl_scion_agg(bits, lohi, C, words, w, b);
+      float a = 0.f;
+      for (int i = 0; i < C; ++i) a += ((bits_ptrs[i][w] >> b) & 1u) ? lohi[2 * i + 1] : lohi[2 * i];
+      a /= (float)C;
       acc[C] += a; acc[C + 1] += (double)a * a;
-      for (int i = 0; i < C; ++i) if ((bits[(int64_t)i * words + w] >> b) & 1u) acc[i] += a;
+      for (int i = 0; i < C; ++i) if ((bits_ptrs[i][w] >> b) & 1u) acc[i] += a;
     }
   for (int i = 0; i < C + 2; ++i) out[i] = (float)acc[i];
   return 0;
+}
+
+int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out,
+                     void* stream) {
+  CHECK_ARG(C >= 1 && C <= 4096 && d_pad % 32 == 0, "afl_scion_scores: 1 <= C <= 4096, d_pad % 32 == 0");
+  const int64_t words = d_pad / 32;
+  std::vector<const uint32_t*> ptrs((size_t)C);
+  for (int i = 0; i < C; ++i) ptrs[i] = bits + (int64_t)i * words;
+  return afl_scion_scores_ptrs(ptrs.data(), valid, lohi, C, d_pad, 0, words, out, stream);
 }
 
 // ---------------------------------------------------------------------------------------- hyper (host loops)

@@ -95,7 +95,7 @@ __global__ void scion_minmax_finish_kernel(unsigned* ord, int n) {
 __global__ void __launch_bounds__(256) scion_quantize_kernel(const float* __restrict__ rows, const float* __restrict__ valid,
                                                              const float* __restrict__ minmax, int64_t d_pad,
                                                              uint32_t s0, uint32_t s1, uint32_t* __restrict__ bits,
-                                                             int* __restrict__ counts) {
+                                                             int* __restrict__ counts, int row0) {
   const int c = blockIdx.y;
   const float mn = minmax[2 * c], inv = 1.0f / (minmax[2 * c + 1] - mn + 1e-6f);
   const float* row = rows + (int64_t)c * d_pad;
@@ -103,29 +103,42 @@ __global__ void __launch_bounds__(256) scion_quantize_kernel(const float* __rest
   int cnt = 0;
   for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < d_pad; j += (int64_t)gridDim.x * 256) {
     const bool ok = !valid || valid[j] != 0.f;
-    const bool bit = ok && afl_scion_bit(row[j], mn, inv, s0, s1, (uint32_t)c, (uint32_t)j);
+    const bool bit = ok && afl_scion_bit(row[j], mn, inv, s0, s1, (uint32_t)(row0 + c), (uint32_t)j);
     const unsigned w = __ballot_sync(0xffffffffu, bit);
     if ((threadIdx.x & 31) == 0) { bits[(int64_t)c * words + (j >> 5)] = w; cnt += __popc(w); }
   }
   if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(counts + c, cnt);
 }
 
-// one warp per 32-coordinate word; S_c partials live in shared memory until the block is done
+// one warp per 32-coordinate word; S_c partials live in shared memory until the block is done.  `bptr` (optional): the
+// packed rows by address, one per client (peer-mapped addresses allowed: the 1-bit codes are read where their owner
+// wrote them), and only the words [w_lo, w_hi) are visited (slice ownership on N GPUs).
 __global__ void __launch_bounds__(256) scion_scores_kernel(const uint32_t* __restrict__ bits, const float* __restrict__ valid,
                                                            const float* __restrict__ lohi, int C, int64_t d_pad,
-                                                           float* __restrict__ out) {
+                                                           float* __restrict__ out, const uint32_t* const* bptr = nullptr,
+                                                           int64_t w_lo = 0, int64_t w_hi = -1) {
   extern __shared__ float acc[];                     // [C + 2]
   for (int i = threadIdx.x; i < C + 2; i += 256) acc[i] = 0.f;
   __syncthreads();
   const int64_t words = d_pad / 32;
+  if (w_hi < 0) w_hi = words;
   const int lane = threadIdx.x & 31;
   float sa = 0.f, sq = 0.f;
-  for (int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < words; w += (int64_t)gridDim.x * 8) {
+  for (int64_t w = w_lo + (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < w_hi; w += (int64_t)gridDim.x * 8) {
     const bool ok = !valid || valid[w * 32 + lane] != 0.f;
-    const float a = ok ? afl_scion_agg(bits, lohi, C, words, w, lane) : 0.f;
+    float a = 0.f;
+    if (bptr) {
+      if (ok) {
+        for (int i = 0; i < C; ++i) a += ((bptr[i][w] >> lane) & 1u) ? lohi[2 * i + 1] : lohi[2 * i];
+        a /= (float)C;
+      }
+    } else {
+      a = ok ? afl_scion_agg(bits, lohi, C, words, w, lane) : 0.f;
+    }
     sa += a; sq += a * a;
     for (int i = 0; i < C; ++i) {
-      float v = ((bits[(int64_t)i * words + w] >> lane) & 1u) ? a : 0.f;
+      const uint32_t word = bptr ? bptr[i][w] : bits[(int64_t)i * words + w];
+      float v = ((word >> lane) & 1u) ? a : 0.f;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0 && v != 0.f) atomicAdd(acc + i, v);
@@ -563,16 +576,36 @@ int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad
   return afl_rt::check_last("afl_scion_minmax");
 }
 
-int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
-                       uint32_t* bits, int* counts, void* stream) {
-  AFL_CHECK_ARG(C >= 1 && d_pad % 32 == 0, "afl_scion_quantize: C >= 1, d_pad % 32 == 0");
+int afl_scion_quantize_rows(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                            int row0, uint32_t* bits, int* counts, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && d_pad % 32 == 0 && row0 >= 0, "afl_scion_quantize: C >= 1, d_pad % 32 == 0, row0 >= 0");
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)C, st);
   const int gx = (int)std::min<int64_t>((d_pad + 2047) / 2048, 128);
   scion_quantize_kernel<<<dim3(gx, C), 256, 0, st>>>(rows, valid, minmax, d_pad, (uint32_t)seed, (uint32_t)(seed >> 32),
-                                                     bits, counts);
+                                                     bits, counts, row0);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_scion_quantize");
+}
+
+int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                       uint32_t* bits, int* counts, void* stream) {
+  return afl_scion_quantize_rows(rows, valid, minmax, C, d_pad, seed, 0, bits, counts, stream);
+}
+
+int afl_scion_scores_ptrs(const uint32_t* const* bits_ptrs_dev, const float* valid, const float* lohi, int C, int64_t d_pad,
+                          int64_t w_lo, int64_t w_hi, float* out, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && C <= 4096 && d_pad % 32 == 0 && 0 <= w_lo && w_lo <= w_hi && w_hi <= d_pad / 32,
+                "afl_scion_scores_ptrs: 1 <= C <= 4096, d_pad % 32 == 0, 0 <= w_lo <= w_hi <= d_pad / 32");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(out, 0, sizeof(float) * (size_t)(C + 2), st);
+  if (w_hi > w_lo) {
+    const int grid = grid_for(w_hi - w_lo, 8, 4);
+    scion_scores_kernel<<<grid, 256, sizeof(float) * (size_t)(C + 2), st>>>(nullptr, valid, lohi, C, d_pad, out, bits_ptrs_dev,
+                                                                             w_lo, w_hi);
+    afl_rt::count_launch();
+  }
+  return afl_rt::check_last("afl_scion_scores_ptrs");
 }
 
 int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out,

@@ -162,6 +162,13 @@ int afl_har_head(const float* pooled, const float* w1, const float* b1, const fl
 int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void* stream);
 int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
                        uint32_t* bits, int* counts, void* stream);
+/* N-GPU forms (CUDA build): _quantize_rows keys the Philox stream of local row c by row0 + c (its position in the round's
+ * reporting list), so every rank draws the bits the one-GPU pass would; _scores_ptrs takes the packed rows by address
+ * (bits_ptrs_dev [C], peer-mapped allowed) and visits the words [w_lo, w_hi) only: partial sums of an owned slice. */
+int afl_scion_quantize_rows(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
+                            int row0, uint32_t* bits, int* counts, void* stream);
+int afl_scion_scores_ptrs(const uint32_t* const* bits_ptrs_dev, const float* valid, const float* lohi, int C, int64_t d_pad,
+                          int64_t w_lo, int64_t w_hi, float* out, void* stream);
 int afl_scion_scores(const uint32_t* bits, const float* valid, const float* lohi, int C, int64_t d_pad, float* out,
                      void* stream);
 

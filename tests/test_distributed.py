@@ -69,10 +69,10 @@ def test_gpus_fused_matches_nccl_path(tmp_path, attack, world):
 @pytest.mark.gpu
 @pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("mode,attack", [("median", "Random"), ("trimmed_mean", ""), ("krum", "Min-Max"), ("shieldfl", ""),
-                                         ("FLTrust", "Random")])
+                                         ("FLTrust", "Random"), ("scionfl", "Random")])
 def test_gpus_slice_owned_defences_match_gathered_path(tmp_path, mode, attack, world):
-    """Defences without gathering rows (K6 over peer rows, K-slice Gram + K1-fused weights) vs all-gather + replicated
-    aggregation; full global vectors compared."""
+    """Defences without gathering rows (K6 over peer rows, K-slice Gram + K1-fused weights, ScionFL on 1-bit codes read
+    in place) vs all-gather + replicated aggregation; full global vectors compared."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     out = {}

@@ -194,3 +194,31 @@ def test_scion_quantize_and_scores(device):
     assert torch.allclose(cosd, again, atol=1e-6) and not torch.allclose(cosd, other, atol=1e-7)
     out, kept = agg.scionfl(rows, [1.0] * c, valid=valid.bool(), scores=cosd.tolist())
     assert 1 <= len(kept) < c and out.shape == (d_pad,)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_scion_slice_owned_pieces_reproduce_the_one_pass(device):
+    """The N-GPU decomposition of the ScionFL scoring pass: every 'rank' quantises only its own rows (Philox stream id =
+    position of the row in the reporting list) and scores only its slice of the packed words, reading every client's
+    codes by address; scalars and partial sums added up must give the one-GPU distances."""
+    c, d_pad, world = 10, 4096, 2
+    rows = _rand_rows(c, d_pad, device, seed=5, spread=0.5)
+    valid = torch.ones(d_pad, device=device)
+    valid[-40:] = 0
+    rows[:, -40:] = 0
+    want, aux = flat.scion_cosine_distances(rows, valid, seed=21)
+    cpg, words = c // world, d_pad // 32
+    bits, counts, minmax = [], [], []
+    for r in range(world):                                   # owner-computes: rows r * cpg .. (r + 1) * cpg
+        b, n, mm = flat.scion_quantize(rows[r * cpg:(r + 1) * cpg].contiguous(), valid, 21, row0=r * cpg)
+        bits.append(b.contiguous()); counts.append(n); minmax.append(mm)
+    assert torch.equal(torch.cat(bits), aux["bits"]) and torch.equal(torch.cat(counts), aux["counts"])
+    counts, minmax = torch.cat(counts), torch.cat(minmax)
+    d = float(valid.sum().item())
+    lo, hi = flat.scion_clipped_levels(counts, minmax, d)
+    lohi = torch.stack([lo, hi], 1)
+    ptrs = [bits[i // cpg][i % cpg].data_ptr() for i in range(c)]
+    sums = sum(flat.scion_scores_ptrs(ptrs, words, r * words // world, (r + 1) * words // world, valid, lohi)
+               for r in range(world))
+    got = flat.scion_distances_from_sums(sums, counts, lo, hi, d)
+    assert torch.allclose(got, want, atol=2e-6)
