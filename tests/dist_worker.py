@@ -58,7 +58,8 @@ def main():
         glob = fed.global_row
     rec = {"rank": ctx.rank, "world": ctx.world, "ok": [r.ok for r in res], "metric": [r.metric for r in res],
            "attackers": [r.attackers for r in res], "checksum": float(glob.double().sum()),
-           "absmax": float(glob.abs().max()), "local": fed.local, "fused": fed.fused_comm is not None, "head_rows": head_rows, "d_pad": int(fed.layout.padded)}
+           "absmax": float(glob.abs().max()), "local": fed.local, "fused": fed.fused_comm is not None,
+           "kept": [r.info.get("scionfl_kept") for r in res], "head_rows": head_rows, "d_pad": int(fed.layout.padded)}
     with open(f"{out}.rank{ctx.rank}.json", "w") as fh:
         json.dump(rec, fh)
     torch.save(glob.detach().float().cpu(), f"{out}.rank{ctx.rank}.pt")           # full vector: compared element-wise
