@@ -343,12 +343,13 @@ def run_config(cfg: dict, attackers: dict, steps: int, warmup_req: int, clients_
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, wall = float(t[0]), float(t[1])
-        auc = None
+        auc, auc_trace = None, []
         if rank == 0:
             try:
                 with open(os.path.join(workdir, "app.log")) as fh:
                     aucs = [ln.rsplit("ROC_AUC:", 1)[1].strip() for ln in fh if "ROC_AUC:" in ln]
                 auc = float(aucs[-1]) if aucs else None
+                auc_trace = [float(x) for x in aucs]
             except Exception:                                  # noqa: BLE001
                 auc = None
     finally:
@@ -373,7 +374,7 @@ def run_config(cfg: dict, attackers: dict, steps: int, warmup_req: int, clients_
                                           + test_rows * 4),
                 "note": "the reference loop already moves every batch host->device and every loss device->host; bytes are "
                         "computed from the mean num_data of the configured range"},
-        "gpu_launches": 0, "roc_auc_last": auc,
+        "gpu_launches": 0, "roc_auc_last": auc, "roc_auc_trace": auc_trace,
     }
     if world > 1:
         dist.barrier()

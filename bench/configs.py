@@ -76,7 +76,7 @@ def run_ours(cfg_d, attackers, rounds, warmup, backend="auto"):
             fed.run_round()
     torch.cuda.synchronize(); ctx.barrier()
     native.reset_launch_count()
-    ev, phases, metric = [], {}, None
+    ev, phases, metric, trace = [], {}, None, []
     for _ in range(rounds):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -84,6 +84,7 @@ def run_ours(cfg_d, attackers, rounds, warmup, backend="auto"):
             r = fed.run_round()
         e1.record()
         ev.append((e0, e1)); metric = r.metric
+        trace.append(round(r.metric, 4) if (r.ok and r.metric == r.metric) else None)
         for k, v in r.timings_ms.items():
             phases[k] = phases.get(k, 0.0) + v / rounds
     torch.cuda.synchronize()
@@ -93,7 +94,7 @@ def run_ours(cfg_d, attackers, rounds, warmup, backend="auto"):
            "n_gpus": ctx.world, "clients": C, "rounds": rounds, "warmup": warmup, "model": cfg.server.model,
            "mode": cfg.server.mode, "attackers": {str(k): list(v) for k, v in attackers.items()},
            "phases_ms": {k: round(v, 3) for k, v in phases.items()}, "gpu_launches": native.launch_count(),
-           "metric_last": metric, "trainer": getattr(fed, "trainer", None), "plan": ({"G": fed.plan.G, "M": fed.plan.M, "S": fed.plan.S, "chunk": fed.plan.chunk} if getattr(fed, "plan", None)
+           "metric_last": metric, "metric_trace": trace, "trainer": getattr(fed, "trainer", None), "plan": ({"G": fed.plan.G, "M": fed.plan.M, "S": fed.plan.S, "chunk": fed.plan.chunk} if getattr(fed, "plan", None)
                                              else {"trainer": "har-native" if fed.har_trainer is not None else "torch"})}
     return out if ctx.rank == 0 else {}
 
