@@ -62,6 +62,21 @@ def main():
     # per-phase breakdown of the native step
     w, g = lay.views(row), lay.views(grad)
     out["native_fwd_ms"] = round(timeit(lambda: tr.forward(w, x, 1, 0, 1, True)), 3)
+    # Is the 61-launch Python loop the limit?  Enqueue 16 steps back to back without synchronising: the host time to
+    # issue them against the device time to run them (host < device: the GPU never waits for a launch, a CUDA graph of
+    # the step would not shorten the round).
+    import time
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    a.record()
+    for _ in range(16):
+        native_step()
+    b.record()
+    host = (time.perf_counter() - t0) * 1e3
+    torch.cuda.synchronize()
+    out["host_enqueue_ms_per_step"] = round(host / 16, 3)
+    out["device_ms_per_step_back_to_back"] = round(a.elapsed_time(b) / 16, 3)
     print(json.dumps(out), flush=True)
 
 

@@ -174,3 +174,35 @@ def test_client_device_cpu_is_accepted_on_a_cpu_server(tmp_path):
     fed = Federation(cfg, [ClientSpec(0, device="cpu"), ClientSpec(1)], device="cpu", workdir=str(tmp_path), verbose=False)
     assert fed._cpu_slots() == []
     assert fed.run()[0].ok
+
+
+@pytest.mark.gpu
+def test_cpu_client_slot_on_a_gpu_server(tmp_path):
+    """A client registered with ``--device cpu`` on a CUDA server trains its slot through the CPU twin and its row is
+    copied into the device arena (reference client.py:50-61: every client picks its own device)."""
+    cfg = _cfg("fedavg", "TransformerModel", 3, rounds=2)
+    fed = Federation(cfg, [ClientSpec(0, device="cpu"), ClientSpec(1), ClientSpec(2)], device="cuda", workdir=str(tmp_path),
+                     verbose=False, save=False)
+    assert fed._cpu_slots() == [0]
+    res = fed.run()
+    assert [r.ok for r in res] == [True, True] and res[-1].metric > 0.6
+    assert all(x == x and x > 0 for x in res[-1].losses)          # the CPU slot reported a loss like the GPU slots
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("trainer,clients,want", [("auto", 3, "ffma"), ("tcgen05", 3, "tcgen05"), ("ffma", 12, "ffma"),
+                                                  ("auto", 12, "tcgen05")])
+def test_trainer_selection_and_both_trainers_learn(tmp_path, trainer, clients, want):
+    """``runtime.trainer``: the interpreter while it can give every client 16 blocks, the tensor-core trainer beyond
+    (or when forced); both must learn the task through the public API."""
+    cfg = _cfg("fedavg", "TransformerModel", clients, rounds=2, runtime={"trainer": trainer},
+               learning={"batch-size": 128})
+    fed = Federation(cfg, _specs(clients), device="cuda", workdir=str(tmp_path), verbose=False, save=False)
+    assert fed.trainer == want
+    res = fed.run()
+    assert all(r.ok for r in res) and res[-1].metric > 0.6
+
+
+def test_trainer_key_is_validated():
+    with pytest.raises(Exception):
+        _cfg("fedavg", "TransformerModel", 2, runtime={"trainer": "wgmma"})
