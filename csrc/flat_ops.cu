@@ -1,6 +1,7 @@
 // CUDA kernels + C-ABI wrappers for the flat-vector ops (sm_100a).  The numerical cores live in
 // flat_core.h (shared with the CPU twin); this file adds grids, shared-memory staging and the
 // bandwidth-oriented hyper-network kernels.
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdio.h>
 
@@ -696,13 +697,15 @@ int afl_hyper_step(float* head_w, float* head_b, float* mw, float* vw, float* mb
 
 static __device__ __align__(256) float g_hyper_step_scratch[AFL_HS_FLOATS];
 
-static float* g_hs_addr[64];          // per device: device address of g_hyper_step_scratch (0 = not resolved yet)
+static std::atomic<float*> g_hs_addr[64];   // per device: device address of g_hyper_step_scratch (null = not resolved yet);
+                                            // concurrent first calls all store the same value
 
 static int hyper_step_scratch(float** out) {
   int dev = 0;
   AFL_CUDA(cudaGetDevice(&dev));
   AFL_CHECK_ARG(dev >= 0 && dev < 64, "afl_hyper_step_noalloc: device ordinal out of range");
-  if (g_hs_addr[dev] == nullptr) {
+  float* cached = g_hs_addr[dev].load(std::memory_order_acquire);
+  if (cached == nullptr) {
     float* p = nullptr;
     cudaError_t e = cudaGetSymbolAddress((void**)&p, g_hyper_step_scratch);
     if (e != cudaSuccess || p == nullptr) {
@@ -710,9 +713,10 @@ static int hyper_step_scratch(float** out) {
                         cudaGetErrorString(e));
       return e != cudaSuccess ? (int)e : -7;
     }
-    g_hs_addr[dev] = p;
+    g_hs_addr[dev].store(p, std::memory_order_release);
+    cached = p;
   }
-  *out = g_hs_addr[dev];
+  *out = cached;
   return 0;
 }
 
