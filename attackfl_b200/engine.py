@@ -921,6 +921,11 @@ class Federation:
         # The rollback snapshot belongs to THIS attempt: a round that fails before aggregation must not restore the
         # snapshot of an earlier, successful round (that would silently undo a counted and checkpointed update).
         self._hyper_snap = None
+        trace = [] if os.environ.get("ATTACKFL_HOST_TRACE") else None     # host timeline of the round (debug aid)
+
+        def mark(name):
+            if trace is not None:
+                trace.append((name, round((time.perf_counter() - t_wall) * 1e3, 3)))
         for _ in self._faults("stall"):                           # exercises the watchdog
             time.sleep(max(self.cfg.runtime.round_timeout_s * 2, 0.2))
         if self.host_train is not None:
@@ -961,6 +966,7 @@ class Federation:
             if c in self.local:
                 self.rows[self.local.index(c)].fill_(float("nan"))
         # ---- UPDATE: result flags + losses (the only per-client scalars that reach the host)
+        mark("train_enqueued")
         flags = torch.zeros(self.C, 3, device=self.device)
         for j, c in enumerate(self.local):
             flags[c, 0] = loss[j, 1]
@@ -986,7 +992,9 @@ class Federation:
         if need_gather:
             with self.timer.phase("gather"):
                 rows_all = self._all_rows()
+        mark("flags_enqueued")
         flags_h = flags.cpu()                                     # D2H: 3 floats per client
+        mark("flags_on_host")
         ok = bool((flags_h[:, 0] == 0).all()) and bool(torch.isfinite(flags_h[:, 1]).all())
         losses = [float(flags_h[c, 1] / max(float(flags_h[c, 2]) * l.epoch, 1.0)) for c in range(self.C)]
         prev_global = self.global_row.clone() if self.have_global else None
@@ -996,6 +1004,7 @@ class Federation:
             with self.timer.phase("craft"):
                 info.update(self._prepare_crafts(rows_all, genuine, center, defer_lie=fused))
             self.genuine_prev = genuine
+            mark("crafted")
             with self.timer.phase("aggregate"):
                 if sliced and rows_all is None:
                     self._aggregate_sliced(reporting, info)
@@ -1021,11 +1030,15 @@ class Federation:
                     info.update(self._aggregate(rows_all, reporting))
             if info.get("failed"):
                 ok = False
+            mark("aggregated")
         metric = None
         if ok and s.validation:
             with self.timer.phase("validate"):
                 ok = self._validate(reporting)
                 metric = self.validator.last_metric
+        mark("validated")
+        if trace is not None:
+            info["host_trace_ms"] = trace
         # ---- decision (server.py:545-567)
         if not ok:
             self._log("Training failed!", "yellow")

@@ -202,6 +202,12 @@ def run_ours(args) -> dict:
     ctx.all_reduce_max(agg_t)
     per_round, agg_ms = per_round.tolist(), agg_t.tolist()
     dev_ms = float(sum(per_round))
+    # synchronous FL: a round lasts as long as its slowest client; with more clients in the job the expected maximum of
+    # the per-client num_data (drawn from num-data-range every round) grows, which shows here as the spread between ranks
+    tr = torch.tensor([phases.get("train", 0.0), -phases.get("train", 0.0)], device=ctx.device)
+    ctx.all_reduce_max(tr)
+    train_max, train_min = float(tr[0]), -float(tr[1])
+    host_trace = r.info.get("host_trace_ms")
     # ---------------- end-to-end rounds (pinned host -> device every round, results read back)
     pinned = train.packed().pin_memory()
     fed.set_host_train(pinned)
@@ -233,7 +239,8 @@ def run_ours(args) -> dict:
                         "collectives": cfg.runtime.collectives if ctx.distributed else "single-gpu",
                         "fused_attached": fed.fused_comm is not None,
                         "nvls": bool(getattr(fed.fused_comm, "multicast", False)) if fed.fused_comm is not None else False,
-                        "launches_per_round": round(launches / max(args.steps, 1), 2)},
+                        "launches_per_round": round(launches / max(args.steps, 1), 2),
+                        "train_ms_slowest_rank": round(train_max, 3), "train_ms_fastest_rank": round(train_min, 3)},
         "round_ms": {"median": _pct(per_round, 0.5), "p95": _pct(per_round, 0.95), "max": _pct(per_round, 1.0)},
         "aggregate_ms": {"median": _pct(agg_ms, 0.5), "p95": _pct(agg_ms, 0.95), "max": _pct(agg_ms, 1.0)},
         "clocks": clocks,
@@ -245,6 +252,8 @@ def run_ours(args) -> dict:
         "phases_ms": {k: round(v, 3) for k, v in phases.items()},
         "roc_auc_last": metrics[-1],
     }
+    if host_trace:
+        out["host_trace_ms_last_round"] = host_trace
     fed.close()
     if ctx.distributed:
         dist.barrier()
