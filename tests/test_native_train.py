@@ -263,3 +263,38 @@ def test_infer_matches_module(device, name):
     assert probs.shape == (2, 133)
     assert torch.allclose(probs[0], want, atol=1e-5)
     assert not torch.allclose(probs[1], want, atol=1e-3)
+
+
+@pytest.mark.gpu
+def test_production_plan_round_matches_torch_adam():
+    """The plan bench.py runs (8 clients, 16 blocks per client, tiles of 8 samples, batch 128) against torch.optim.Adam
+    on the PyTorch module, dropout off; then dropout on: the same plan against a different split of the batch (the
+    Philox masks are keyed by sample, so the result may not depend on G / M / S)."""
+    name, device = "TransformerModel", "cuda"
+    _, lay = _setup(name, seed=8)
+    ds = synthetic_icu(1400, 21)
+    n_data = [300, 257, 384, 129, 512, 640, 200, 1024]       # ragged; clients 1 and 3 end on a batch of one sample (skipped)
+    batch, epochs = 128, 2
+    idx = make_round_indices(1400, n_data, epochs, torch.Generator().manual_seed(4))
+    rows = torch.stack([lay.flatten(models.build(name).state_dict()) for _ in n_data])
+    got, loss, steps = _native_round(name, lay, rows, ds, idx, n_data, batch, epochs, device, 16, 1, 8, lr=0.004)
+    for c, n in enumerate(n_data):
+        want, tot, st = _torch_round(name, lay, rows[c], ds, idx[c], n, batch, epochs, 0.004)
+        assert int(steps[c]) == st
+        assert loss[c, 1].item() == 0 and loss[c, 0].item() == pytest.approx(tot, rel=1e-4)
+        diff = (got[c] - want).abs()
+        assert float((diff > 2e-4).float().mean()) < 2e-3 and float(diff.max()) < 2 * 0.004, (c, diff.max())
+    res = []
+    for (S, G, M) in ((8, 16, 1), (8, 4, 4), (16, 8, 1)):
+        prog = build_program(name, lay, S=S, train=True, dropout=True).to(device)
+        w = rows.clone().to(device)
+        m, v = torch.zeros_like(w), torch.zeros_like(w)
+        gpart = torch.zeros(len(n_data) * G, lay.padded, device=device)
+        T.train_round(prog, T.TrainPlan(G, M, S, len(n_data)), w, m, v, gpart, ds.packed().to(device), idx.to(device),
+                      torch.tensor(n_data, dtype=torch.int32, device=device),
+                      torch.arange(len(n_data), dtype=torch.int32, device=device), batch, epochs, seed=5, dropout=True)
+        res.append(w.cpu())
+    assert not torch.allclose(res[0], got, atol=1e-4)          # dropout did change the trajectory
+    for r in res[1:]:
+        d = (res[0] - r).abs()
+        assert float((d > 2e-4).float().mean()) < 2e-3 and float(d.max()) < 2 * 0.004
