@@ -1004,6 +1004,8 @@ class Federation:
             with self.timer.phase("craft"):
                 info.update(self._prepare_crafts(rows_all, genuine, center, defer_lie=fused))
             self.genuine_prev = genuine
+            if self.fused_comm is not None and os.environ.get("ATTACKFL_DEBUG_OWNERSHIP"):
+                self.fused_comm.assert_ownership(reporting)
             mark("crafted")
             with self.timer.phase("aggregate"):
                 if sliced and rows_all is None:

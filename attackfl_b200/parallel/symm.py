@@ -91,6 +91,36 @@ class FusedComm:
             dist.all_reduce(flag, op=dist.ReduceOp.MAX)
             self.any_rank_saves = bool(flag.item() > 0)       # checkpoints need the shards gathered: a collective
 
+    def assert_ownership(self, reporting: List[int]) -> None:
+        """Debug build of the arena (``ATTACKFL_DEBUG_OWNERSHIP=1``): checks, every round and on every rank,
+        the invariants the fused kernels rely on but cannot see — client c lives on rank ``c // cpg`` and nowhere else,
+        this rank's view of its own rows is the tensor the trainer writes, the coordinate slices of the ranks partition
+        ``[0, D)`` on 128-byte boundaries, a sharded hyper head holds exactly this rank's slice, and every rank enters
+        the collective with the same reporting list and epoch (a mismatch would deadlock or mix rounds)."""
+        fed = self.fed
+        D, W, r = fed.D, self.world, self.rank
+        assert fed.local == list(range(r * self.cpg, min(fed.C, (r + 1) * self.cpg))), "clients are not block-distributed"
+        assert fed.rows.data_ptr() == self.rows.data_ptr() == int(self.h_rows.buffer_ptrs[r]), "trainer rows are not the symmetric rows"
+        assert fed.global_row.data_ptr() == int(self.h_glob.buffer_ptrs[r]), "global row is not the symmetric buffer"
+        for c in fed.local:
+            assert self.row_ptr(c) == fed.rows[c - fed.local[0]].data_ptr(), f"row of client {c} is not where its owner trains it"
+        for c in reporting:
+            assert 0 <= c // self.cpg < W, f"client {c} has no owner rank"
+        sl = D // W
+        assert sl * W == D and sl % 32 == 0, "coordinate slices must partition the row on 128-byte boundaries"
+        nh = getattr(fed, "native_hyper", None)
+        if self.hyper_sharded and nh is not None:
+            assert (nh.lo, nh.hi) == (r * sl, (r + 1) * sl), "hyper head slice is not this rank's coordinate slice"
+            if nh.fused.sharded:
+                assert nh.head_w.shape[0] == sl and nh.mw.shape[0] == sl and nh.vw.shape[0] == sl
+        h = 0
+        for c in reporting:
+            h = (h * 1000003 + c + 1) % 2147483647
+        t = torch.tensor([float(h), -float(h), float(self.epoch), -float(self.epoch)], dtype=torch.float64, device=fed.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        assert float(t[0]) == -float(t[1]), "ranks disagree on the reporting clients of this round"
+        assert float(t[2]) == -float(t[3]), "ranks disagree on the epoch of the fused collectives"
+
     def row_ptr(self, client: int) -> int:
         """Device address of a client's row on this rank's view of its owner's arena (peer-mapped)."""
         return int(self.h_rows.buffer_ptrs[client // self.cpg]) + (client % self.cpg) * self.fed.D * 4

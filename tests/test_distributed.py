@@ -50,7 +50,7 @@ def test_gpus_fused_matches_nccl_path(tmp_path, attack, world):
     for collectives in ("nccl", "fused"):
         d = tmp_path / collectives
         d.mkdir()
-        recs = _launch(d, world, "fedavg", attack, {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives,
+        recs = _launch(d, world, "fedavg", attack, {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives, "ATTACKFL_DEBUG_OWNERSHIP": "1",
                                                     "AFL_TEST_CLIENTS": "8"})
         a = recs[0]
         for b in recs[1:]:
@@ -79,7 +79,7 @@ def test_gpus_slice_owned_defences_match_gathered_path(tmp_path, mode, attack, w
     for collectives in ("nccl", "fused"):
         d = tmp_path / collectives
         d.mkdir()
-        recs = _launch(d, world, mode, attack, {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives,
+        recs = _launch(d, world, mode, attack, {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives, "ATTACKFL_DEBUG_OWNERSHIP": "1",
                                                 "AFL_TEST_CLIENTS": "8", "AFL_TEST_ROUNDS": "3"})
         a = recs[0]
         assert a["ok"] == [True] * 3
@@ -108,7 +108,7 @@ def test_gpus_sharded_hyper_matches_gathered_path(tmp_path, world):
     for collectives in ("nccl", "fused"):
         d = tmp_path / collectives
         d.mkdir()
-        recs = _launch(d, world, "hyper", "", {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives,
+        recs = _launch(d, world, "hyper", "", {"AFL_TEST_DEVICE": "cuda", "AFL_TEST_COLLECTIVES": collectives, "ATTACKFL_DEBUG_OWNERSHIP": "1",
                                                "AFL_TEST_CLIENTS": "8", "AFL_TEST_ROUNDS": "3"})
         a = recs[0]
         assert a["ok"] == [True] * 3
