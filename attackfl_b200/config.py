@@ -95,6 +95,8 @@ class RuntimeCfg:
     cta_per_client: int = 0          # 0 = auto
     trainer: str = "auto"            # auto | ffma (op-program interpreter) | tcgen05 (tensor-core trainer, TransformerModel)
     collectives: str = "fused"       # fused (P2P/multimem kernels) | nccl (debug fall-back)
+    index_rng: str = "perm"          # per-round sample indices: perm (keyed permutations, one launch, device-independent)
+                                     # | torch (argsort of torch.rand keys on the run's device generator)
     synthetic_train_rows: int = 16384
     synthetic_test_rows: int = 4096
     metrics_file: str = "metrics.jsonl"
@@ -191,6 +193,8 @@ def validate(cfg: Config) -> None:
         raise ValueError(f"attack.search '{cfg.attack.search}' is not valid")
     if s.hyper_update not in ("sequential", "batched"):
         raise ValueError(f"server.hyper-update '{s.hyper_update}' is not valid")
+    if cfg.runtime.index_rng not in ("perm", "torch"):
+        raise ValueError(f"runtime.index-rng '{cfg.runtime.index_rng}' is not valid (perm|torch)")
     if cfg.runtime.trainer not in ("auto", "ffma", "tcgen05"):
         raise ValueError(f"runtime.trainer '{cfg.runtime.trainer}' is not valid (auto|ffma|tcgen05)")
     for f in cfg.runtime.fault_inject:

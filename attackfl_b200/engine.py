@@ -179,7 +179,8 @@ class Federation:
         self.genuine_prev: Optional[List[int]] = None        # indices of last round's genuine reporters
         self.timer = PhaseTimer(self.device, nvtx=cfg.runtime.nvtx)
         self.watchdog = Watchdog(cfg.runtime.round_timeout_s)
-        self.validator = Validator(self.data_name, self.logger if ctx.rank == 0 else None, quiet=ctx.rank != 0)
+        self.validator = Validator(self.data_name, self.logger if ctx.rank == 0 else None, quiet=ctx.rank != 0,
+                                   native=self.backend == "native")
         self.metrics = MetricsWriter(os.path.join(workdir, cfg.runtime.metrics_file) if (save and ctx.rank == 0) else None)
         self.history: List[RoundResult] = []
         self.fused_comm = None                               # set by parallel.symm.attach()
@@ -302,13 +303,28 @@ class Federation:
             return []
         return [j for j, c in enumerate(self.local) if str(self.specs[c].device or "").startswith("cpu")]
 
+    def _round_indices(self, sizes_local: List[int]) -> torch.Tensor:
+        """int32 ``[CL, epochs, max_size]``: the records every local client visits this round, per epoch
+        (``random.sample`` + ``DataLoader(shuffle=True)``, ``/root/reference/src/RpcClient.py:166,169``).  Default: keyed
+        permutations in one native launch (``ops.flat.round_indices``; the same indices on every device and for every
+        trainer); ``runtime.index-rng: torch`` keeps the argsort-of-random-keys generator on the run's device generator."""
+        l = self.cfg.learning
+        sizes = [max(s, 1) for s in sizes_local]
+        if self.cfg.runtime.index_rng == "torch":
+            return make_round_indices(self.n_train, sizes, l.epoch, self.dev_gen, self.device)
+        from .ops import flat
+        st = torch.tensor(sizes, dtype=torch.int32, device=self.device)
+        cids = torch.tensor(self.local, dtype=torch.int32, device=self.device)
+        seed = (int(self.cfg.server.random_seed or 0) * 0x9E3779B97F4A7C15 + self.attempt * 0xD1B54A32D192ED03 + 0x1234) & (2 ** 64 - 1)
+        return flat.round_indices(self.n_train, st, cids, l.epoch, max(sizes), seed)
+
     def _train_native(self, sizes_local: List[int]) -> torch.Tensor:
         l = self.cfg.learning
         T = self.T
         cpu_slots = self._cpu_slots()
         sizes_dev = [0 if j in cpu_slots else n for j, n in enumerate(sizes_local)]
         n_data = torch.tensor(sizes_dev, dtype=torch.int32, device=self.device)
-        idx = make_round_indices(self.n_train, [max(s, 1) for s in sizes_local], l.epoch, self.dev_gen, self.device)
+        idx = self._round_indices(sizes_local)
         self.m[:self.CL].zero_()
         self.v[:self.CL].zero_()
         cids = torch.tensor(self.local, dtype=torch.int32, device=self.device)
@@ -350,7 +366,7 @@ class Federation:
         from .ops import flat
         l = self.cfg.learning
         loss_out = torch.zeros(self.CL, 2, device=self.device)
-        idx = make_round_indices(self.n_train, [max(s, 1) for s in sizes_local], l.epoch, self.dev_gen, self.device)
+        idx = self._round_indices(sizes_local)
         mod = self.module.to(self.device)
         for j in range(self.CL):
             n = sizes_local[j]
@@ -402,7 +418,7 @@ class Federation:
         l = self.cfg.learning
         tr = self.har_trainer
         loss_out = torch.zeros(self.CL, 2, device=self.device)
-        idx = make_round_indices(self.n_train, [max(s, 1) for s in sizes_local], l.epoch, self.dev_gen, self.device)
+        idx = self._round_indices(sizes_local)
         seed = (int(self.cfg.server.random_seed or 0) << 20) ^ (self.attempt * 2654435761 & 0xFFFFFFFF)
         if not hasattr(self, "_har_grad"):
             self._har_grad = torch.zeros(self.D, device=self.device)

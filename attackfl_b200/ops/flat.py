@@ -114,6 +114,35 @@ def coord_select(rows: torch.Tensor, mode: str, trim: int = 0, out: Optional[tor
     return out
 
 
+ROC_AUC_MAX = 8192
+
+
+def roc_auc(scores: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """``[auc, #NaN scores, #positives, #negatives]`` (device tensor, no host sync) for up to ``ROC_AUC_MAX`` scores:
+    the tie-aware trapezoid of ``validation.roc_auc`` in one launch."""
+    s = scores.reshape(-1).to(torch.float32).contiguous()
+    y = labels.reshape(-1).to(device=s.device, dtype=torch.float32).contiguous()
+    assert s.numel() == y.numel() and 1 <= s.numel() <= ROC_AUC_MAX
+    lib = lib_for(s)
+    out = torch.empty(4, dtype=torch.float32, device=s.device)
+    check(lib, lib.afl_roc_auc(ptr(s), ptr(y), c_i64(s.numel()), ptr(out), stream_ptr(s)), "afl_roc_auc")
+    return out
+
+
+def round_indices(n_rows: int, sizes: torch.Tensor, client_ids: torch.Tensor, epochs: int, max_size: int, seed: int) -> torch.Tensor:
+    """Per-round sample indices ``[C, epochs, max_size]`` int32 (-1 past a client's size): a random subset of ``sizes[c]``
+    of the ``n_rows`` records per client and a fresh order per epoch (``random.sample`` + ``DataLoader(shuffle=True)``,
+    ``src/RpcClient.py:166,169``), as keyed permutations evaluated per element — one launch, no sort, the same indices on
+    the CPU twin and on the GPU.  ``sizes`` / ``client_ids``: int32 tensors on the target device."""
+    assert sizes.dtype == torch.int32 and client_ids.dtype == torch.int32 and sizes.numel() == client_ids.numel()
+    C = sizes.numel()
+    lib = lib_for(sizes)
+    idx = torch.empty(C, epochs, max_size, dtype=torch.int32, device=sizes.device)
+    check(lib, lib.afl_round_indices(ptr(idx), ptr(sizes), ptr(client_ids), c_i(C), c_i(epochs), c_i(max_size), c_i(n_rows),
+                                     c_u64(seed & (2 ** 64 - 1)), stream_ptr(sizes)), "afl_round_indices")
+    return idx
+
+
 def scion_quantize(rows: torch.Tensor, valid: Optional[torch.Tensor], seed: int, row0: int = 0,
                    bits: Optional[torch.Tensor] = None):
     """ScionFL 1-bit stochastic quantisation of every row (``src/Utils.py:372-376``), packed 32 coordinates per word.

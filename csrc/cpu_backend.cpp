@@ -9,6 +9,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "../include/attackfl_b200.h"
@@ -91,6 +92,35 @@ int afl_coord_select(const float* rows, int C, int64_t d_pad, float* out, int mo
   CHECK_ARG(C >= 1 && C <= AFL_SEL_MAX, "afl_coord_select: 1 <= C <= 256");
   CHECK_ARG(mode == 0 || 2 * trim < C, "afl_coord_select: 2*trim must be < C");
   afl_select_core(rows, C, d_pad, out, mode, trim, 0, d_pad, 0, 1);
+  return 0;
+}
+
+int afl_roc_auc(const float* scores, const float* labels, int64_t n, float* out4, void*) {
+  CHECK_ARG(n >= 1 && n <= 8192, "afl_roc_auc: 1 <= n <= 8192 (larger sets: sort on the caller's side)");
+  int n_nan = 0;
+  for (int64_t i = 0; i < n; ++i) if (scores[i] != scores[i]) ++n_nan;
+  if (n_nan) { out4[0] = NAN; out4[1] = (float)n_nan; out4[2] = 0.f; out4[3] = 0.f; return 0; }
+  std::vector<int> order((size_t)n);
+  for (int64_t i = 0; i < n; ++i) order[(size_t)i] = (int)i;
+  std::sort(order.begin(), order.end(), [&](int a, int b) { return scores[a] > scores[b]; });
+  double area = 0.0;
+  int64_t tp = 0, fp = 0, tp_prev = 0, fp_prev = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (labels[order[(size_t)i]] > 0.5f) ++tp; else ++fp;
+    if (i == n - 1 || scores[order[(size_t)i]] != scores[order[(size_t)(i + 1)]]) {      // end of a tie group
+      area += 0.5 * (double)(fp - fp_prev) * (double)(tp + tp_prev);
+      tp_prev = tp; fp_prev = fp;
+    }
+  }
+  out4[0] = (tp == 0 || fp == 0) ? NAN : (float)(area / ((double)tp * (double)fp));
+  out4[1] = 0.f; out4[2] = (float)tp; out4[3] = (float)fp;
+  return 0;
+}
+
+int afl_round_indices(int32_t* idx, const int32_t* sizes, const int32_t* client_ids, int C, int E, int mx, int n_rows,
+                      uint64_t seed, void*) {
+  CHECK_ARG(C >= 1 && E >= 1 && mx >= 1 && n_rows >= 1, "afl_round_indices: C, E, mx, n_rows >= 1");
+  afl_round_indices_core(idx, sizes, client_ids, C, E, mx, n_rows, (uint32_t)seed, (uint32_t)(seed >> 32), 0, 1);
   return 0;
 }
 

@@ -183,6 +183,56 @@ AFL_DEV void afl_craft_random_core(float* out, const float* w, const float* vali
   }
 }
 
+// ----------------------------------------------------------------------------------------- per-round sample indices
+// A client's round draws `size` of the `n_rows` training records without replacement (random.sample, RpcClient.py:166) and
+// walks them in a fresh random order every epoch (DataLoader(shuffle=True), :169).  Instead of sorting random keys, both
+// are keyed pseudo-random PERMUTATIONS evaluated per element: an unbalanced Feistel network on ceil(log2 n) bits with
+// cycle walking is a bijection of [0, n), so idx[e][i] = P_subset(P_epoch_e(i)) needs no memory, no sort and is the same
+// function on the CPU twin and on the GPU.
+AFL_HD uint32_t afl_mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+
+AFL_HD uint32_t afl_prp(uint32_t i, uint32_t n, uint32_t k0, uint32_t k1) {
+  if (n <= 1) return 0;
+  int bits = 2;
+  while (bits < 32 && (1u << bits) < n) ++bits;
+  const int lb = bits / 2, rb = bits - lb;
+  const uint32_t lm = (1u << lb) - 1u, rm = (1u << rb) - 1u;
+  uint32_t x = i;
+  do {
+    uint32_t L = x >> rb, R = x & rm;
+    for (uint32_t r = 0; r < 6; ++r) {
+      if (r & 1u) R = (R ^ afl_mix32(L * 0x9E3779B9u + k1 + r * 0x632BE5ABu)) & rm;
+      else        L = (L ^ afl_mix32(R * 0x85EBCA6Bu + k0 + r * 0xC2B2AE35u)) & lm;
+    }
+    x = (L << rb) | R;
+  } while (x >= n);
+  return x;
+}
+
+// record index of position i (< size) of epoch `epoch` of client `client`
+AFL_HD int32_t afl_round_index(uint32_t seed_lo, uint32_t seed_hi, uint32_t client, uint32_t epoch, uint32_t i,
+                               uint32_t size, uint32_t n_rows) {
+  const uint32_t kc = afl_mix32(seed_lo ^ afl_mix32(client + 0x9E3779B9u)), kd = afl_mix32(seed_hi + 0x7F4A7C15u * (client + 1u));
+  const uint32_t ke = afl_mix32(kc ^ afl_mix32(epoch + 0x51ED270Bu));
+  const uint32_t pos = afl_prp(i, size, ke, kd ^ epoch);               // this epoch's order
+  return (int32_t)afl_prp(pos, n_rows, kc, kd);                       // the round's subset (first `size` images of the PRP)
+}
+
+AFL_DEV void afl_round_indices_core(int32_t* idx, const int32_t* sizes, const int32_t* client_ids, int C, int E, int mx,
+                                    int n_rows, uint32_t seed_lo, uint32_t seed_hi, int64_t tid, int64_t nt) {
+  const int64_t total = (int64_t)C * E * mx;
+  for (int64_t t = tid; t < total; t += nt) {
+    const int i = (int)(t % mx), e = (int)((t / mx) % E), c = (int)(t / ((int64_t)mx * E));
+    const int size = sizes[c] < n_rows ? sizes[c] : n_rows;
+    idx[t] = i < size ? afl_round_index(seed_lo, seed_hi, (uint32_t)client_ids[c], (uint32_t)e, (uint32_t)i, (uint32_t)size,
+                                        (uint32_t)n_rows)
+                      : -1;
+  }
+}
+
 // ----------------------------------------------------------------------------------------- ScionFL (S7)
 // 1-bit stochastic quantisation of a row: sigma_j ~ Bernoulli((x_j - min) / (max - min + 1e-6)), one Philox stream
 // per (seed, row).  The dequantised rows  lo_i + sigma_ij (hi_i - lo_i)  are never materialised: everything the filter

@@ -62,6 +62,127 @@ __global__ void __launch_bounds__(128) select_kernel(const float* rows, int C, i
   afl_select_core(rows, C, d_pad, out, mode, trim, 0, d_pad, blockIdx.x * 128 + threadIdx.x, gridDim.x * 128);
 }
 
+__global__ void __launch_bounds__(256) round_indices_kernel(int32_t* __restrict__ idx, const int32_t* __restrict__ sizes,
+                                                            const int32_t* __restrict__ client_ids, int C, int E, int mx,
+                                                            int n_rows, uint32_t s0, uint32_t s1) {
+  afl_round_indices_core(idx, sizes, client_ids, C, E, mx, n_rows, s0, s1, (int64_t)blockIdx.x * 256 + threadIdx.x,
+                         (int64_t)gridDim.x * 256);
+}
+
+// ---- ROC-AUC of <= 8192 scores in ONE block (src/Validation.py:113-120: roc_curve + auc on the pooled outputs): 64-bit
+// keys (ordered score | label | index) bitonic-sorted in shared memory, prefix count of positives, previous-tie-group scan
+// and the tie-aware trapezoid sum; out = {auc, #NaN scores, #positives, #negatives}.  Replaces ~20 torch launches and three
+// host syncs of the validation phase by one launch and one 16-byte read.
+__device__ __forceinline__ unsigned f2ord_auc(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+
+__global__ void __launch_bounds__(1024) roc_auc_kernel(const float* __restrict__ scores, const float* __restrict__ labels, int n,
+                                                       int P, float* __restrict__ out) {
+  extern __shared__ unsigned long long auc_keys[];          // [P]
+  int* tp = reinterpret_cast<int*>(auc_keys + P);          // [P] inclusive count of positives in sorted order
+  int* pe = tp + P;                                        // [P] index of the last tie-group end before i (-1: none)
+  __shared__ int s_nan;
+  __shared__ int wtmp[32];
+  __shared__ double wred[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_nan = 0;
+  __syncthreads();
+  int nan_local = 0;
+  for (int i = tid; i < P; i += 1024) {
+    unsigned long long k = 0ull;                           // padding sorts after every real key
+    if (i < n) {
+      const float sc = scores[i];
+      if (sc != sc) ++nan_local;
+      const unsigned lab = labels[i] > 0.5f ? 1u : 0u;
+      k = ((unsigned long long)f2ord_auc(sc) << 32) | (unsigned long long)((lab << 31) | (unsigned)i);
+    }
+    auc_keys[i] = k;
+  }
+  if (nan_local) atomicAdd(&s_nan, nan_local);
+  __syncthreads();
+  if (s_nan) {
+    if (tid == 0) { out[0] = __int_as_float(0x7fc00000); out[1] = (float)s_nan; out[2] = 0.f; out[3] = 0.f; }
+    return;
+  }
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < P; i += 1024) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long a = auc_keys[i], b = auc_keys[ixj];
+          const bool desc = (i & k) == 0;
+          if (desc ? a < b : a > b) { auc_keys[i] = b; auc_keys[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // contiguous chunk per thread
+  const int ipt = P / 1024, i0 = tid * ipt;
+  int pos = 0, last_end = -1;
+  for (int q = 0; q < ipt; ++q) {
+    const int i = i0 + q;
+    if (i < n) {
+      pos += (int)((auc_keys[i] >> 31) & 1ull);
+      const bool end = i == n - 1 || (unsigned)(auc_keys[i] >> 32) != (unsigned)(auc_keys[i + 1] >> 32);
+      if (end) last_end = i;
+    }
+  }
+  // block exclusive scans of (pos: sum) and (last_end: max)
+  int sp = pos, se = last_end;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int vp = __shfl_up_sync(0xffffffffu, sp, o), ve = __shfl_up_sync(0xffffffffu, se, o);
+    if (lane >= o) { sp += vp; se = max(se, ve); }
+  }
+  if (lane == 31) { wtmp[warp] = sp; }
+  __syncthreads();
+  int wp = 0;
+  for (int w = 0; w < warp; ++w) wp += wtmp[w];
+  __syncthreads();
+  if (lane == 31) wtmp[warp] = se;
+  __syncthreads();
+  int we = -1;
+  for (int w = 0; w < warp; ++w) we = max(we, wtmp[w]);
+  int run_p = wp + sp - pos;                               // positives before this thread's chunk
+  int ex_e = __shfl_up_sync(0xffffffffu, se, 1);
+  int run_e = max(we, lane ? ex_e : -1);                   // last group end before this thread's chunk
+  for (int q = 0; q < ipt; ++q) {
+    const int i = i0 + q;
+    if (i < n) {
+      run_p += (int)((auc_keys[i] >> 31) & 1ull);
+      tp[i] = run_p;
+      pe[i] = run_e;
+      const bool end = i == n - 1 || (unsigned)(auc_keys[i] >> 32) != (unsigned)(auc_keys[i + 1] >> 32);
+      if (end) run_e = i;
+    }
+  }
+  __syncthreads();
+  double area = 0.0;
+  for (int q = 0; q < ipt; ++q) {
+    const int i = i0 + q;
+    if (i < n) {
+      const bool end = i == n - 1 || (unsigned)(auc_keys[i] >> 32) != (unsigned)(auc_keys[i + 1] >> 32);
+      if (end) {
+        const int p = pe[i];
+        const int tp_p = p >= 0 ? tp[p] : 0, fp_p = p >= 0 ? (p + 1 - tp[p]) : 0;
+        const int tp_i = tp[i], fp_i = i + 1 - tp_i;
+        area += 0.5 * (double)(fp_i - fp_p) * (double)(tp_i + tp_p);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) area += __shfl_xor_sync(0xffffffffu, area, o);
+  if (lane == 0) wred[warp] = area;
+  __syncthreads();
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < 32; ++w) tot += wred[w];
+    const int n_pos = tp[n - 1], n_neg = n - n_pos;
+    out[0] = (n_pos == 0 || n_neg == 0) ? __int_as_float(0x7fc00000) : (float)(tot / ((double)n_pos * (double)n_neg));
+    out[1] = 0.f; out[2] = (float)n_pos; out[3] = (float)n_neg;
+  }
+}
+
 // ---- ScionFL: min/max per row (one block per (chunk, row); partials merged with ordered-int atomics)
 __device__ __forceinline__ unsigned f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __device__ __forceinline__ float ord2f(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u); }
@@ -564,6 +685,27 @@ int afl_coord_select_ptrs(const float* const* row_ptrs_dev, int C, int64_t lo, i
   else select_warp_kernel<8><<<grid, 256, smem, st>>>(nullptr, C, hi, nullptr, mode, trim, row_ptrs_dev, lo, hi, dst_dev, n_dst);
   afl_rt::count_launch();
   return afl_rt::check_last("afl_coord_select_ptrs");
+}
+
+int afl_round_indices(int32_t* idx, const int32_t* sizes, const int32_t* client_ids, int C, int E, int mx, int n_rows,
+                      uint64_t seed, void* stream) {
+  AFL_CHECK_ARG(C >= 1 && E >= 1 && mx >= 1 && n_rows >= 1, "afl_round_indices: C, E, mx, n_rows >= 1");
+  const int64_t total = (int64_t)C * E * mx;
+  round_indices_kernel<<<grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>(idx, sizes, client_ids, C, E, mx, n_rows,
+                                                                                   (uint32_t)seed, (uint32_t)(seed >> 32));
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_round_indices");
+}
+
+int afl_roc_auc(const float* scores, const float* labels, int64_t n, float* out4, void* stream) {
+  AFL_CHECK_ARG(n >= 1 && n <= 8192, "afl_roc_auc: 1 <= n <= 8192 (larger sets: sort on the caller's side)");
+  int P = 1024;
+  while (P < n) P <<= 1;
+  const size_t smem = (size_t)P * 16;
+  AFL_CUDA(cudaFuncSetAttribute(roc_auc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 16));
+  roc_auc_kernel<<<1, 1024, smem, (cudaStream_t)stream>>>(scores, labels, (int)n, P, out4);
+  afl_rt::count_launch();
+  return afl_rt::check_last("afl_roc_auc");
 }
 
 int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void* stream) {

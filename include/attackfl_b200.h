@@ -162,6 +162,14 @@ int afl_har_head(const float* pooled, const float* w1, const float* b1, const fl
 int afl_scion_minmax(const float* rows, const float* valid, int C, int64_t d_pad, float* minmax, void* stream);
 int afl_scion_quantize(const float* rows, const float* valid, const float* minmax, int C, int64_t d_pad, uint64_t seed,
                        uint32_t* bits, int* counts, void* stream);
+/* Tie-aware ROC-AUC of n <= 8192 scores (= sklearn auc(roc_curve), src/Validation.py:113-120) in one launch:
+ * out4 = {auc (NaN if one class is empty or a score is NaN), number of NaN scores, positives, negatives}. */
+int afl_roc_auc(const float* scores, const float* labels, int64_t n, float* out4, void* stream);
+/* Per-round sample indices of C clients (RpcClient.py:166,169): idx [C][E][mx] int32, entry (c, e, i) = the record client
+ * client_ids[c] visits at position i of epoch e, -1 for i >= sizes[c].  Subset and per-epoch order are keyed permutations
+ * (Feistel network + cycle walking) of (seed, client, epoch): no sort, no state, identical on the CPU twin and the GPU. */
+int afl_round_indices(int32_t* idx, const int32_t* sizes, const int32_t* client_ids, int C, int E, int mx, int n_rows,
+                      uint64_t seed, void* stream);
 /* N-GPU forms (CUDA build): _quantize_rows keys the Philox stream of local row c by row0 + c (its position in the round's
  * reporting list), so every rank draws the bits the one-GPU pass would; _scores_ptrs takes the packed rows by address
  * (bits_ptrs_dev [C], peer-mapped allowed) and visits the words [w_lo, w_hi) only: partial sums of an owned slice. */

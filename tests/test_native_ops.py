@@ -222,3 +222,69 @@ def test_scion_slice_owned_pieces_reproduce_the_one_pass(device):
                for r in range(world))
     got = flat.scion_distances_from_sums(sums, counts, lo, hi, d)
     assert torch.allclose(got, want, atol=2e-6)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_round_indices_are_keyed_permutations(device):
+    """``afl_round_indices``: every (client, epoch) row is a permutation of ONE subset of the pool (sampling without
+    replacement, a fresh order per epoch), reproducible from (seed, client id), different across clients / seeds, and
+    statistically uniform: every record is picked with probability size / n_rows and lands anywhere in the epoch."""
+    n_rows, epochs = 1000, 3
+    sizes = torch.tensor([400, 257, 1, 1000, 640], dtype=torch.int32, device=device)
+    cids = torch.tensor([0, 1, 2, 9, 4], dtype=torch.int32, device=device)
+    idx = flat.round_indices(n_rows, sizes, cids, epochs, 1000, seed=77).cpu()
+    assert idx.shape == (5, epochs, 1000) and idx.dtype == torch.int32
+    for c, n in enumerate(sizes.tolist()):
+        first = set(idx[c, 0, :n].tolist())
+        assert len(first) == n and min(first) >= 0 and max(first) < n_rows
+        for e in range(epochs):
+            assert (idx[c, e, n:] == -1).all()
+            assert set(idx[c, e, :n].tolist()) == first                      # the same subset every epoch ...
+        if n > 8:
+            assert idx[c, 0, :n].tolist() != idx[c, 1, :n].tolist()           # ... in a different order
+    again = flat.round_indices(n_rows, sizes, cids, epochs, 1000, seed=77).cpu()
+    other = flat.round_indices(n_rows, sizes, cids, epochs, 1000, seed=78).cpu()
+    assert torch.equal(idx, again) and not torch.equal(idx, other)
+    # the CPU twin and the GPU evaluate the same integer function
+    ref = flat.round_indices(n_rows, sizes.cpu(), cids.cpu(), epochs, 1000, seed=77)
+    assert torch.equal(idx, ref)
+    # statistics over 400 clients: inclusion frequency of every record ~ Binomial(400, 0.3); mean position of a record
+    # inside the epochs it appears in ~ uniform
+    C = 400
+    big = flat.round_indices(n_rows, torch.full((C,), 300, dtype=torch.int32, device=device),
+                             torch.arange(C, dtype=torch.int32, device=device), 2, 300, seed=5).cpu().long()
+    counts = torch.bincount(big[:, 0, :].reshape(-1), minlength=n_rows).float()
+    z = (counts - C * 0.3) / (C * 0.3 * 0.7) ** 0.5
+    assert float(z.abs().max()) < 5.0 and abs(float(z.mean())) < 0.2 and 0.8 < float(z.std()) < 1.2
+    pos = torch.arange(300).repeat(C).float()
+    mean_pos = torch.zeros(n_rows).index_add_(0, big[:, 1, :].reshape(-1), pos) / counts.clamp_min(1)
+    assert abs(float(mean_pos[counts > 0].mean()) - 149.5) < 2.0
+    # consecutive positions are not correlated with consecutive records
+    d = (big[:, 0, 1:] - big[:, 0, :-1]).float()
+    assert abs(float(d.mean())) < 3.0 and float((d == 1).float().mean()) < 0.01
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_native_roc_auc_matches_the_torch_restatement(device):
+    """``afl_roc_auc`` (one block: bitonic sort of 64-bit keys, prefix counts, tie-group scan, trapezoid) against
+    ``validation.roc_auc`` (== sklearn ``auc(roc_curve)``), with heavy ties, tiny sets, a single class and NaN scores."""
+    from attackfl_b200.validation import roc_auc
+    g = torch.Generator().manual_seed(3)
+    for n in (2, 3, 31, 100, 1000, 1024, 1025, 4096, 5000, 8192):
+        s = torch.rand(n, generator=g)
+        s[::3] = (s[::3] * 8).round() / 8                      # large tie groups, also across classes
+        y = (torch.rand(n, generator=g) < 0.3).float()
+        y[0], y[1] = 1.0, 0.0
+        out = flat.roc_auc(s.to(device), y.to(device)).cpu()
+        assert float(out[0]) == pytest.approx(roc_auc(s, y), abs=2e-6), n
+        assert out[1] == 0 and out[2] == y.sum() and out[3] == n - y.sum()
+    const = flat.roc_auc(torch.full((64,), 0.5, device=device), (torch.arange(64) % 2).float().to(device)).cpu()
+    assert float(const[0]) == pytest.approx(0.5)               # all scores tied: chance level
+    perfect = flat.roc_auc(torch.arange(10, device=device).float(), (torch.arange(10) >= 5).float().to(device)).cpu()
+    assert float(perfect[0]) == pytest.approx(1.0)
+    one_class = flat.roc_auc(torch.rand(10).to(device), torch.ones(10, device=device)).cpu()
+    assert one_class[0] != one_class[0] and one_class[1] == 0
+    bad = torch.rand(50)
+    bad[7] = float("nan")
+    out = flat.roc_auc(bad.to(device), torch.ones(50, device=device)).cpu()
+    assert out[0] != out[0] and out[1] == 1
