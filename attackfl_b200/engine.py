@@ -465,13 +465,16 @@ class Federation:
         native = self.backend == "native"
         lie = [sp for sp in attackers if sp.attack_mode == "LIE"]
         if lie and defer_lie:
-            # fused multi-GPU path: the moments are computed inside the K1-fused pass over peer memory
+            # the moments are computed inside the K1 pass of the aggregation (one GPU: the same launch as FedAvg;
+            # N GPUs: the K1-fused pass over peer memory)
             member = torch.zeros(len(lie), self.C)
             for q, sp in enumerate(lie):
                 member[q, subsets[sp.index]] = 1.0
             info["_lie_specs"] = lie
             info["_lie_member"] = member
             info["_lie_z"] = torch.tensor([float((sp.attack_args or [0.74])[0]) for sp in lie])
+            if rows_all is not None:
+                info["_lie_ref"] = (center if center is not None else rows_all[genuine[0]]).contiguous()
         elif lie:
             if native:
                 from .ops import flat
@@ -607,6 +610,7 @@ class Federation:
     def _aggregate(self, rows_all: torch.Tensor, reporting: List[int]) -> Dict[str, object]:
         s = self.cfg.server
         info: Dict[str, object] = {}
+        info_in, self._agg_info = getattr(self, "_agg_info", None), None      # deferred LIE request of this round
         native = self.backend == "native"
         sel = rows_all if len(reporting) == rows_all.shape[0] else rows_all[reporting]
         sizes = [self.sizes[c] for c in reporting]
@@ -617,7 +621,18 @@ class Federation:
                 w = torch.tensor(sizes, dtype=torch.float32)
                 w = (w / w.sum()).to(self.device)
                 bc = self.rows[:self.CL] if (not self.ctx.distributed or self.fused_comm is None) else None
-                flat.fedavg(sel.contiguous(), w, out=self.global_row, bcast=bc)
+                lie_specs = info_in.pop("_lie_specs", None) if info_in is not None else None
+                if lie_specs:
+                    # K1 + K2 in ONE pass: FedAvg, broadcast and every LIE attacker's mean / std / crafted row
+                    member = info_in.pop("_lie_member")[:, reporting]
+                    _, _, _, lrows = flat.fedavg(sel.contiguous(), w, out=self.global_row, bcast=bc, member=member,
+                                                 z=info_in.pop("_lie_z"), ref=info_in.pop("_lie_ref"), want_lie=True,
+                                                 strict_k1=self.cfg.attack.strict_reference)
+                    for q, sp in enumerate(lie_specs):
+                        self.crafted[sp.index] = lrows[q]
+                        self.crafted_own[sp.index] = False
+                else:
+                    flat.fedavg(sel.contiguous(), w, out=self.global_row, bcast=bc)
                 self._rows_hold_global = bc is not None
             else:
                 self.global_row.copy_(agg.fedavg(sel, sizes))
@@ -694,6 +709,7 @@ class Federation:
         w = w / w.sum()
         lie_specs = info.pop("_lie_specs", None)
         member, z = info.pop("_lie_member", None), info.pop("_lie_z", None)
+        info.pop("_lie_ref", None)
         ref = center if center is not None else self.init_row
         rows = self.fused_comm.fedavg(w, member, z, ref.contiguous(), self.cfg.attack.strict_reference)
         if lie_specs:
@@ -984,10 +1000,11 @@ class Federation:
         # ---- UPDATE: result flags + losses (the only per-client scalars that reach the host)
         mark("train_enqueued")
         flags = torch.zeros(self.C, 3, device=self.device)
-        for j, c in enumerate(self.local):
-            flags[c, 0] = loss[j, 1]
-            flags[c, 1] = loss[j, 0]
-            flags[c, 2] = float(max(sizes_local[j], 0))
+        if self.local:                                            # local clients are one contiguous block of ids
+            lo_c, n_c = self.local[0], len(self.local)
+            flags[lo_c:lo_c + n_c, 0] = loss[:n_c, 1]
+            flags[lo_c:lo_c + n_c, 1] = loss[:n_c, 0]
+            flags[lo_c:lo_c + n_c, 2] = torch.tensor([float(max(x, 0)) for x in sizes_local], device=self.device)
         if self.ctx.distributed:
             self.ctx.all_reduce_sum(flags)
         reporting = list(starting)
@@ -1018,7 +1035,9 @@ class Federation:
             genuine = [c for c in reporting if not self.specs[c].attack]
             center = self.global_row.clone() if (self.have_global and self.mode != "hyper") else None
             with self.timer.phase("craft"):
-                info.update(self._prepare_crafts(rows_all, genuine, center, defer_lie=fused))
+                one_pass = (self.backend == "native" and self.mode == "fedavg" and not self.ctx.distributed
+                            and rows_all is not None)
+                info.update(self._prepare_crafts(rows_all, genuine, center, defer_lie=fused or one_pass))
             self.genuine_prev = genuine
             if self.fused_comm is not None and os.environ.get("ATTACKFL_DEBUG_OWNERSHIP"):
                 self.fused_comm.assert_ownership(reporting)
@@ -1045,6 +1064,7 @@ class Federation:
                 elif self.mode == "hyper":
                     info.update(self._hyper_round(rows_all, reporting))
                 else:
+                    self._agg_info = info
                     info.update(self._aggregate(rows_all, reporting))
             if info.get("failed"):
                 ok = False
