@@ -33,6 +33,8 @@ def main():
     ap.add_argument("--rows", type=int, default=1, help="client rows per rank")
     ap.add_argument("--sizes-mb", default="1,4,16,64,256,1024")
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--tune", action="store_true",
+                    help="time the fused kernel over pipeline depths (ATTACKFL_FUSED_CHUNKS) and grid caps (ATTACKFL_FUSED_MAX_BLOCKS)")
     a = ap.parse_args()
     ctx = pctx.init_from_env("cuda")
     assert ctx.distributed, "run under torchrun with >= 2 ranks"
@@ -112,6 +114,26 @@ def main():
             err_nvls = float((glob - part).abs().max())
             rows.copy_(keep); torch.cuda.synchronize(); dist.barrier()
             paths.insert(1, ("fused_nvls", lambda: fused(True)))
+        if a.tune:
+            best = None
+            fn = (lambda: fused(True)) if (mc_part and mc_glob) else fused
+            for blocks in (148, 296, 592):
+                for chunks in (1, 2, 4, 8, 16, 32):
+                    os.environ["ATTACKFL_FUSED_CHUNKS"] = str(chunks)
+                    os.environ["ATTACKFL_FUSED_MAX_BLOCKS"] = str(blocks)
+                    t = timeit(fn)
+                    rec = {"tune": True, "size_mb": mb, "gpus": G, "rows_per_rank": R, "chunks": chunks, "max_blocks": blocks,
+                           "nvls": bool(mc_part and mc_glob), "ms": round(t * 1e3, 4)}
+                    if best is None or t < best[0]:
+                        best = (t, chunks, blocks)
+                    if rank == 0:
+                        print(json.dumps(rec), flush=True)
+            os.environ.pop("ATTACKFL_FUSED_CHUNKS", None); os.environ.pop("ATTACKFL_FUSED_MAX_BLOCKS", None)
+            t = timeit(fn)
+            if rank == 0:
+                print(json.dumps({"tune": True, "size_mb": mb, "default_ms": round(t * 1e3, 4), "best_ms": round(best[0] * 1e3, 4),
+                                  "best_chunks": best[1], "best_max_blocks": best[2]}), flush=True)
+            paths = []
         for name, fn in paths:
             t = timeit(fn)
             nv_bytes = (G - 1) / G * S              # per direction per rank: partial slices in, result slices out
