@@ -65,6 +65,14 @@ nat.emit(list(range(8)))
 # ---- ScionFL
 flat.scion_cosine_distances(torch.randn(64, D, device=dev), torch.ones(D, device=dev), seed=3)
 
+# ---- slice-owned ScionFL scoring over row pointers, per-round indices, single-block ROC-AUC
+rs = torch.randn(64, D, device=dev)
+bits, counts, minmax = flat.scion_quantize(rs, torch.ones(D, device=dev), 3, row0=0)
+lo, hi = flat.scion_clipped_levels(counts, minmax, float(D))
+flat.scion_scores_ptrs([bits[i].data_ptr() for i in range(64)], D // 32, 0, D // 32, torch.ones(D, device=dev), torch.stack([lo, hi], 1))
+flat.round_indices(16384, torch.full((8,), 14000, dtype=torch.int32, device=dev), torch.arange(8, dtype=torch.int32, device=dev), 5, 14000, 1)
+flat.roc_auc(torch.rand(4096, device=dev), (torch.rand(4096, device=dev) < 0.3).float())
+
 # ---- ICU training (interpreter + tensor-core trainer) and inference
 name = "TransformerModel"
 layT = FlatLayout.from_module(models.build(name))
