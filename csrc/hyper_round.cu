@@ -318,21 +318,39 @@ __global__ void __launch_bounds__(kRT) hyper_round_kernel(HRArgs a) {
 #pragma unroll
       for (int j = 0; j < J; ++j) { const int h = lane + 32 * j; fl[j] = h < H ? f[h] : 0.f; }
       for (int64_t d = gw; d < a.rows; d += 2 * nw) {
+        // every load of the two rows (W, m, v: 24 independent 128-byte warp loads) is issued before the first store: the
+        // three arrays may alias as far as the compiler knows, so loads written after a store would wait for it and the
+        // pass would run at the latency of one row at a time (measured 1.75 TB/s for the whole kernel before)
+        float wr[2][J], mr[2][J], vr[2][J], cdr[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int64_t dd = d + u * nw;
+          cdr[u] = dd < a.rows ? coef * a.delta[dd] : 0.f;
+#pragma unroll
+          for (int j = 0; j < J; ++j) {
+            const int h = lane + 32 * j;
+            const bool ok = dd < a.rows && h < H;
+            const int64_t it = dd * H + h;
+            wr[u][j] = ok ? a.head_w[it] : 0.f;
+            mr[u][j] = ok ? a.mw[it] : 0.f;
+            vr[u][j] = ok ? a.vw[it] : 0.f;
+          }
+        }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int64_t dd = d + u * nw;
           if (dd >= a.rows) break;
-          const float cd = coef * a.delta[dd];
+          const float cd = cdr[u];
 #pragma unroll
           for (int j = 0; j < J; ++j) {
             const int h = lane + 32 * j;
             if (h < H) {
               const int64_t it = dd * H + h;
               const float g = cd * fl[j];
-              const float mi = a.b1 * a.mw[it] + (1.f - a.b1) * g;
-              const float vi = a.b2 * a.vw[it] + (1.f - a.b2) * g * g;
+              const float mi = a.b1 * mr[u][j] + (1.f - a.b1) * g;
+              const float vi = a.b2 * vr[u][j] + (1.f - a.b2) * g * g;
               a.mw[it] = mi; a.vw[it] = vi;
-              a.head_w[it] -= stepsz * (mi / (sqrtf(vi) * isq + a.eps));
+              a.head_w[it] = wr[u][j] - stepsz * (mi / (sqrtf(vi) * isq + a.eps));
             }
           }
           if (lane == 0) {
