@@ -80,16 +80,20 @@ __global__ void __launch_bounds__(128) multi_gamma_kernel(const float* G, int R,
   const int pa = n + a;
   if (k <= 1) { if (threadIdx.x == 0) { out[4 * a] = out[4 * a + 1] = out[4 * a + 2] = out[4 * a + 3] = 0.f; } return; }
   const double inv = 1.0 / (double)k;
+  __shared__ int s_sub[200];                                            // the sample, staged once (kmax + 2 <= 200)
+  for (int i = threadIdx.x; i < k; i += blockDim.x) s_sub[i] = S[i];
+  __syncthreads();
   for (int e = threadIdx.x; e < k * k; e += blockDim.x) {
     const int i = e / k, j = e - i * k;
-    gs[i * Rs + j] = G[(int64_t)S[i] * R + S[j]];
+    gs[i * Rs + j] = G[(int64_t)s_sub[i] * R + s_sub[j]];
   }
+  __syncthreads();
   for (int i = threadIdx.x; i < k; i += blockDim.x) {
     double sm = 0.0;
-    for (int t = 0; t < k; ++t) sm += (double)G[(int64_t)S[i] * R + S[t]];
+    for (int t = 0; t < k; ++t) sm += (double)gs[i * Rs + t];            // same terms, same order as the global gather
     const float gm = (float)(sm * inv);
     gs[i * Rs + k] = gm; gs[k * Rs + i] = gm;                          // <g_i, mu>
-    const float gp = G[(int64_t)S[i] * R + pa];
+    const float gp = G[(int64_t)s_sub[i] * R + pa];
     gs[i * Rs + k + 1] = gp; gs[(k + 1) * Rs + i] = gp;                // <g_i, p>
   }
   __syncthreads();
