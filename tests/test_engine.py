@@ -206,3 +206,15 @@ def test_trainer_selection_and_both_trainers_learn(tmp_path, trainer, clients, w
 def test_trainer_key_is_validated():
     with pytest.raises(Exception):
         _cfg("fedavg", "TransformerModel", 2, runtime={"trainer": "wgmma"})
+
+
+@pytest.mark.parametrize("rng", ["perm", "torch"])
+def test_both_index_generators_train(tmp_path, rng):
+    """``runtime.index-rng``: keyed permutations (default, one native launch) or argsort of torch.rand keys."""
+    cfg = _cfg("fedavg", "TransformerModel", 3, rounds=2, runtime={"index-rng": rng})
+    fed = Federation(cfg, _specs(3), device="cpu", workdir=str(tmp_path), verbose=False, save=False)
+    idx = fed._round_indices([300, 0, 350])
+    assert idx.shape[0] == 3 and idx.dtype == torch.int32 and int(idx[0, 0, :300].min()) >= 0
+    assert len(set(idx[2, 1, :350].tolist())) == 350 and int(idx[0, 0, 300:].max()) == -1
+    res = fed.run()
+    assert all(r.ok for r in res) and res[-1].metric > 0.6
